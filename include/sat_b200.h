@@ -1,0 +1,149 @@
+/* sat_b200 -- C ABI of the B200-native soft-attention LSTM caption decoder.
+ *
+ * Drop-in boundary for the hot path of yvokeller/Show-Attend-and-Tell (attention.py, decoder.py and the
+ * loss lines of train.py).  The reference has no FFI layer: its boundary is the nn.Module surface
+ * (SURVEY.md section 8(b)).  The Python modules in show-attend-and-tell_b200/ keep that surface and call
+ * these entry points through ctypes.  Everything here takes plain device pointers, sizes/strides and a
+ * cudaStream_t (as void*); no torch types; the library never allocates or frees device memory.
+ *
+ * All functions return 0 on success or a negative error code; sat_last_error() returns a thread-local
+ * message.  There is no CPU fallback: every entry point requires an sm_100 device.
+ */
+#ifndef SAT_B200_H
+#define SAT_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SAT_DTYPE_F32 0   /* storage + arithmetic fp32 (true-fp32 FMA GEMMs): bit-exact beam tokens, config c1/c4 */
+#define SAT_DTYPE_BF16 1  /* bf16 storage / tensor-core operands, fp32 accumulate, fp32 softmax/alphas/cell state */
+
+const char* sat_last_error(void);
+int sat_version(void);
+/* debug knob: 1 = run bf16 GEMMs on the SIMT kernel (bring-up cross-check of the tcgen05 kernel) */
+int sat_set_force_simt(int on);
+
+/* Generic GEMM  C[M,N] = act(A[M,K] * B[N,K]^T + bias[N])  (nn.Linear: attention.py:15-16, decoder.py:99,125,139-145).
+ * a_kmajor: A[m*lda+k] (1) or A[k*lda+m] (0); same for B.  Cf (fp32) and/or Ct (dtype) outputs, either may be NULL. */
+int sat_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, int a_kmajor, const void* B, int64_t ldb,
+             int b_kmajor, const float* bias, int act, float* Cf, int64_t ldcf, void* Ct, int64_t ldct, int bn_override,
+             void* stream);
+
+/* K2: one fused attention decode step.  Replaces attention.py:14-21 (with W(img_features) hoisted, Q3) and the
+ * gate decoder.py:99-100.  Rows r = img*NB + nb share image img's features (NB = 1 in training, beam width in
+ * caption).  uf[r] = [U h + b_U (H) | f_beta h + b (D)] fp32.  Outputs alpha fp32, ctx / z (gated ctx) in dtype. */
+int sat_attn_step_fwd(int dtype, int NI, int NB, int L, int D, int H, const void* a, const void* wa, const float* uf,
+                      int64_t ld_uf, const float* v, const float* bv, int gate, float* alpha, int64_t ld_alpha,
+                      void* ctx, int64_t ld_ctx, void* z, int64_t ld_z, void* stream);
+
+/* K2 backward (autograd of the lines above inside loss.backward(), train.py:163). */
+int sat_attn_step_bwd(int dtype, int B, int L, int D, int H, const void* a, const void* wa, const float* uf, int64_t ld_uf,
+                      const float* v, const float* alpha, int64_t ld_alpha, const void* ctx, int64_t ld_ctx,
+                      const float* dz, int64_t ld_dz, const float* dctx_extra, int64_t ld_dce, const float* galpha,
+                      int64_t ld_ga, int gate, void* duf, int64_t ld_duf, float* dwa_acc, float* dv_acc, float* dbv_acc,
+                      float* da_acc, int first, void* stream);
+
+/* Arguments of the sequence drivers: Decoder.forward (decoder.py:69-135) and its backward.  Parameter pointers are
+ * the fp32 tensors of the reference state_dict; NULL where a module does not exist (f_* without ado). */
+typedef struct sat_decoder_args {
+    int32_t struct_bytes;       /* sizeof(sat_decoder_args), checked */
+    int32_t dtype;              /* SAT_DTYPE_* compute mode */
+    int32_t B, L, D, H, V, T;   /* T = captions.size(1) - 1 decode steps (decoder.py:77) */
+    int32_t tf, ado, attention, gate;   /* Decoder(...) flags; gate=0 is the "no gating scalar" extension (Q5) */
+    int32_t start_token;        /* 0, or BERT [CLS] = 101 (decoder.py:79-82) */
+    int32_t need_grad;          /* keep activations for sat_decoder_backward */
+    int32_t fused_loss;         /* 1: also compute the train.py:150-162 loss (+ its gradient seed) on device */
+    int32_t a_dtype;            /* dtype of img_features (SAT_DTYPE_*) */
+    float alpha_c;              /* train.py:154 */
+    float reserved0;
+    const void* img_features;   /* (B,L,D), arbitrary strides in elements (Q20) */
+    int64_t a_stride_b, a_stride_l, a_stride_d;
+    const int64_t* captions;    /* (B, T+1) int64, row stride cap_stride */
+    int64_t cap_stride;
+    const float* dropout_mask;  /* (B,T,H) fp32 scaled keep mask, NULL in eval mode (decoder.py:121-125, Q9) */
+    /* parameters */
+    const float* embedding;
+    const float* init_h_w; const float* init_h_b; const float* init_c_w; const float* init_c_b;
+    const float* f_beta_w; const float* f_beta_b;
+    const float* att_U_w; const float* att_U_b; const float* att_W_w; const float* att_W_b;
+    const float* att_v_w; const float* att_v_b;
+    const float* lstm_w_ih; const float* lstm_w_hh; const float* lstm_b_ih; const float* lstm_b_hh;
+    const float* deep_w; const float* deep_b;
+    const float* f_h_w; const float* f_h_b; const float* f_z_w; const float* f_z_b; const float* f_out_w; const float* f_out_b;
+    /* outputs */
+    float* preds;               /* (B,T,V) fp32 (decoder.py:92); may be NULL only with fused_loss */
+    float* alphas;              /* (B,T,L) fp32 (decoder.py:93) */
+    float* loss;                /* [3] fp32: CE mean, alpha regulariser, total (fused_loss) */
+    /* workspace (PyTorch-owned) */
+    void* workspace;
+    int64_t workspace_bytes;
+    void* stream;
+} sat_decoder_args;
+
+typedef struct sat_decoder_grads {
+    int32_t struct_bytes;
+    int32_t reserved;
+    const float* dpreds;        /* (B,T,V) fp32 upstream grad, NULL with fused_loss */
+    const float* dalphas;       /* (B,T,L) fp32 upstream grad or NULL */
+    const float* dloss;         /* device scalar upstream grad of the fused loss (NULL = 1) */
+    /* parameter gradients, fp32, same shapes as the parameters; overwritten; NULL = skip */
+    float* embedding;
+    float* init_h_w; float* init_h_b; float* init_c_w; float* init_c_b;
+    float* f_beta_w; float* f_beta_b;
+    float* att_U_w; float* att_U_b; float* att_W_w; float* att_W_b; float* att_v_w; float* att_v_b;
+    float* lstm_w_ih; float* lstm_w_hh; float* lstm_b_ih; float* lstm_b_hh;
+    float* deep_w; float* deep_b;
+    float* f_h_w; float* f_h_b; float* f_z_w; float* f_z_b; float* f_out_w; float* f_out_b;
+    float* img_features;        /* (B,L,D) fp32 contiguous grad or NULL */
+} sat_decoder_grads;
+
+int sat_decoder_workspace_bytes(const sat_decoder_args* args, int64_t* bytes);
+int sat_decoder_forward(const sat_decoder_args* args);
+int sat_decoder_backward(const sat_decoder_args* args, const sat_decoder_grads* grads);
+
+/* Decoder.caption (decoder.py:160-269) batched over NI images, each with its own shrinking beam.
+ * Outputs per image: n_tokens, tokens[max_len], alphas[max_len][L], status (0 = completed sentence, 1 = the
+ * "No completed sentences found" fallback (Q18), in which case last_alpha holds the live rows' last-step alphas). */
+typedef struct sat_beam_args {
+    int32_t struct_bytes;
+    int32_t dtype;
+    int32_t NI, L, D, H, V;
+    int32_t beam, max_steps;    /* max_steps = 50: the loop runs at most max_steps+1 iterations (Q17) */
+    int32_t ado, attention, gate, bert;  /* bert selects the stop-token set {1,0} instead of {1,102} (Q15) */
+    int32_t start_token;
+    int32_t a_dtype;
+    const void* img_features;   /* (NI,L,D) one row per image (the reference expands it to beam rows, generate_caption.py:89) */
+    int64_t a_stride_b, a_stride_l, a_stride_d;
+    const float* embedding;
+    const float* init_h_w; const float* init_h_b; const float* init_c_w; const float* init_c_b;
+    const float* f_beta_w; const float* f_beta_b;
+    const float* att_U_w; const float* att_U_b; const float* att_W_w; const float* att_W_b;
+    const float* att_v_w; const float* att_v_b;
+    const float* lstm_w_ih; const float* lstm_w_hh; const float* lstm_b_ih; const float* lstm_b_hh;
+    const float* deep_w; const float* deep_b;
+    const float* f_h_w; const float* f_h_b; const float* f_z_w; const float* f_z_b; const float* f_out_w; const float* f_out_b;
+    /* outputs (device) */
+    int32_t* out_len;           /* (NI) number of tokens incl. start */
+    int32_t* out_status;        /* (NI) */
+    int64_t* out_tokens;        /* (NI, max_steps+2) */
+    float* out_alphas;          /* (NI, max_steps+2, L): row 0 is all ones (decoder.py:173) */
+    float* out_last_alpha;      /* (NI, beam, L) last-step alpha of the live rows (fallback return value) */
+    int32_t* out_live;          /* (NI) live rows at loop exit */
+    void* workspace;
+    int64_t workspace_bytes;
+    void* stream;
+} sat_beam_args;
+
+int sat_beam_workspace_bytes(const sat_beam_args* args, int64_t* bytes);
+int sat_beam_search(const sat_beam_args* args);
+
+/* N1 (next row): fused multi-tensor Adam over flat fp32 buffers (train.py:71,164). */
+int sat_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                  float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SAT_B200_H */

@@ -1,0 +1,619 @@
+// Fused soft-attention decode step (attention.py:14-21 + gate decoder.py:99-100), forward and backward.
+//
+// One thread-block CLUSTER per image: CTA `rank` owns the L-chunk [rank*Lc, rank*Lc+Lc) of the
+// image's L locations.  Forward, per CTA:
+//   (0) its contiguous chunk of encoder features a[img, l0:l1, :] is staged into shared memory by the
+//       TMA engine (cp.async.bulk, mbarrier completion) while
+//   (1) scores e_l = v . tanh(Wa[l,:] + Uh) + b_v are computed from coalesced 16-byte streaming loads of
+//       the hoisted projection Wa (warp per location, warp-shuffle reduction),
+//   (2) a chunk-local (online) softmax gives p_l = exp(e_l - m_rank) and s_rank,
+//   (3) the un-normalised partial context sum_l p_l a_l is accumulated from shared memory,
+//   (4) (m, s, partial ctx) are exchanged through distributed shared memory; every CTA finalises the
+//       alphas of its chunk and a D-slice of the context, applies the sigmoid(f_beta h) gate and writes
+//       alpha (fp32), ctx and gated ctx.
+// Each element of `a` and `Wa` is read from HBM exactly once per step: L*(H+D)*sizeof(T) bytes/image.
+// NB > 1 rows per image (beam search) share the staged features.
+#pragma once
+#include "sat_common.cuh"
+
+namespace attn {
+constexpr int THREADS = 256;
+constexpr int NWARPS = THREADS / 32;
+constexpr int MAXC = 8;        // max cluster size (portable)
+constexpr int NCHUNK = 4;      // bulk-copy sub-chunks (separate mbarriers)
+constexpr int GMAX = 8;        // max L-groups in the context phase
+
+struct FwdParams {
+    const void* a;        // (NI, L, D) T
+    const void* wa;       // (NI, L, H) T
+    const float* uf;      // (NR, ld_uf) fp32: [0,H) = U h + b_U ; [H,H+D) = f_beta h + b (pre-sigmoid)
+    int64_t ld_uf;
+    const float* v;       // (H) attention.v.weight
+    const float* bv;      // (1) attention.v.bias
+    float* alpha;         // row r -> alpha + r*ld_alpha (L floats)
+    int64_t ld_alpha;
+    void* ctx;            // T (NR, ld_ctx) un-gated context, or null
+    int64_t ld_ctx;
+    void* z;              // T (NR, ld_z) gated context, or null
+    int64_t ld_z;
+    int NI, NB, L, D, H;
+    int gate;             // apply sigmoid gate
+    int C, Lc, Ds, G;
+};
+
+struct SmemLayout {
+    size_t a_off, uh_off, v_off, e_off, ms_off, ctx_off, f_off, bar_off, total;
+    int lcpad;
+};
+
+template <typename T>
+inline SmemLayout fwd_layout(int NBG, int NB, int Lc, int D, int H, int G) {
+    SmemLayout s;
+    size_t o = 0;
+    const size_t a_bytes = ((size_t)Lc * D * sizeof(T) + 127) & ~(size_t)127;
+    const size_t ctx_bytes = (size_t)G * NBG * D * 4;
+    // single beam group: the partial-context buffer may reuse the staged-feature region
+    const bool alias = (NB <= NBG) && (ctx_bytes <= a_bytes);
+    s.a_off = o; o += a_bytes;
+    s.uh_off = o; o += (size_t)NBG * H * 4;
+    s.v_off = o; o += (size_t)H * 4;
+    s.lcpad = (Lc + 3) & ~3;
+    s.e_off = o; o += (size_t)NBG * s.lcpad * 4;
+    s.ms_off = o; o += 64;
+    if (alias) s.ctx_off = s.a_off; else { s.ctx_off = o; o += ctx_bytes; }
+    s.f_off = o; o += (size_t)MAXC * 8 * 4;
+    o = (o + 15) & ~(size_t)15;
+    s.bar_off = o; o += NCHUNK * 8;
+    s.total = o;
+    return s;
+}
+
+template <typename T, int NBG, bool PRECISE>
+__global__ void __launch_bounds__(THREADS)
+fwd_kernel(FwdParams p, SmemLayout sl) {
+    constexpr int VEC = Vec16<T>::N;
+    extern __shared__ __align__(128) uint8_t smem[];
+    T* a_s = reinterpret_cast<T*>(smem + sl.a_off);
+    float* uh_s = reinterpret_cast<float*>(smem + sl.uh_off);
+    float* v_s = reinterpret_cast<float*>(smem + sl.v_off);
+    float* e_s = reinterpret_cast<float*>(smem + sl.e_off);
+    float* ms_s = reinterpret_cast<float*>(smem + sl.ms_off);     // [nb][2]
+    float* ctx_s = reinterpret_cast<float*>(smem + sl.ctx_off);   // [g][nb][D]
+    float* f_s = reinterpret_cast<float*>(smem + sl.f_off);       // [rank][8]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sl.bar_off);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int rank = blockIdx.x;            // == cluster CTA rank (gridDim.x == cluster size)
+    const int img = blockIdx.y;
+    const int L = p.L, D = p.D, H = p.H, C = p.C;
+    const int l0 = min(L, rank * p.Lc), l1 = min(L, l0 + p.Lc);
+    const int Lr = l1 - l0;
+    const int lcpad = sl.lcpad;
+
+    // (0) stage this CTA's feature chunk with the TMA engine
+    const size_t row_bytes = (size_t)D * sizeof(T);
+    const int rows_per_chunk = (Lr + NCHUNK - 1) / NCHUNK;
+    if (tid == 0) {
+        for (int c = 0; c < NCHUNK; ++c) mbar_init(&bars[c], 1);
+        mbar_fence_init();
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(p.a) + ((size_t)img * L + l0) * row_bytes;
+        for (int c = 0; c < NCHUNK; ++c) {
+            const int r0 = min(Lr, c * rows_per_chunk), r1 = min(Lr, r0 + rows_per_chunk);
+            const uint32_t bytes = (uint32_t)((r1 - r0) * row_bytes);
+            if (bytes) {
+                mbar_expect_tx(&bars[c], bytes);
+                bulk_g2s(reinterpret_cast<uint8_t*>(a_s) + (size_t)r0 * row_bytes, src + (size_t)r0 * row_bytes, bytes, &bars[c]);
+            } else {
+                mbar_arrive(&bars[c]);
+            }
+        }
+    }
+    for (int i = tid; i < H; i += THREADS) v_s[i] = p.v[i];
+    const float bv = p.bv[0];
+    const int HV = H / VEC;
+    const int nchunks = D / VEC;
+    const T* wa_img = reinterpret_cast<const T*>(p.wa) + (size_t)img * L * H;
+    bool a_ready = false;
+
+    for (int bg = 0; bg * NBG < p.NB; ++bg) {
+        const int row_base = img * p.NB + bg * NBG;
+        const int nb_valid = min(NBG, p.NB - bg * NBG);
+        for (int i = tid; i < NBG * H; i += THREADS) {
+            const int nb = i / H, h = i - nb * H;
+            uh_s[i] = (nb < nb_valid) ? p.uf[(int64_t)(row_base + nb) * p.ld_uf + h] : 0.0f;
+        }
+        __syncthreads();
+
+        // (1) scores: warp per location, lanes stride over 16-byte chunks of the Wa row
+        for (int li = warp; li < Lr; li += NWARPS) {
+            const T* wrow = wa_img + (size_t)(l0 + li) * H;
+            float s[NBG];
+#pragma unroll
+            for (int nb = 0; nb < NBG; ++nb) s[nb] = 0.0f;
+            for (int cb = 0; cb < HV; cb += 128) {
+                uint4 u[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int c = cb + lane + 32 * j;
+                    u[j] = (c < HV) ? ldg_stream16(wrow + (size_t)c * VEC) : make_uint4(0, 0, 0, 0);
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int c = cb + lane + 32 * j;
+                    if (c < HV) {
+                        float w[VEC];
+                        Vec16<T>::unpack(u[j], w);
+                        const float* vv = v_s + c * VEC;
+#pragma unroll
+                        for (int nb = 0; nb < NBG; ++nb) {
+                            const float* uu = uh_s + nb * H + c * VEC;
+#pragma unroll
+                            for (int i = 0; i < VEC; ++i) s[nb] = fmaf(vv[i], sat_tanh<PRECISE>(w[i] + uu[i]), s[nb]);
+                        }
+                    }
+                }
+            }
+#pragma unroll
+            for (int nb = 0; nb < NBG; ++nb) {
+                const float t = warp_sum(s[nb]);
+                if (lane == 0) e_s[nb * lcpad + li] = t + bv;
+            }
+        }
+        __syncthreads();
+
+        // (2) chunk-local softmax statistics: warp nb handles beam row nb
+        for (int nb = warp; nb < NBG; nb += NWARPS) {
+            float m = -INFINITY;
+            for (int li = lane; li < Lr; li += 32) m = fmaxf(m, e_s[nb * lcpad + li]);
+            m = warp_max(m);
+            float sum = 0.0f;
+            for (int li = lane; li < Lr; li += 32) {
+                const float pe = sat_exp<PRECISE>(e_s[nb * lcpad + li] - m);
+                e_s[nb * lcpad + li] = pe;
+                sum += pe;
+            }
+            sum = warp_sum(sum);
+            if (lane == 0) { ms_s[nb * 2] = m; ms_s[nb * 2 + 1] = sum; }
+        }
+        __syncthreads();
+
+        // (3) partial context from the staged features
+        if (!a_ready) {
+            for (int c = 0; c < NCHUNK; ++c) mbar_wait(&bars[c], 0);
+            a_ready = true;
+        }
+        {
+            // thread -> (L-group g, 16-byte chunk ch); for wide D one thread owns up to KDMAX chunks
+            const int G = p.G;
+            constexpr int KDMAX = 2;
+            float acc[KDMAX][NBG][VEC];
+#pragma unroll
+            for (int kd = 0; kd < KDMAX; ++kd)
+#pragma unroll
+                for (int nb = 0; nb < NBG; ++nb)
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) acc[kd][nb][i] = 0.0f;
+            const bool wide = nchunks >= THREADS;
+            const int g = wide ? 0 : tid / nchunks;
+            const int ch0 = wide ? tid : tid - g * nchunks;
+            const int lstep = wide ? 1 : G;
+            if (g < G) {
+#pragma unroll
+                for (int kd = 0; kd < KDMAX; ++kd) {
+                    const int ch = ch0 + kd * THREADS;
+                    if (ch < nchunks && (wide || kd == 0)) {
+#pragma unroll 4
+                        for (int li = g; li < Lr; li += lstep) {
+                            const uint4 u = *reinterpret_cast<const uint4*>(a_s + (size_t)li * D + ch * VEC);
+                            float f[VEC];
+                            Vec16<T>::unpack(u, f);
+#pragma unroll
+                            for (int nb = 0; nb < NBG; ++nb) {
+                                const float pe = e_s[nb * lcpad + li];
+#pragma unroll
+                                for (int i = 0; i < VEC; ++i) acc[kd][nb][i] = fmaf(pe, f[i], acc[kd][nb][i]);
+                            }
+                        }
+                    }
+                }
+            }
+            __syncthreads();        // ctx_s may alias the staged features: all reads of a_s are done
+            if (g < G) {
+#pragma unroll
+                for (int kd = 0; kd < KDMAX; ++kd) {
+                    const int ch = ch0 + kd * THREADS;
+                    if (ch < nchunks && (wide || kd == 0)) {
+#pragma unroll
+                        for (int nb = 0; nb < NBG; ++nb)
+#pragma unroll
+                            for (int i = 0; i < VEC; ++i) ctx_s[((size_t)g * NBG + nb) * D + ch * VEC + i] = acc[kd][nb][i];
+                    }
+                }
+            }
+            if (G > 1) {
+                __syncthreads();
+                for (int i = tid; i < NBG * D; i += THREADS) {
+                    float t = ctx_s[i];
+                    for (int gg = 1; gg < G; ++gg) t += ctx_s[(size_t)gg * NBG * D + i];
+                    ctx_s[i] = t;
+                }
+            }
+        }
+        // (4) cluster exchange
+        cluster_sync_all();
+        if (tid < NBG) {
+            float mr[MAXC], sr[MAXC];
+            float M = -INFINITY;
+            for (int r = 0; r < C; ++r) {
+                const uint32_t ad = dsmem_addr(ms_s + tid * 2, r);
+                mr[r] = dsmem_ld_f32(ad);
+                sr[r] = dsmem_ld_f32(ad + 4);
+                M = fmaxf(M, mr[r]);
+            }
+            float S = 0.0f;
+            for (int r = 0; r < C; ++r) { mr[r] = sat_exp<PRECISE>(mr[r] - M); S = fmaf(sr[r], mr[r], S); }
+            const float inv = 1.0f / S;
+            for (int r = 0; r < C; ++r) f_s[r * 8 + tid] = mr[r] * inv;
+        }
+        __syncthreads();
+        for (int i = tid; i < nb_valid * Lr; i += THREADS) {
+            const int nb = i / Lr, li = i - nb * Lr;
+            p.alpha[(int64_t)(row_base + nb) * p.ld_alpha + l0 + li] = e_s[nb * lcpad + li] * f_s[rank * 8 + nb];
+        }
+        {
+            const int d0 = min(D, rank * p.Ds), d1 = min(D, d0 + p.Ds);
+            const int nd = d1 - d0;
+            for (int i = tid; i < nb_valid * nd; i += THREADS) {
+                const int nb = i / nd, d = d0 + (i - nb * nd);
+                float t = 0.0f;
+                for (int r = 0; r < C; ++r) t = fmaf(f_s[r * 8 + nb], dsmem_ld_f32(dsmem_addr(ctx_s + nb * D + d, r)), t);
+                const int64_t row = row_base + nb;
+                if (p.ctx) reinterpret_cast<T*>(p.ctx)[row * p.ld_ctx + d] = from_f32<T>(t);
+                if (p.z) {
+                    const float g = p.gate ? sat_sigmoid<PRECISE>(p.uf[row * p.ld_uf + H + d]) : 1.0f;
+                    reinterpret_cast<T*>(p.z)[row * p.ld_z + d] = from_f32<T>(t * g);
+                }
+            }
+        }
+        cluster_sync_all();   // peers finished reading this CTA's smem; also orders reuse in the next beam group
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// backward of one attention step (NB == 1).  See DESIGN.md "K2-bwd".
+// ------------------------------------------------------------------------------------------------
+struct BwdParams {
+    const void* a;          // (B, L, D) T
+    const void* wa;         // (B, L, H) T
+    const float* uf;        // saved (B, ld_uf) [Uh | f_beta pre]
+    int64_t ld_uf;
+    const float* v;         // (H)
+    const float* alpha;     // saved alpha rows, row b -> alpha + b*ld_alpha
+    int64_t ld_alpha;
+    const void* ctx;        // saved un-gated ctx T (B, ld_ctx)
+    int64_t ld_ctx;
+    const float* dz;        // grad wrt gated context (B, ld_dz) fp32
+    int64_t ld_dz;
+    const float* dctx_extra;  // grad wrt un-gated context (ado path) fp32 or null
+    int64_t ld_dce;
+    const float* galpha;    // external grad wrt alpha rows or null
+    int64_t ld_ga;
+    void* duf;              // T (B, ld_duf): [dUh (H) | d f_beta pre (D)]
+    int64_t ld_duf;
+    float* dwa_acc;         // (B, L, H) fp32 accumulated over time
+    float* dv_acc;          // (B, H) fp32
+    float* dbv_acc;         // (B)   fp32
+    float* da_acc;          // (B, L, D) fp32 or null
+    int first;              // first backward step: overwrite the accumulators
+    int B, L, D, H, gate;
+    int C, Lc, Ds, Hs;
+};
+
+struct BwdSmem {
+    size_t a_off, dctx_off, uh_off, v_off, dal_off, red_off, misc_off, bar_off, total;
+};
+
+template <typename T>
+inline BwdSmem bwd_layout(int Lc, int D, int H) {
+    BwdSmem s;
+    size_t o = 0;
+    s.a_off = o; o += ((size_t)Lc * D * sizeof(T) + 127) & ~(size_t)127;
+    s.dctx_off = o; o += (size_t)D * 4;
+    s.uh_off = o; o += (size_t)H * 4;
+    s.v_off = o; o += (size_t)H * 4;
+    s.dal_off = o; o += (size_t)((Lc + 3) & ~3) * 4 * 2;   // dalpha/de and alpha
+    // the dUh/dv reduction buffer is only live after the features are consumed: reuse their region
+    if ((size_t)2 * H * 4 <= (size_t)Lc * D * sizeof(T)) s.red_off = s.a_off; else { s.red_off = o; o += (size_t)2 * H * 4; }
+    s.misc_off = o; o += 64;
+    o = (o + 15) & ~(size_t)15;
+    s.bar_off = o; o += NCHUNK * 8;
+    s.total = o;
+    return s;
+}
+
+template <typename T, bool PRECISE>
+__global__ void __launch_bounds__(THREADS)
+bwd_kernel(BwdParams p, BwdSmem sl) {
+    constexpr int VEC = Vec16<T>::N;
+    constexpr int JMAX = 24 / VEC;          // 16-byte chunks per lane per h-block (block = 768 elements)
+    extern __shared__ __align__(128) uint8_t smem[];
+    T* a_s = reinterpret_cast<T*>(smem + sl.a_off);
+    float* dctx_s = reinterpret_cast<float*>(smem + sl.dctx_off);
+    float* uh_s = reinterpret_cast<float*>(smem + sl.uh_off);
+    float* v_s = reinterpret_cast<float*>(smem + sl.v_off);
+    float* de_s = reinterpret_cast<float*>(smem + sl.dal_off);
+    const int lcpad = (p.Lc + 3) & ~3;
+    float* al_s = de_s + lcpad;
+    float* red_s = reinterpret_cast<float*>(smem + sl.red_off);   // [2][H]: dUh partial, dv partial
+    float* misc_s = reinterpret_cast<float*>(smem + sl.misc_off); // [0]=sum alpha*dalpha partial, [1]=sum de partial, [2]=S
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sl.bar_off);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int rank = blockIdx.x, b = blockIdx.y;
+    const int L = p.L, D = p.D, H = p.H, C = p.C;
+    const int l0 = min(L, rank * p.Lc), l1 = min(L, l0 + p.Lc);
+    const int Lr = l1 - l0;
+
+    const size_t row_bytes = (size_t)D * sizeof(T);
+    const int rows_per_chunk = (Lr + NCHUNK - 1) / NCHUNK;
+    if (tid == 0) {
+        for (int c = 0; c < NCHUNK; ++c) mbar_init(&bars[c], 1);
+        mbar_fence_init();
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const uint8_t* src = reinterpret_cast<const uint8_t*>(p.a) + ((size_t)b * L + l0) * row_bytes;
+        for (int c = 0; c < NCHUNK; ++c) {
+            const int r0 = min(Lr, c * rows_per_chunk), r1 = min(Lr, r0 + rows_per_chunk);
+            const uint32_t bytes = (uint32_t)((r1 - r0) * row_bytes);
+            if (bytes) {
+                mbar_expect_tx(&bars[c], bytes);
+                bulk_g2s(reinterpret_cast<uint8_t*>(a_s) + (size_t)r0 * row_bytes, src + (size_t)r0 * row_bytes, bytes, &bars[c]);
+            } else {
+                mbar_arrive(&bars[c]);
+            }
+        }
+    }
+    // (0) per-image vectors: dctx = dz * gate (+ extra); d f_beta_pre = dz * ctx * g (1-g) for this CTA's D-slice
+    {
+        const int d0 = min(D, rank * p.Ds), d1 = min(D, d0 + p.Ds);
+        for (int d = tid; d < D; d += THREADS) {
+            const float dzv = p.dz[(int64_t)b * p.ld_dz + d];
+            float g = 1.0f;
+            if (p.gate) g = sat_sigmoid<PRECISE>(p.uf[(int64_t)b * p.ld_uf + H + d]);
+            float dc = dzv * g;
+            if (p.dctx_extra) dc += p.dctx_extra[(int64_t)b * p.ld_dce + d];
+            dctx_s[d] = dc;
+            if (d >= d0 && d < d1) {
+                float dfb = 0.0f;
+                if (p.gate) dfb = dzv * to_f32<T>(reinterpret_cast<const T*>(p.ctx)[(int64_t)b * p.ld_ctx + d]) * g * (1.0f - g);
+                reinterpret_cast<T*>(p.duf)[(int64_t)b * p.ld_duf + H + d] = from_f32<T>(dfb);
+            }
+        }
+        for (int i = tid; i < H; i += THREADS) { v_s[i] = p.v[i]; uh_s[i] = p.uf[(int64_t)b * p.ld_uf + i]; }
+        for (int i = tid; i < Lr; i += THREADS) al_s[i] = p.alpha[(int64_t)b * p.ld_alpha + l0 + i];
+    }
+    __syncthreads();
+    for (int c = 0; c < NCHUNK; ++c) mbar_wait(&bars[c], 0);
+
+    // (1) dalpha_l = dctx . a_l (+ external grad); optional d a
+    const int nchunks = D / VEC;
+    float part = 0.0f;
+    for (int li = warp; li < Lr; li += NWARPS) {
+        float s = 0.0f;
+        for (int ch = lane; ch < nchunks; ch += 32) {
+            const uint4 u = *reinterpret_cast<const uint4*>(a_s + (size_t)li * D + ch * VEC);
+            float f[VEC];
+            Vec16<T>::unpack(u, f);
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) s = fmaf(f[i], dctx_s[ch * VEC + i], s);
+        }
+        s = warp_sum(s);
+        if (p.galpha) s += p.galpha[(int64_t)b * p.ld_ga + l0 + li];
+        const float al = al_s[li];
+        if (lane == 0) de_s[li] = s;
+        part += al * s;     // identical in all lanes
+        if (p.da_acc) {
+            float* dst = p.da_acc + ((size_t)b * L + l0 + li) * D;
+            for (int d = lane; d < D; d += 32) {
+                const float val = al * dctx_s[d];
+                dst[d] = p.first ? val : dst[d] + val;
+            }
+        }
+    }
+    if (lane == 0) misc_s[4 + warp] = part;
+    __syncthreads();
+    if (tid == 0) {
+        float t = 0.0f;
+        for (int w = 0; w < NWARPS; ++w) t += misc_s[4 + w];
+        misc_s[0] = t;
+    }
+    cluster_sync_all();
+    if (tid == 0) {
+        float S = 0.0f;
+        for (int r = 0; r < C; ++r) S += dsmem_ld_f32(dsmem_addr(misc_s, r));
+        misc_s[2] = S;
+    }
+    __syncthreads();
+    {
+        const float S = misc_s[2];
+        for (int i = tid; i < Lr; i += THREADS) de_s[i] = al_s[i] * (de_s[i] - S);   // softmax backward
+    }
+    __syncthreads();
+
+    // (2) pass over Wa: dpre = de_l * v * (1 - tanh^2);  dWa_acc += dpre;  dUh += dpre;  dv += de_l * tanh
+    const int HV = H / VEC;
+    const T* wa_img = reinterpret_cast<const T*>(p.wa) + (size_t)b * L * H;
+    float* dwa_img = p.dwa_acc + (size_t)b * L * H;
+    float dbv_part = 0.0f;
+    for (int i = tid; i < 2 * H; i += THREADS) red_s[i] = 0.0f;
+    __syncthreads();
+    for (int hb = 0; hb * 32 * JMAX < HV; ++hb) {
+        float dU[JMAX][VEC], dV[JMAX][VEC];
+#pragma unroll
+        for (int j = 0; j < JMAX; ++j)
+#pragma unroll
+            for (int i = 0; i < VEC; ++i) { dU[j][i] = 0.0f; dV[j][i] = 0.0f; }
+        for (int li = warp; li < Lr; li += NWARPS) {
+            const float de = de_s[li];
+            if (hb == 0) dbv_part += de;
+            const T* wrow = wa_img + (size_t)(l0 + li) * H;
+            float* drow = dwa_img + (size_t)(l0 + li) * H;
+            uint4 u[JMAX];
+#pragma unroll
+            for (int j = 0; j < JMAX; ++j) {
+                const int c = hb * 32 * JMAX + lane + 32 * j;
+                u[j] = (c < HV) ? ldg_stream16(wrow + (size_t)c * VEC) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int j = 0; j < JMAX; ++j) {
+                const int c = hb * 32 * JMAX + lane + 32 * j;
+                if (c < HV) {
+                    float w[VEC], dp[VEC];
+                    Vec16<T>::unpack(u[j], w);
+#pragma unroll
+                    for (int i = 0; i < VEC; ++i) {
+                        const int h = c * VEC + i;
+                        const float th = sat_tanh<PRECISE>(w[i] + uh_s[h]);
+                        dp[i] = de * v_s[h] * (1.0f - th * th);
+                        dU[j][i] += dp[i];
+                        dV[j][i] = fmaf(de, th, dV[j][i]);
+                    }
+#pragma unroll
+                    for (int i4 = 0; i4 < VEC / 4; ++i4) {
+                        float4* dst = reinterpret_cast<float4*>(drow + (size_t)c * VEC + 4 * i4);
+                        float4 o = make_float4(dp[4 * i4], dp[4 * i4 + 1], dp[4 * i4 + 2], dp[4 * i4 + 3]);
+                        if (!p.first) { const float4 old = *dst; o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w; }
+                        *dst = o;
+                    }
+                }
+            }
+        }
+        // deterministic cross-warp accumulation into red_s
+        for (int w = 0; w < NWARPS; ++w) {
+            if (warp == w) {
+#pragma unroll
+                for (int j = 0; j < JMAX; ++j) {
+                    const int c = hb * 32 * JMAX + lane + 32 * j;
+                    if (c < HV) {
+#pragma unroll
+                        for (int i = 0; i < VEC; ++i) {
+                            red_s[c * VEC + i] += dU[j][i];
+                            red_s[H + c * VEC + i] += dV[j][i];
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+        }
+    }
+    // sum of de over this CTA (all lanes of a warp hold the same dbv_part)
+    if (lane == 0) misc_s[4 + warp] = dbv_part;
+    __syncthreads();
+    if (tid == 0) {
+        float t = 0.0f;
+        for (int w = 0; w < NWARPS; ++w) t += misc_s[4 + w];
+        misc_s[1] = t;
+    }
+    cluster_sync_all();
+    {
+        const int h0 = min(H, rank * p.Hs), h1 = min(H, h0 + p.Hs);
+        for (int h = h0 + tid; h < h1; h += THREADS) {
+            float du = 0.0f, dv = 0.0f;
+            for (int r = 0; r < C; ++r) {
+                du += dsmem_ld_f32(dsmem_addr(red_s + h, r));
+                dv += dsmem_ld_f32(dsmem_addr(red_s + H + h, r));
+            }
+            reinterpret_cast<T*>(p.duf)[(int64_t)b * p.ld_duf + h] = from_f32<T>(du);
+            float* dst = p.dv_acc + (size_t)b * H + h;
+            *dst = p.first ? dv : *dst + dv;
+        }
+        if (rank == 0 && tid == 0) {
+            float t = 0.0f;
+            for (int r = 0; r < C; ++r) t += dsmem_ld_f32(dsmem_addr(misc_s + 1, r));
+            p.dbv_acc[b] = p.first ? t : p.dbv_acc[b] + t;
+        }
+    }
+    cluster_sync_all();
+}
+
+// ---- host launchers -------------------------------------------------------------------------------
+inline void pick_cluster(int NI, int L, int D, size_t elt, int* C_out, int* Lc_out) {
+    int C = 1;
+    // grow the cluster until the staged chunk fits ~96 KB (2 CTAs/SM) and the grid has >= 2 waves
+    while (C < MAXC) {
+        const int Lc = (L + C - 1) / C;
+        const size_t bytes = (size_t)Lc * D * elt;
+        const bool fits = bytes <= 96 * 1024;
+        const bool enough = (int64_t)NI * C >= 2 * 148;
+        if (fits && enough) break;
+        if ((L + 2 * C - 1) / (2 * C) < 2) break;     // keep >= 2 locations per CTA
+        C *= 2;
+    }
+    *C_out = C;
+    *Lc_out = (L + C - 1) / C;
+}
+
+template <typename KernT>
+inline int launch_cluster(KernT kern, dim3 grid, int C, size_t smem, cudaStream_t stream, void** args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = C; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    SAT_CHECK_CUDA(cudaLaunchKernelExC(&cfg, (const void*)kern, args));
+    return SAT_OK;
+}
+
+template <typename T, int NBG, bool PRECISE>
+int launch_fwd_t(FwdParams p, cudaStream_t stream) {
+    constexpr int VEC = Vec16<T>::N;
+    pick_cluster(p.NI, p.L, p.D, sizeof(T), &p.C, &p.Lc);
+    const int nchunks = p.D / VEC;
+    p.G = 1;
+    if (nchunks < THREADS) { p.G = THREADS / nchunks; if (p.G > GMAX) p.G = GMAX; if (p.G < 1) p.G = 1; }
+    p.Ds = (((p.D + p.C - 1) / p.C) + 3) & ~3;
+    SAT_REQUIRE(nchunks <= 2 * THREADS, "attention fwd: D=%d too wide for this build", p.D);
+    SmemLayout sl = fwd_layout<T>(NBG, p.NB, p.Lc, p.D, p.H, p.G);
+    SAT_REQUIRE(sl.total <= 227 * 1024, "attention fwd: staged chunk needs %zu B shared memory (> 227 KB): L=%d D=%d", sl.total, p.L, p.D);
+    auto kern = fwd_kernel<T, NBG, PRECISE>;
+    static size_t configured = 0;
+    if (sl.total > configured) {
+        SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        configured = 227 * 1024;
+    }
+    void* args[] = {&p, &sl};
+    return launch_cluster(kern, dim3(p.C, p.NI), p.C, sl.total, stream, args);
+}
+
+template <typename T, bool PRECISE>
+int launch_fwd(FwdParams p, cudaStream_t stream) {
+    SAT_REQUIRE(p.D % Vec16<T>::N == 0 && p.H % Vec16<T>::N == 0, "attention: D and H must be multiples of %d", Vec16<T>::N);
+    SAT_REQUIRE(p.NB >= 1, "attention: NB >= 1");
+    if (p.NB == 1) return launch_fwd_t<T, 1, PRECISE>(p, stream);
+    if (p.NB <= 3) return launch_fwd_t<T, 3, PRECISE>(p, stream);
+    return launch_fwd_t<T, 5, PRECISE>(p, stream);
+}
+
+template <typename T, bool PRECISE>
+int launch_bwd(BwdParams p, cudaStream_t stream) {
+    SAT_REQUIRE(p.D % Vec16<T>::N == 0 && p.H % Vec16<T>::N == 0, "attention: D and H must be multiples of %d", Vec16<T>::N);
+    pick_cluster(p.B, p.L, p.D, sizeof(T), &p.C, &p.Lc);
+    p.Ds = (p.D + p.C - 1) / p.C;
+    p.Hs = (p.H + p.C - 1) / p.C;
+    BwdSmem sl = bwd_layout<T>(p.Lc, p.D, p.H);
+    SAT_REQUIRE(sl.total <= 227 * 1024, "attention bwd: needs %zu B shared memory (> 227 KB)", sl.total);
+    auto kern = bwd_kernel<T, PRECISE>;
+    static size_t configured = 0;
+    if (sl.total > configured) {
+        SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        configured = 227 * 1024;
+    }
+    void* args[] = {&p, &sl};
+    return launch_cluster(kern, dim3(p.C, p.B), p.C, sl.total, stream, args);
+}
+}  // namespace attn

@@ -1,0 +1,152 @@
+// C-ABI entry points of libsat_b200.so (declared in include/sat_b200.h).
+#include <stdarg.h>
+#include "sat_decoder.cuh"
+#include "sat_beam.cuh"
+
+int g_force_simt = 0;
+static thread_local char g_err[1024] = "";
+
+void sat_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static int require_sm100() {
+    static int ok = -1;
+    if (ok < 0) {
+        int dev = 0;
+        cudaDeviceProp prop;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+            sat_set_error("no CUDA device: sat_b200 has no CPU fallback");
+            return SAT_ERR_CUDA;
+        }
+        ok = (prop.major == 10) ? 1 : 0;
+        if (!ok) sat_set_error("sat_b200 kernels are built for sm_100a only; found sm_%d%d", prop.major, prop.minor);
+    }
+    if (!ok) { sat_set_error("sat_b200 kernels are built for sm_100a only"); return SAT_ERR_UNSUPPORTED; }
+    return SAT_OK;
+}
+
+extern "C" {
+
+const char* sat_last_error(void) { return g_err; }
+int sat_version(void) { return 100; }
+int sat_set_force_simt(int on) { g_force_simt = on ? 1 : 0; return SAT_OK; }
+
+int sat_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, int a_kmajor, const void* B, int64_t ldb,
+             int b_kmajor, const float* bias, int act, float* Cf, int64_t ldcf, void* Ct, int64_t ldct, int bn_override,
+             void* stream) {
+    SAT_TRY(require_sm100());
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (dtype == SAT_DTYPE_F32) {
+        auto e = lin<float>(M, N, bias, act, Cf, ldcf, reinterpret_cast<float*>(Ct), ldct);
+        return gemm<float>(st, reinterpret_cast<const float*>(A), lda, a_kmajor != 0, reinterpret_cast<const float*>(B), ldb,
+                           b_kmajor != 0, M, N, K, e);
+    } else if (dtype == SAT_DTYPE_BF16) {
+        auto e = lin<bf16>(M, N, bias, act, Cf, ldcf, reinterpret_cast<bf16*>(Ct), ldct);
+        return gemm<bf16>(st, reinterpret_cast<const bf16*>(A), lda, a_kmajor != 0, reinterpret_cast<const bf16*>(B), ldb,
+                          b_kmajor != 0, M, N, K, e, bn_override);
+    }
+    sat_set_error("bad dtype %d", dtype);
+    return SAT_ERR_ARG;
+}
+
+int sat_attn_step_fwd(int dtype, int NI, int NB, int L, int D, int H, const void* a, const void* wa, const float* uf,
+                      int64_t ld_uf, const float* v, const float* bv, int gate, float* alpha, int64_t ld_alpha,
+                      void* ctx, int64_t ld_ctx, void* z, int64_t ld_z, void* stream) {
+    SAT_TRY(require_sm100());
+    attn::FwdParams p;
+    memset(&p, 0, sizeof(p));
+    p.a = a; p.wa = wa; p.uf = uf; p.ld_uf = ld_uf; p.v = v; p.bv = bv; p.alpha = alpha; p.ld_alpha = ld_alpha;
+    p.ctx = ctx; p.ld_ctx = ld_ctx; p.z = z; p.ld_z = ld_z;
+    p.NI = NI; p.NB = NB; p.L = L; p.D = D; p.H = H; p.gate = gate;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (dtype == SAT_DTYPE_F32) return attn::launch_fwd<float, true>(p, st);
+    if (dtype == SAT_DTYPE_BF16) return attn::launch_fwd<bf16, false>(p, st);
+    sat_set_error("bad dtype %d", dtype);
+    return SAT_ERR_ARG;
+}
+
+int sat_attn_step_bwd(int dtype, int B, int L, int D, int H, const void* a, const void* wa, const float* uf, int64_t ld_uf,
+                      const float* v, const float* alpha, int64_t ld_alpha, const void* ctx, int64_t ld_ctx,
+                      const float* dz, int64_t ld_dz, const float* dctx_extra, int64_t ld_dce, const float* galpha,
+                      int64_t ld_ga, int gate, void* duf, int64_t ld_duf, float* dwa_acc, float* dv_acc, float* dbv_acc,
+                      float* da_acc, int first, void* stream) {
+    SAT_TRY(require_sm100());
+    attn::BwdParams p;
+    memset(&p, 0, sizeof(p));
+    p.a = a; p.wa = wa; p.uf = uf; p.ld_uf = ld_uf; p.v = v; p.alpha = alpha; p.ld_alpha = ld_alpha;
+    p.ctx = ctx; p.ld_ctx = ld_ctx; p.dz = dz; p.ld_dz = ld_dz; p.dctx_extra = dctx_extra; p.ld_dce = ld_dce;
+    p.galpha = galpha; p.ld_ga = ld_ga; p.duf = duf; p.ld_duf = ld_duf; p.dwa_acc = dwa_acc; p.dv_acc = dv_acc;
+    p.dbv_acc = dbv_acc; p.da_acc = da_acc; p.first = first;
+    p.B = B; p.L = L; p.D = D; p.H = H; p.gate = gate;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (dtype == SAT_DTYPE_F32) return attn::launch_bwd<float, true>(p, st);
+    if (dtype == SAT_DTYPE_BF16) return attn::launch_bwd<bf16, false>(p, st);
+    sat_set_error("bad dtype %d", dtype);
+    return SAT_ERR_ARG;
+}
+
+int sat_decoder_workspace_bytes(const sat_decoder_args* args, int64_t* bytes) {
+    SAT_TRY(check_args(args));
+    SAT_REQUIRE(bytes != nullptr, "null out pointer");
+    if (args->dtype == SAT_DTYPE_F32) { DecWs<float> w; *bytes = carve<float>(*args, w, nullptr); }
+    else { DecWs<bf16> w; *bytes = carve<bf16>(*args, w, nullptr); }
+    return SAT_OK;
+}
+
+int sat_decoder_forward(const sat_decoder_args* args) {
+    SAT_TRY(check_args(args));
+    SAT_TRY(require_sm100());
+    return args->dtype == SAT_DTYPE_F32 ? decoder_forward_t<float>(*args) : decoder_forward_t<bf16>(*args);
+}
+
+int sat_decoder_backward(const sat_decoder_args* args, const sat_decoder_grads* grads) {
+    SAT_TRY(check_args(args));
+    SAT_TRY(require_sm100());
+    SAT_REQUIRE(grads && grads->struct_bytes == (int32_t)sizeof(sat_decoder_grads), "sat_decoder_grads size mismatch");
+    return args->dtype == SAT_DTYPE_F32 ? decoder_backward_t<float>(*args, *grads) : decoder_backward_t<bf16>(*args, *grads);
+}
+
+int sat_beam_workspace_bytes(const sat_beam_args* args, int64_t* bytes) {
+    SAT_TRY(beam_check_args(args));
+    SAT_REQUIRE(bytes != nullptr, "null out pointer");
+    if (args->dtype == SAT_DTYPE_F32) { BeamWs<float> w; *bytes = beam_carve<float>(*args, w, nullptr); }
+    else { BeamWs<bf16> w; *bytes = beam_carve<bf16>(*args, w, nullptr); }
+    return SAT_OK;
+}
+
+int sat_beam_search(const sat_beam_args* args) {
+    SAT_TRY(beam_check_args(args));
+    SAT_TRY(require_sm100());
+    return args->dtype == SAT_DTYPE_F32 ? beam_search_t<float>(*args) : beam_search_t<bf16>(*args);
+}
+
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                            int64_t n, float lr, float b1, float b2, float eps, float wd, float bc1, float bc2, float gs) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        float gr = g[i] * gs;
+        const float pv = p[i];
+        if (wd != 0.0f) gr += wd * pv;
+        const float mi = b1 * m[i] + (1.0f - b1) * gr;
+        const float vi = b2 * v[i] + (1.0f - b2) * gr * gr;
+        m[i] = mi; v[i] = vi;
+        const float denom = sqrtf(vi) / sqrtf(bc2) + eps;       // torch.optim.Adam (train.py:71)
+        p[i] = pv - (lr / bc1) * (mi / denom);
+    }
+}
+
+int sat_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
+                  float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream) {
+    SAT_TRY(require_sm100());
+    if (n <= 0) return SAT_OK;
+    const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
+    adam_kernel<<<misc::grid_for(n), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1,
+                                                                                      beta2, eps, weight_decay, bc1, bc2, grad_scale);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,470 @@
+// Sequence drivers: Decoder.forward (decoder.py:69-135) and its backward (loss.backward(), train.py:163).
+// Host code only launches kernels on the caller's stream; every buffer lives in the PyTorch-owned workspace.
+#pragma once
+#include <type_traits>
+#include "../../include/sat_b200.h"
+#include "sat_common.cuh"
+#include "sat_epilogue.cuh"
+#include "sat_gemm_simt.cuh"
+#include "sat_gemm_tc.cuh"
+#include "sat_attn.cuh"
+#include "sat_misc.cuh"
+
+extern int g_force_simt;
+
+template <typename T> struct IsF32 { static constexpr bool value = std::is_same<T, float>::value; };
+
+template <typename T, typename Epi>
+int gemm(cudaStream_t s, const T* A, int64_t lda, bool a_k, const T* B, int64_t ldb, bool b_k, int M, int N, int K,
+         const Epi& epi, int bn = 0) {
+    if constexpr (IsF32<T>::value) {
+        return simt::launch<float, Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi);
+    } else {
+        if (g_force_simt) return simt::launch<bf16, Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi);
+        return tc::launch<Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi, bn);
+    }
+}
+
+static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+
+template <typename T>
+EpiLinear<T, IsF32<T>::value> lin(int M, int N, const float* bias, int act, float* Cf, int64_t ldcf, T* Ct, int64_t ldct,
+                                  const float* addend = nullptr, int64_t ld_add = 0) {
+    EpiLinear<T, IsF32<T>::value> e;
+    e.bias = bias; e.addend = addend; e.ld_add = ld_add; e.Cf = Cf; e.ldcf = ldcf; e.Ct = Ct; e.ldct = ldct;
+    e.mulmask = nullptr; e.ld_mm = 0; e.act = act; e.M = M; e.N = N; e.remapB = 0; e.remapT = 0;
+    e.vec_ok = al16(bias) && al16(addend) && al16(Cf) && al16(Ct) && (ld_add % 8 == 0) && (ldcf % 8 == 0) && (ldct % 8 == 0);
+    return e;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// workspace carve-up (identical in forward and backward).  Internal activations are TIME-MAJOR (t, b, .)
+// so that every per-step slice is a contiguous (B x width) matrix and the batched weight-gradient GEMMs
+// contract over one affine row index k = t*B + b.  Reference-facing tensors keep the reference layouts.
+// ---------------------------------------------------------------------------------------------------
+template <typename T>
+struct DecWs {
+    T *w_att, *w_uf, *w_gx, *w_gzh, *w_init, *w_out, *w_fh, *w_fz;     // packed compute-dtype weights
+    float *b_uf, *b_g, *b_init;
+    T *a_c, *wa, *abar;
+    float* abar_f;
+    T* E;            // (T,B,H)     embeddings fed to each step
+    float* Xg;       // (T,B,4H)    embedding share of the gate pre-activations (+ biases), interleaved
+    float* UF;       // (T,B,H+D)   [U h | f_beta h] pre-activations
+    T* ZH;           // (T+1,B,D+H) [gated ctx z_t | h_t]  (h_t = state entering step t)
+    float* Cst;      // (T+1,B,H)   cell states
+    T* Gates;        // (T,B,4H)    activated gates
+    T* Ctx;          // (T,B,D)     un-gated context
+    T* Hdrop;        // (T,B,H)     dropout(h_{t+1})
+    float* hc0;      // (B,2H)      [h0 | c0]
+    T *P1, *P2, *Comb;   // ado (T,B,H)
+    int64_t* tok_in; // (T,B) token fed to each step (free-running mode)
+    float* rowloss;  // (B*T)
+    float* logits_tmp;   // (B,T,V) when preds == NULL
+    // backward
+    T* dlog;         // (T,B,Vp)
+    float* dHd;      // (T,B,H)
+    T* dG;           // (T,B,4H)
+    float* dZH;      // (B,D+H)
+    T* dUF;          // (T,B,H+D)
+    float *dh_carry, *dc_carry;
+    float* dwa_acc;  // (B,L,H)
+    T* dwa_t;        // (B,L,H)
+    float *dv_acc, *dbv_acc;
+    T* dE;           // (T,B,H)
+    T* dpre0;        // (B,2H)
+    float* galpha;   // (B,T,L)
+    float* gscratch;
+    float* csum;
+    float* dcomb;    // ado (T,B,H) fp32
+    T *dP1, *dP2;    // ado (T,B,H)
+    float* dctx_all; // ado (T,B,D) fp32
+    int64_t csum_floats;
+    int64_t Vp;
+    int64_t total;
+};
+
+template <typename T>
+int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
+    int64_t off = 0;
+    auto take = [&](int64_t bytes) -> void* {
+        void* p = base ? base + off : nullptr;
+        off += (bytes + 255) & ~(int64_t)255;
+        return p;
+    };
+    const int64_t B = a.B, L = a.L, D = a.D, H = a.H, V = a.V, Tn = a.T;
+    w.Vp = (V + 7) & ~(int64_t)7;
+#define TK(field, count, type) w.field = reinterpret_cast<type*>(take((int64_t)(count) * (int64_t)sizeof(type)))
+    TK(w_att, H * D, T); TK(w_uf, (H + D) * H, T); TK(w_gx, 4 * H * H, T); TK(w_gzh, 4 * H * (D + H), T);
+    TK(w_init, 2 * H * D, T); TK(w_out, V * H, T);
+    TK(w_fh, a.ado ? H * H : 0, T); TK(w_fz, a.ado ? H * D : 0, T);
+    TK(b_uf, H + D, float); TK(b_g, 4 * H, float); TK(b_init, 2 * H, float);
+    const bool a_alias = (a.a_dtype == a.dtype) && a.a_stride_d == 1 && a.a_stride_l == D && a.a_stride_b == L * D &&
+                         al16(a.img_features);
+    TK(a_c, a_alias ? 0 : B * L * D, T);
+    if (a_alias) w.a_c = reinterpret_cast<T*>(const_cast<void*>(a.img_features));
+    TK(wa, a.attention ? B * L * H : 0, T);
+    TK(abar, B * D, T); TK(abar_f, B * D, float);
+    TK(E, B * Tn * H, T); TK(Xg, B * Tn * 4 * H, float); TK(UF, B * Tn * (H + D), float);
+    TK(ZH, B * (Tn + 1) * (D + H), T); TK(Cst, B * (Tn + 1) * H, float);
+    TK(Gates, B * Tn * 4 * H, T); TK(Ctx, B * Tn * D, T); TK(Hdrop, B * Tn * H, T); TK(hc0, B * 2 * H, float);
+    TK(P1, a.ado ? B * Tn * H : 0, T); TK(P2, a.ado ? B * Tn * H : 0, T); TK(Comb, a.ado ? B * Tn * H : 0, T);
+    TK(tok_in, B * Tn, int64_t); TK(rowloss, B * Tn, float);
+    TK(logits_tmp, a.preds ? 0 : B * Tn * V, float);
+    if (a.need_grad) {
+        TK(dlog, B * Tn * w.Vp, T); TK(dHd, B * Tn * H, float); TK(dG, B * Tn * 4 * H, T); TK(dZH, B * (D + H), float);
+        TK(dUF, B * Tn * (H + D), T); TK(dh_carry, B * H, float); TK(dc_carry, B * H, float);
+        TK(dwa_acc, a.attention ? B * L * H : 0, float); TK(dwa_t, a.attention ? B * L * H : 0, T);
+        TK(dv_acc, B * H, float); TK(dbv_acc, B, float);
+        TK(dE, B * Tn * H, T); TK(dpre0, B * 2 * H, T); TK(galpha, B * Tn * L, float);
+        int64_t gs = 4 * H * (D + H);
+        if (gs < (H + D) * H) gs = (H + D) * H;
+        if (gs < 2 * H * D) gs = 2 * H * D;
+        TK(gscratch, gs, float);
+        w.csum_floats = 64 * (V > 4 * H ? V : 4 * H);
+        if (w.csum_floats < 64 * (H + D)) w.csum_floats = 64 * (H + D);
+        TK(csum, w.csum_floats, float);
+        TK(dcomb, a.ado ? B * Tn * H : 0, float); TK(dP1, a.ado ? B * Tn * H : 0, T); TK(dP2, a.ado ? B * Tn * H : 0, T);
+        TK(dctx_all, a.ado ? B * Tn * D : 0, float);
+    }
+#undef TK
+    w.total = off;
+    return off;
+}
+
+static inline int check_args(const sat_decoder_args* a) {
+    SAT_REQUIRE(a != nullptr, "null args");
+    SAT_REQUIRE(a->struct_bytes == (int32_t)sizeof(sat_decoder_args), "sat_decoder_args size mismatch: got %d, library expects %zu",
+                a->struct_bytes, sizeof(sat_decoder_args));
+    SAT_REQUIRE(a->dtype == SAT_DTYPE_F32 || a->dtype == SAT_DTYPE_BF16, "bad dtype %d", a->dtype);
+    SAT_REQUIRE(a->B > 0 && a->L > 0 && a->D > 0 && a->H > 0 && a->V > 0 && a->T > 0, "bad dims");
+    SAT_REQUIRE(a->D % 8 == 0 && a->H % 8 == 0, "D (%d) and H (%d) must be multiples of 8", a->D, a->H);
+    SAT_REQUIRE(!(a->fused_loss && a->ado), "fused_loss with ado is not supported yet");
+    SAT_REQUIRE(a->alphas != nullptr && (a->preds != nullptr || a->fused_loss), "missing output buffers");
+    return SAT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------------------------------
+template <typename T>
+int prep_weights(const sat_decoder_args& a, DecWs<T>& w, cudaStream_t st) {
+    const int D = a.D, H = a.H, V = a.V;
+    if (a.attention) {
+        SAT_TRY(misc::pack_weight<T>(st, w.w_att, D, a.att_W_w, D, H, D, 0, 0));
+        SAT_TRY(misc::pack_weight<T>(st, w.w_uf, H, a.att_U_w, H, H, H, 0, 0));                       // rows [0,H): U
+        SAT_TRY(misc::pack_weight<T>(st, w.w_uf + (size_t)H * H, H, a.f_beta_w, H, D, H, 0, 0));       // rows [H,H+D): f_beta
+        SAT_TRY(misc::pack_bias(st, w.b_uf, a.att_U_b, nullptr, H, 0));
+        SAT_TRY(misc::pack_bias(st, w.b_uf + H, a.f_beta_b, nullptr, D, 0));
+    }
+    // gate weights, rows interleaved (4j+g).  lstm.weight_ih columns: [0,H) embedding, [H,H+D) context.
+    SAT_TRY(misc::pack_weight<T>(st, w.w_gx, H, a.lstm_w_ih, H + D, 4 * H, H, 0, H));
+    SAT_TRY(misc::pack_weight<T>(st, w.w_gzh, D + H, a.lstm_w_ih, H + D, 4 * H, D, H, H));            // cols [0,D): context
+    SAT_TRY(misc::pack_weight<T>(st, w.w_gzh + D, D + H, a.lstm_w_hh, H, 4 * H, H, 0, H));            // cols [D,D+H): hidden
+    SAT_TRY(misc::pack_bias(st, w.b_g, a.lstm_b_ih, a.lstm_b_hh, 4 * H, H));
+    SAT_TRY(misc::pack_weight<T>(st, w.w_init, D, a.init_h_w, D, H, D, 0, 0));
+    SAT_TRY(misc::pack_weight<T>(st, w.w_init + (size_t)H * D, D, a.init_c_w, D, H, D, 0, 0));
+    SAT_TRY(misc::pack_bias(st, w.b_init, a.init_h_b, nullptr, H, 0));
+    SAT_TRY(misc::pack_bias(st, w.b_init + H, a.init_c_b, nullptr, H, 0));
+    if (a.ado) {
+        SAT_REQUIRE(a.f_h_w && a.f_z_w && a.f_out_w, "ado=1 needs f_h/f_z/f_out parameters");
+        SAT_TRY(misc::pack_weight<T>(st, w.w_fh, H, a.f_h_w, H, H, H, 0, 0));
+        SAT_TRY(misc::pack_weight<T>(st, w.w_fz, D, a.f_z_w, D, H, D, 0, 0));
+        SAT_TRY(misc::pack_weight<T>(st, w.w_out, H, a.f_out_w, H, V, H, 0, 0));
+    } else {
+        SAT_TRY(misc::pack_weight<T>(st, w.w_out, H, a.deep_w, H, V, H, 0, 0));
+    }
+    return SAT_OK;
+}
+
+// output layer for steps [t0, t0+nt): nt == T (teacher forcing: one GEMM over all (t,b) rows) or nt == 1.
+template <typename T>
+int output_layer(const sat_decoder_args& a, DecWs<T>& w, cudaStream_t st, int t0, int nt) {
+    const int B = a.B, D = a.D, H = a.H, V = a.V, Tn = a.T;
+    const int M = nt * B;
+    float* logits = a.preds ? a.preds : w.logits_tmp;            // (B,T,V)
+    const T* hd = w.Hdrop + (size_t)t0 * B * H;
+    auto set_out = [&](EpiLinear<T, IsF32<T>::value>& e) {
+        if (nt == 1) { e.Cf = logits + (size_t)t0 * V; e.ldcf = (int64_t)Tn * V; }
+        else { e.Cf = logits; e.ldcf = V; e.remapB = B; e.remapT = Tn; }
+        e.vec_ok = e.vec_ok && (V % 8 == 0);
+    };
+    if (!a.ado) {
+        auto e = lin<T>(M, V, a.deep_b, SAT_ACT_NONE, logits, V, nullptr, 0);
+        set_out(e);
+        return gemm<T>(st, hd, H, true, w.w_out, H, true, M, V, H, e);
+    }
+    // advanced deep output (decoder.py:149-158): relu(f_out(relu(f_h h) + relu(f_z ctx) + emb)), un-gated ctx (Q8)
+    T* p1 = w.P1 + (size_t)t0 * B * H; T* p2 = w.P2 + (size_t)t0 * B * H; T* cb = w.Comb + (size_t)t0 * B * H;
+    const T* ctx = w.Ctx + (size_t)t0 * B * D; const T* emb = w.E + (size_t)t0 * B * H;
+    auto e1 = lin<T>(M, H, a.f_h_b, SAT_ACT_RELU, nullptr, 0, p1, H);
+    SAT_TRY(gemm<T>(st, hd, H, true, w.w_fh, H, true, M, H, H, e1));
+    auto e2 = lin<T>(M, H, a.f_z_b, SAT_ACT_RELU, nullptr, 0, p2, H);
+    SAT_TRY(gemm<T>(st, ctx, D, true, w.w_fz, D, true, M, H, D, e2));
+    misc::add3_kernel<T><<<misc::grid_for((int64_t)M * H), 256, 0, st>>>(cb, p1, p2, emb, (int64_t)M * H);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    auto e3 = lin<T>(M, V, a.f_out_b, SAT_ACT_RELU, logits, V, nullptr, 0);
+    set_out(e3);
+    return gemm<T>(st, cb, H, true, w.w_out, H, true, M, V, H, e3);
+}
+
+template <typename T>
+int decoder_forward_t(const sat_decoder_args& a) {
+    constexpr bool PRECISE = IsF32<T>::value;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(a.stream);
+    DecWs<T> w;
+    const int64_t need = carve<T>(a, w, reinterpret_cast<uint8_t*>(a.workspace));
+    SAT_REQUIRE(a.workspace && a.workspace_bytes >= need, "workspace too small: %lld < %lld", (long long)a.workspace_bytes, (long long)need);
+    SAT_REQUIRE(((uintptr_t)a.workspace & 255) == 0, "workspace must be 256B aligned");
+    const int B = a.B, L = a.L, D = a.D, H = a.H, V = a.V, Tn = a.T;
+    const int64_t zw = D + H;
+    SAT_TRY(prep_weights<T>(a, w, st));
+
+    // features in compute dtype, contiguous (Q20)
+    if (reinterpret_cast<const void*>(w.a_c) != a.img_features) {
+        if (a.a_dtype == SAT_DTYPE_F32)
+            SAT_TRY((misc::cast3d<float, T>(st, w.a_c, reinterpret_cast<const float*>(a.img_features), B, L, D, a.a_stride_b, a.a_stride_l, a.a_stride_d)));
+        else
+            SAT_TRY((misc::cast3d<bf16, T>(st, w.a_c, reinterpret_cast<const bf16*>(a.img_features), B, L, D, a.a_stride_b, a.a_stride_l, a.a_stride_d)));
+    }
+    // initial state (decoder.py:137-147): [h0 | c0] = tanh(abar [init_h; init_c]^T + b)
+    SAT_TRY(misc::mean_l<T>(st, w.a_c, w.abar_f, w.abar, B, L, D));
+    {
+        auto e = lin<T>(B, 2 * H, w.b_init, SAT_ACT_TANH, w.hc0, 2 * H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.abar, D, true, w.w_init, D, true, B, 2 * H, D, e));
+        misc::init_state_scatter_kernel<T><<<sat_cdiv(B * H, 256), 256, 0, st>>>(w.hc0, w.ZH + D, zw, w.Cst, H, B, H);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    }
+    if (a.attention) {
+        // K1: hoisted encoder projection Wa = a W^T + b_W (attention.py:16, Q3)
+        auto e = lin<T>(B * L, H, a.att_W_b, SAT_ACT_NONE, nullptr, 0, w.wa, H);
+        SAT_TRY(gemm<T>(st, w.a_c, D, true, w.w_att, D, true, B * L, H, D, e));
+    } else {
+        // decoder.py:101-105: alpha = 1/L, context = mean(a), no gate; identical for every step
+        dim3 g(Tn, B);
+        misc::bcast_rows_kernel<T><<<g, 128, 0, st>>>(w.ZH, (int64_t)B * zw, zw, w.abar, D, Tn);
+        misc::bcast_rows_kernel<T><<<g, 128, 0, st>>>(w.Ctx, (int64_t)B * D, D, w.abar, D, Tn);
+        misc::fill_kernel<<<misc::grid_for((int64_t)B * Tn * L), 256, 0, st>>>(a.alphas, (int64_t)B * Tn * L, 1.0f / (float)L);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    }
+    // embeddings (decoder.py:85-89) and their share of the gate pre-activations, batched over t when teacher forcing
+    if (a.tf) {
+        misc::gather_bt_kernel<T><<<B * Tn, 128, 0, st>>>(w.E, a.embedding, H, a.captions, a.cap_stride, B, V);
+        SAT_CHECK_CUDA(cudaGetLastError());
+        auto e = lin<T>(B * Tn, 4 * H, w.b_g, SAT_ACT_NONE, w.Xg, 4 * H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.E, H, true, w.w_gx, H, true, B * Tn, 4 * H, H, e));
+    } else {
+        misc::fill_tokens_kernel<<<sat_cdiv(B, 128), 128, 0, st>>>(w.tok_in, B, (int64_t)a.start_token);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    }
+    for (int t = 0; t < Tn; ++t) {
+        T* zh_t = w.ZH + (size_t)t * B * zw;
+        if (!a.tf) {
+            // token fed at step t: start token, then argmax of the previous logits (decoder.py:79-82,132-133)
+            SAT_TRY(misc::gather_rows<T>(st, w.E + (size_t)t * B * H, H, a.embedding, H, w.tok_in + (size_t)t * B, 1, B, V));
+            auto e = lin<T>(B, 4 * H, w.b_g, SAT_ACT_NONE, w.Xg + (size_t)t * B * 4 * H, 4 * H, nullptr, 0);
+            SAT_TRY(gemm<T>(st, w.E + (size_t)t * B * H, H, true, w.w_gx, H, true, B, 4 * H, H, e));
+        }
+        if (a.attention) {
+            float* uf_t = w.UF + (size_t)t * B * (H + D);
+            auto e = lin<T>(B, H + D, w.b_uf, SAT_ACT_NONE, uf_t, H + D, nullptr, 0);
+            SAT_TRY(gemm<T>(st, zh_t + D, zw, true, w.w_uf, H, true, B, H + D, H, e));       // [U h | f_beta h]
+            attn::FwdParams p;
+            memset(&p, 0, sizeof(p));
+            p.a = w.a_c; p.wa = w.wa; p.uf = uf_t; p.ld_uf = H + D; p.v = a.att_v_w; p.bv = a.att_v_b;
+            p.alpha = a.alphas + (size_t)t * L; p.ld_alpha = (int64_t)Tn * L;
+            p.ctx = w.Ctx + (size_t)t * B * D; p.ld_ctx = D;
+            p.z = zh_t; p.ld_z = zw;
+            p.NI = B; p.NB = 1; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
+            SAT_TRY((attn::launch_fwd<T, PRECISE>(p, st)));
+        }
+        // K3: gates = Xg[t] + [z | h] [W_ih[:,H:] | W_hh]^T, LSTM cell in the epilogue (decoder.py:108-115)
+        EpiLstm<T, PRECISE> e;
+        e.xg = w.Xg + (size_t)t * B * 4 * H; e.ld_xg = 4 * H; e.bias = nullptr;
+        e.c_prev = w.Cst + (size_t)t * B * H; e.ld_cp = H;
+        e.c_out = w.Cst + (size_t)(t + 1) * B * H; e.ld_co = H;
+        e.h_next = w.ZH + (size_t)(t + 1) * B * zw + D; e.ld_hn = zw;
+        e.h_out = w.Hdrop + (size_t)t * B * H; e.ld_ho = H;
+        e.mask = a.dropout_mask ? a.dropout_mask + (size_t)t * H : nullptr; e.ld_mask = (int64_t)Tn * H;
+        e.gates = a.need_grad ? w.Gates + (size_t)t * B * 4 * H : nullptr; e.ld_g = 4 * H;
+        e.M = B; e.H = H;
+        SAT_TRY(gemm<T>(st, zh_t, zw, true, w.w_gzh, zw, true, B, 4 * H, D + H, e));
+        if (!a.tf) {
+            SAT_TRY(output_layer<T>(a, w, st, t, 1));
+            if (t + 1 < Tn) {
+                float* logits = (a.preds ? a.preds : w.logits_tmp) + (size_t)t * V;
+                misc::argmax_rows_kernel<<<B, 256, 0, st>>>(logits, (int64_t)Tn * V, V, w.tok_in + (size_t)(t + 1) * B, 1);
+                SAT_CHECK_CUDA(cudaGetLastError());
+            }
+        }
+    }
+    if (a.tf) SAT_TRY(output_layer<T>(a, w, st, 0, Tn));   // K4: one (T*B) x H x V GEMM after the loop
+    if (a.fused_loss) {
+        SAT_REQUIRE(a.loss != nullptr, "fused_loss needs a loss output");
+        const float* logits = a.preds ? a.preds : w.logits_tmp;
+        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, V, V, Tn, a.captions, a.cap_stride, w.rowloss, (T*)nullptr, 0, nullptr, 1.0f);
+        misc::loss_finalize_kernel<<<1, 1024, 0, st>>>(w.rowloss, B * Tn, B * (Tn - 1), a.alphas, B, Tn, L, a.alpha_c, a.loss);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    }
+    return SAT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// backward (BPTT)
+// ---------------------------------------------------------------------------------------------------
+template <typename T>
+int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
+    constexpr bool PRECISE = IsF32<T>::value;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(a.stream);
+    SAT_REQUIRE(a.need_grad, "forward was run without need_grad");
+    DecWs<T> w;
+    const int64_t need = carve<T>(a, w, reinterpret_cast<uint8_t*>(a.workspace));
+    SAT_REQUIRE(a.workspace && a.workspace_bytes >= need, "workspace too small");
+    const int B = a.B, L = a.L, D = a.D, H = a.H, V = a.V, Tn = a.T;
+    const int64_t zw = D + H;
+    const int BT = B * Tn;
+    const int64_t Vp = w.Vp;
+    const float* logits = a.preds ? a.preds : w.logits_tmp;
+
+    // ---- seed: dlogits (T dtype, time-major rows, row pitch Vp) ------------------------------------
+    const float* galpha = g.dalphas;
+    if (a.fused_loss) {
+        const float scale = 1.0f / (float)(B * (Tn - 1));
+        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, V, V, Tn, a.captions, a.cap_stride, nullptr, w.dlog, Vp, g.dloss, scale);
+        if (a.attention) {
+            misc::alpha_reg_grad_kernel<<<sat_cdiv(B * L, 128), 128, 0, st>>>(a.alphas, w.galpha, B, Tn, L, a.alpha_c, g.dloss);
+            galpha = w.galpha;
+        }
+        SAT_CHECK_CUDA(cudaGetLastError());
+    } else {
+        SAT_REQUIRE(g.dpreds != nullptr, "dpreds is NULL");
+        misc::dpreds_to_dlog_kernel<T><<<BT, 256, 0, st>>>(w.dlog, Vp, g.dpreds, a.ado ? logits : nullptr, B, Tn, V);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    }
+
+    // ---- output layer backward, batched over all (t,b) ---------------------------------------------
+    float* g_out_w = a.ado ? g.f_out_w : g.deep_w;
+    float* g_out_b = a.ado ? g.f_out_b : g.deep_b;
+    const T* out_in = a.ado ? w.Comb : w.Hdrop;     // input rows of the V-projection
+    if (g_out_w) {
+        auto e = lin<T>(V, H, nullptr, SAT_ACT_NONE, g_out_w, H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.dlog, Vp, false, out_in, H, false, V, H, BT, e));          // dW = dlog^T X
+    }
+    if (g_out_b) SAT_TRY(misc::colsum<T>(st, w.dlog, Vp, BT, V, g_out_b, w.csum, w.csum_floats));
+    if (!a.ado) {
+        auto e = lin<T>(BT, H, nullptr, SAT_ACT_NONE, w.dHd, H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.dlog, Vp, true, w.w_out, H, false, BT, H, V, e));          // dHdrop = dlog W_out
+    } else {
+        // dcomb = dlog W_fout ; dP1 = dcomb*relu'(P1) ; dP2 = dcomb*relu'(P2) ; dE += dcomb
+        auto e = lin<T>(BT, H, nullptr, SAT_ACT_NONE, w.dcomb, H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.dlog, Vp, true, w.w_out, H, false, BT, H, V, e));
+        misc::relu_bwd_kernel<T><<<misc::grid_for((int64_t)BT * H), 256, 0, st>>>(w.dP1, w.dcomb, w.P1, (int64_t)BT * H);
+        misc::relu_bwd_kernel<T><<<misc::grid_for((int64_t)BT * H), 256, 0, st>>>(w.dP2, w.dcomb, w.P2, (int64_t)BT * H);
+        SAT_CHECK_CUDA(cudaGetLastError());
+        if (g.f_h_w) { auto e1 = lin<T>(H, H, nullptr, SAT_ACT_NONE, g.f_h_w, H, nullptr, 0);
+            SAT_TRY(gemm<T>(st, w.dP1, H, false, w.Hdrop, H, false, H, H, BT, e1)); }
+        if (g.f_h_b) SAT_TRY(misc::colsum<T>(st, w.dP1, H, BT, H, g.f_h_b, w.csum, w.csum_floats));
+        if (g.f_z_w) { auto e1 = lin<T>(H, D, nullptr, SAT_ACT_NONE, g.f_z_w, D, nullptr, 0);
+            SAT_TRY(gemm<T>(st, w.dP2, H, false, w.Ctx, D, false, H, D, BT, e1)); }
+        if (g.f_z_b) SAT_TRY(misc::colsum<T>(st, w.dP2, H, BT, H, g.f_z_b, w.csum, w.csum_floats));
+        auto e2 = lin<T>(BT, H, nullptr, SAT_ACT_NONE, w.dHd, H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.dP1, H, true, w.w_fh, H, false, BT, H, H, e2));            // dHdrop = dP1 W_fh
+        auto e3 = lin<T>(BT, D, nullptr, SAT_ACT_NONE, w.dctx_all, D, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.dP2, H, true, w.w_fz, D, false, BT, D, H, e3));            // dctx (un-gated) = dP2 W_fz
+    }
+
+    // ---- BPTT loop ------------------------------------------------------------------------------------
+    SAT_CHECK_CUDA(cudaMemsetAsync(w.dh_carry, 0, (size_t)B * H * 4, st));
+    SAT_CHECK_CUDA(cudaMemsetAsync(w.dc_carry, 0, (size_t)B * H * 4, st));
+    for (int t = Tn - 1; t >= 0; --t) {
+        dim3 lg(sat_cdiv(H, 128), B);
+        misc::lstm_bwd_kernel<T><<<lg, 128, 0, st>>>(
+            w.Gates + (size_t)t * B * 4 * H, 4 * H, w.Cst + (size_t)t * B * H, H, w.Cst + (size_t)(t + 1) * B * H, H,
+            w.dHd + (size_t)t * B * H, H, a.dropout_mask ? a.dropout_mask + (size_t)t * H : nullptr, (int64_t)Tn * H,
+            w.dh_carry, w.dc_carry, w.dG + (size_t)t * B * 4 * H, 4 * H, B, H);
+        SAT_CHECK_CUDA(cudaGetLastError());
+        // d[z | h_prev] = dG [W_ih[:,H:] | W_hh]
+        {
+            auto e = lin<T>(B, D + H, nullptr, SAT_ACT_NONE, w.dZH, zw, nullptr, 0);
+            SAT_TRY(gemm<T>(st, w.dG + (size_t)t * B * 4 * H, 4 * H, true, w.w_gzh, zw, false, B, D + H, 4 * H, e));
+        }
+        if (a.attention) {
+            attn::BwdParams p;
+            memset(&p, 0, sizeof(p));
+            p.a = w.a_c; p.wa = w.wa; p.uf = w.UF + (size_t)t * B * (H + D); p.ld_uf = H + D;
+            p.v = a.att_v_w; p.alpha = a.alphas + (size_t)t * L; p.ld_alpha = (int64_t)Tn * L;
+            p.ctx = w.Ctx + (size_t)t * B * D; p.ld_ctx = D;
+            p.dz = w.dZH; p.ld_dz = zw;
+            p.dctx_extra = a.ado ? w.dctx_all + (size_t)t * B * D : nullptr; p.ld_dce = D;
+            p.galpha = galpha ? galpha + (size_t)t * L : nullptr; p.ld_ga = (int64_t)Tn * L;
+            p.duf = w.dUF + (size_t)t * B * (H + D); p.ld_duf = H + D;
+            p.dwa_acc = w.dwa_acc; p.dv_acc = w.dv_acc; p.dbv_acc = w.dbv_acc; p.da_acc = nullptr;
+            p.first = (t == Tn - 1);
+            p.B = B; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
+            SAT_TRY((attn::launch_bwd<T, PRECISE>(p, st)));
+            // dh_prev = dZH[:, D:] + [dUh | dfb] [U ; f_beta]
+            auto e = lin<T>(B, H, nullptr, SAT_ACT_NONE, w.dh_carry, H, nullptr, 0, w.dZH + D, zw);
+            SAT_TRY(gemm<T>(st, w.dUF + (size_t)t * B * (H + D), H + D, true, w.w_uf, H, false, B, H, H + D, e));
+        } else {
+            // no attention: z is the constant mean feature; only the hidden path carries on
+            SAT_CHECK_CUDA(cudaMemcpy2DAsync(w.dh_carry, (size_t)H * 4, w.dZH + D, (size_t)zw * 4, (size_t)H * 4, B,
+                                             cudaMemcpyDeviceToDevice, st));
+        }
+    }
+
+    // ---- initial state (decoder.py:137-147) ----------------------------------------------------------
+    misc::dinit_kernel<T><<<sat_cdiv(B * H, 256), 256, 0, st>>>(w.dpre0, w.dh_carry, w.dc_carry, w.hc0, B, H);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    {
+        auto e = lin<T>(2 * H, D, nullptr, SAT_ACT_NONE, w.gscratch, D, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.dpre0, 2 * H, false, w.abar, D, false, 2 * H, D, B, e));
+        if (g.init_h_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_h_w, w.gscratch, (size_t)H * D * 4, cudaMemcpyDeviceToDevice, st));
+        if (g.init_c_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_c_w, w.gscratch + (size_t)H * D, (size_t)H * D * 4, cudaMemcpyDeviceToDevice, st));
+        SAT_TRY(misc::colsum<T>(st, w.dpre0, 2 * H, B, 2 * H, w.gscratch, w.csum, w.csum_floats));
+        if (g.init_h_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_h_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
+        if (g.init_c_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_c_b, w.gscratch + H, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
+    }
+
+    // ---- batched weight gradients (contraction over k = t*B + b) ---------------------------------------
+    {
+        // gate weights: dW_gzh (4H x (D+H)) = dG^T [Z | Hprev] ; dW_gx (4H x H) = dG^T E ; un-interleave rows
+        auto e = lin<T>(4 * H, D + H, nullptr, SAT_ACT_NONE, w.gscratch, zw, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.dG, 4 * H, false, w.ZH, zw, false, 4 * H, D + H, BT, e));
+        if (g.lstm_w_ih) SAT_TRY(misc::unpack_grad(st, g.lstm_w_ih, H + D, w.gscratch, zw, 4 * H, D, H, H));
+        if (g.lstm_w_hh) SAT_TRY(misc::unpack_grad(st, g.lstm_w_hh, H, w.gscratch + D, zw, 4 * H, H, 0, H));
+        auto e2 = lin<T>(4 * H, H, nullptr, SAT_ACT_NONE, w.gscratch, H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.dG, 4 * H, false, w.E, H, false, 4 * H, H, BT, e2));
+        if (g.lstm_w_ih) SAT_TRY(misc::unpack_grad(st, g.lstm_w_ih, H + D, w.gscratch, H, 4 * H, H, 0, H));
+        if (g.lstm_b_ih) SAT_TRY(misc::colsum<T>(st, w.dG, 4 * H, BT, 4 * H, g.lstm_b_ih, w.csum, w.csum_floats, H));
+        if (g.lstm_b_hh) SAT_TRY(misc::colsum<T>(st, w.dG, 4 * H, BT, 4 * H, g.lstm_b_hh, w.csum, w.csum_floats, H));
+    }
+    // embedding: dE = dG W_gx (+ dcomb for ado), scatter-add by token (skipped when frozen / NULL: Q23)
+    if (g.embedding) {
+        SAT_CHECK_CUDA(cudaMemsetAsync(g.embedding, 0, (size_t)V * H * 4, st));
+        auto e = lin<T>(BT, H, nullptr, SAT_ACT_NONE, nullptr, 0, w.dE, H, a.ado ? w.dcomb : nullptr, H);
+        SAT_TRY(gemm<T>(st, w.dG, 4 * H, true, w.w_gx, H, false, BT, H, 4 * H, e));
+        if (a.tf) misc::scatter_add_bt_kernel<T><<<BT, 128, 0, st>>>(g.embedding, H, w.dE, a.captions, a.cap_stride, B, V);
+        else misc::scatter_add_rows_kernel<T><<<BT, 128, 0, st>>>(g.embedding, H, w.dE, w.tok_in, V);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    }
+    if (a.attention) {
+        // [U ; f_beta] grads: dW_uf ((H+D) x H) = dUF^T Hprev  (Hprev = ZH[:, D:], steps 0..T-1)
+        auto e = lin<T>(H + D, H, nullptr, SAT_ACT_NONE, w.gscratch, H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.dUF, H + D, false, w.ZH + D, zw, false, H + D, H, BT, e));
+        if (g.att_U_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_w, w.gscratch, (size_t)H * H * 4, cudaMemcpyDeviceToDevice, st));
+        if (g.f_beta_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_w, w.gscratch + (size_t)H * H, (size_t)D * H * 4, cudaMemcpyDeviceToDevice, st));
+        SAT_TRY(misc::colsum<T>(st, w.dUF, H + D, BT, H + D, w.gscratch, w.csum, w.csum_floats));
+        if (g.att_U_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
+        if (g.f_beta_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_b, w.gscratch + H, (size_t)D * 4, cudaMemcpyDeviceToDevice, st));
+        // encoder projection: dW (H x D) = (sum_t dpre)^T a ; db_W = colsum ; dv, db_v
+        SAT_TRY((misc::cast<float, T>(st, w.dwa_t, w.dwa_acc, (int64_t)B * L * H)));
+        if (g.att_W_w) {
+            auto e2 = lin<T>(H, D, nullptr, SAT_ACT_NONE, g.att_W_w, D, nullptr, 0);
+            SAT_TRY(gemm<T>(st, w.dwa_t, H, false, w.a_c, D, false, H, D, B * L, e2));
+        }
+        if (g.att_W_b) SAT_TRY(misc::colsum<float>(st, w.dwa_acc, H, B * L, H, g.att_W_b, w.csum, w.csum_floats));
+        if (g.att_v_w) SAT_TRY(misc::colsum<float>(st, w.dv_acc, H, B, H, g.att_v_w, w.csum, w.csum_floats));
+        if (g.att_v_b) SAT_TRY(misc::colsum<float>(st, w.dbv_acc, 1, B, 1, g.att_v_b, w.csum, w.csum_floats));
+    }
+    return SAT_OK;
+}

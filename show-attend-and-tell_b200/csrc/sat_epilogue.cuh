@@ -1,0 +1,128 @@
+// GEMM epilogue functors shared by the fp32 SIMT GEMM and the bf16 tcgen05 GEMM.
+// An epilogue consumes NV (multiple of 4) consecutive fp32 accumulator columns of one output row.
+#pragma once
+#include "sat_common.cuh"
+
+enum { SAT_ACT_NONE = 0, SAT_ACT_TANH = 1, SAT_ACT_RELU = 2, SAT_ACT_SIGMOID = 3 };
+
+// out = act(acc + bias[n] + addend[m,n])  -> fp32 and/or T output.  (a1,a4,a5,a8,a9 in SURVEY section 8)
+template <typename T, bool PRECISE>
+struct EpiLinear {
+    const float* bias;       // [N] or null
+    const float* addend;     // fp32 [M, ld_add] or null (may alias Cf: accumulate)
+    int64_t ld_add;
+    float* Cf;               // fp32 out or null
+    int64_t ldcf;
+    T* Ct;                   // T out or null
+    int64_t ldct;
+    const float* mulmask;    // optional fp32 [M, ld_mm] multiplier applied after act (e.g. relu' or dropout) or null
+    int64_t ld_mm;
+    int act;
+    int M, N;
+    int vec_ok;              // all pointers 16B aligned, all ld % 8 == 0
+    int remapB, remapT;      // remapT > 0: GEMM row m = t*remapB + b is stored at output row b*remapT + t
+
+    template <int NV>
+    __device__ __forceinline__ void apply(int m, int n0, const float* acc) const {
+        if (m >= M) return;
+        const int64_t mo = remapT > 0 ? (int64_t)(m % remapB) * remapT + m / remapB : (int64_t)m;
+#pragma unroll
+        for (int q = 0; q < NV / 4; ++q) {
+            const int n = n0 + 4 * q;
+            if (n >= N) return;
+            float v[4] = {acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]};
+            const bool full = vec_ok && (n + 4 <= N);
+            if (full) {
+                if (bias) { float4 b = *reinterpret_cast<const float4*>(bias + n); v[0] += b.x; v[1] += b.y; v[2] += b.z; v[3] += b.w; }
+                if (addend) { float4 b = *reinterpret_cast<const float4*>(addend + (int64_t)m * ld_add + n); v[0] += b.x; v[1] += b.y; v[2] += b.z; v[3] += b.w; }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) if (n + i < N) {
+                    if (bias) v[i] += bias[n + i];
+                    if (addend) v[i] += addend[(int64_t)m * ld_add + n + i];
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                // these activations touch only B x H sized tensors: always use the accurate versions
+                if (act == SAT_ACT_TANH) v[i] = sat_tanh<true>(v[i]);
+                else if (act == SAT_ACT_RELU) v[i] = fmaxf(v[i], 0.0f);
+                else if (act == SAT_ACT_SIGMOID) v[i] = sat_sigmoid<true>(v[i]);
+            }
+            if (mulmask) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) if (n + i < N) v[i] *= mulmask[(int64_t)m * ld_mm + n + i];
+            }
+            if (full) {
+                if (Cf) *reinterpret_cast<float4*>(Cf + mo * ldcf + n) = make_float4(v[0], v[1], v[2], v[3]);
+                if (Ct) {
+                    if (sizeof(T) == 4) {
+                        *reinterpret_cast<float4*>(reinterpret_cast<float*>(Ct) + mo * ldct + n) = make_float4(v[0], v[1], v[2], v[3]);
+                    } else {
+                        __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+                        uint2 u = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+                        *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(Ct) + mo * ldct + n) = u;
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) if (n + i < N) {
+                    if (Cf) Cf[mo * ldcf + n + i] = v[i];
+                    if (Ct) Ct[mo * ldct + n + i] = from_f32<T>(v[i]);
+                }
+            }
+        }
+    }
+};
+
+// LSTM cell epilogue (a7: decoder.py:115 nn.LSTMCell).  The gate GEMM's N axis is gate-interleaved:
+// column n = 4*j + g with g in (i,f,g,o) for hidden unit j, so one group of 4 columns is one unit.
+template <typename T, bool PRECISE>
+struct EpiLstm {
+    const float* xg;         // fp32 [M, ld_xg] pre-activation addend (interleaved) or null
+    int64_t ld_xg;
+    const float* bias;       // fp32 [4H] interleaved or null
+    const float* c_prev;     // fp32 [M, ld_cp]
+    int64_t ld_cp;
+    float* c_out;            // fp32 [M, ld_co]
+    int64_t ld_co;
+    T* h_next;               // [M, ld_hn] un-dropped h for the next step's GEMM operand, or null
+    int64_t ld_hn;
+    T* h_out;                // [M, ld_ho] h * mask (input of the deep-output layer), or null
+    int64_t ld_ho;
+    const float* mask;       // fp32 [M, ld_mask] scaled keep mask or null (eval)
+    int64_t ld_mask;
+    T* gates;                // [M, ld_g] activated gates (interleaved) saved for backward, or null
+    int64_t ld_g;
+    int M, H;
+
+    template <int NV>
+    __device__ __forceinline__ void apply(int m, int n0, const float* acc) const {
+        if (m >= M) return;
+#pragma unroll
+        for (int q = 0; q < NV / 4; ++q) {
+            const int n = n0 + 4 * q;
+            const int j = n >> 2;
+            if (j >= H) return;
+            float p[4] = {acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]};
+            if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + (int64_t)m * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+            if (bias) { float4 x = *reinterpret_cast<const float4*>(bias + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+            const float gi = sat_sigmoid<true>(p[0]);
+            const float gf = sat_sigmoid<true>(p[1]);
+            const float gg = sat_tanh<true>(p[2]);
+            const float go = sat_sigmoid<true>(p[3]);
+            const float c = gf * c_prev[(int64_t)m * ld_cp + j] + gi * gg;
+            const float h = go * sat_tanh<true>(c);
+            c_out[(int64_t)m * ld_co + j] = c;
+            if (h_next) h_next[(int64_t)m * ld_hn + j] = from_f32<T>(h);
+            if (h_out) {
+                const float mk = mask ? mask[(int64_t)m * ld_mask + j] : 1.0f;
+                h_out[(int64_t)m * ld_ho + j] = from_f32<T>(h * mk);
+            }
+            if (gates) {
+                T* g = gates + (int64_t)m * ld_g + n;
+                g[0] = from_f32<T>(gi); g[1] = from_f32<T>(gf); g[2] = from_f32<T>(gg); g[3] = from_f32<T>(go);
+            }
+        }
+    }
+};

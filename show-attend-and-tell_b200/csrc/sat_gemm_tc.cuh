@@ -1,0 +1,256 @@
+// bf16 tensor-core GEMM for sm_100a:  C[M,N] = A[M,K] * B[N,K]^T, fp32 accumulation in TMEM.
+//   * operands staged global -> shared by TMA (cp.async.bulk.tensor, 128B swizzle) through a
+//     multi-stage mbarrier ring,
+//   * tcgen05.mma (cta_group::1, kind::f16, M=128, N=BN, K=16) issued by one elected thread,
+//   * accumulator read back with tcgen05.ld (32x32b.x32) by four epilogue warps that apply a fused
+//     epilogue functor (bias / activation / LSTM cell ...) and write straight to global memory.
+// Either operand may be K-major (row = M/N index, K contiguous) or MN-major (row = K index, M/N
+// contiguous); the latter serves dgrad/wgrad GEMMs without materialised transposes.
+#pragma once
+#include "sat_common.cuh"
+
+namespace tc {
+constexpr int BM = 128, BK = 64, UMMA_K = 16;
+constexpr int THREADS = 192;   // warp0 = TMA producer, warp1 = TMEM alloc + MMA issuer, warps 2-5 = epilogue
+
+template <int BN> struct Cfg {
+    static constexpr int STAGES = (BN <= 64) ? 6 : (BN == 128 ? 5 : 4);
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;   // descriptor version 1 (Blackwell)
+    d |= (uint64_t)2 << 61;   // SWIZZLE_128B
+    return d;
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+        "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+template <int BN, bool A_MN, bool B_MN, typename Epi>
+__global__ void __launch_bounds__(THREADS, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+            int M, int N, int K, Epi epi) {
+    using C = Cfg<BN>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + C::STAGES * C::A_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + C::STAGES;
+    uint64_t* tmem_full_bar = empty_bar + C::STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int nk = (K + BK - 1) / BK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&mapA);
+        tma_prefetch_desc(&mapB);
+        for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_u32(tmem_slot)), "n"(BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (elect_one()) {
+            for (int kb = 0; kb < nk; ++kb) {
+                const int s = kb % C::STAGES;
+                const uint32_t ph = (kb / C::STAGES) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                mbar_expect_tx(&full_bar[s], C::STAGE_BYTES);
+                uint8_t* a_dst = sA + s * C::A_BYTES;
+                uint8_t* b_dst = sB + s * C::B_BYTES;
+                const int k0 = kb * BK;
+                if (!A_MN) {
+                    tma_load_2d(a_dst, &mapA, k0, m0, &full_bar[s]);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < BM / 64; ++c) tma_load_2d(a_dst + c * (BK * 128), &mapA, m0 + c * 64, k0, &full_bar[s]);
+                }
+                if (!B_MN) {
+                    tma_load_2d(b_dst, &mapB, k0, n0, &full_bar[s]);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < BN / 64; ++c) tma_load_2d(b_dst + c * (BK * 128), &mapB, n0 + c * 64, k0, &full_bar[s]);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
+                                       ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            for (int kb = 0; kb < nk; ++kb) {
+                const int s = kb % C::STAGES;
+                const uint32_t ph = (kb / C::STAGES) & 1;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(sA + s * C::A_BYTES);
+                const uint32_t b_addr = smem_u32(sB + s * C::B_BYTES);
+#pragma unroll
+                for (int kk = 0; kk < BK / UMMA_K; ++kk) {
+                    // K-major: 16 elements = 32 B along the swizzled row; MN-major: 16 k-rows of 128 B
+                    const uint64_t ad = A_MN ? make_desc(a_addr + kk * (UMMA_K * 128), BK * 128, 1024)
+                                             : make_desc(a_addr + kk * (UMMA_K * 2), 16, 1024);
+                    const uint64_t bd = B_MN ? make_desc(b_addr + kk * (UMMA_K * 128), BK * 128, 1024)
+                                             : make_desc(b_addr + kk * (UMMA_K * 2), 16, 1024);
+                    umma_bf16(tmem_base, ad, bd, idesc, (kb > 0 || kk > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);          // frees the smem stage when these MMAs retire
+            }
+            umma_commit(tmem_full_bar);              // accumulator complete
+        }
+    } else {
+        const int q = warp & 3;                      // TMEM lane quarter this warp may access
+        mbar_wait(tmem_full_bar, 0);
+        tc_fence_after();
+        const int m = m0 + q * 32 + lane;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+            float v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v);
+            if (n0 + c * 32 < N) epi.template apply<32>(m, n0 + c * 32, v);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(BN) : "memory");
+    }
+}
+
+// ---- host side ---------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+inline EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld elements.
+inline int make_map(CUtensorMap* map, const void* ptr, uint64_t inner, uint64_t outer, int64_t ld,
+                    uint32_t box_inner, uint32_t box_outer) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) { sat_set_error("cuTensorMapEncodeTiled entry point not found"); return SAT_ERR_CUDA; }
+    if (((uintptr_t)ptr & 15) || (ld % 8)) {
+        sat_set_error("tcgen05 GEMM operand needs 16B-aligned base and ld %% 8 == 0 (ptr=%p ld=%lld)", ptr, (long long)ld);
+        return SAT_ERR_ARG;
+    }
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { sat_set_error("cuTensorMapEncodeTiled failed: %d", (int)r); return SAT_ERR_CUDA; }
+    return SAT_OK;
+}
+
+template <int BN, bool A_MN, bool B_MN, typename Epi>
+int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB, int M, int N, int K, const Epi& epi) {
+    auto kern = gemm_kernel<BN, A_MN, B_MN, Epi>;
+    static bool configured = false;
+    if (!configured) {
+        SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+        configured = true;
+    }
+    dim3 grid(sat_cdiv(N, BN), sat_cdiv(M, BM));
+    kern<<<grid, THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(mA, mB, M, N, K, epi);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+inline int pick_bn(int M, int N, bool b_mn) {
+    const int mt = sat_cdiv(M, BM);
+    const int cands[4] = {256, 128, 64, 32};
+    for (int i = 0; i < 4; ++i) {
+        const int bn = cands[i];
+        if (b_mn && bn < 64) break;
+        if (bn > 32 && bn / 2 >= N && !(b_mn && bn == 64)) continue;   // tile far wider than N
+        if (mt * sat_cdiv(N, bn) >= 120) return bn;
+    }
+    return b_mn ? 64 : 32;
+}
+
+template <bool A_MN, bool B_MN, typename Epi>
+int launch_mn(cudaStream_t stream, const bf16* A, int64_t lda, const bf16* B, int64_t ldb, int M, int N, int K,
+              const Epi& epi, int bn) {
+    CUtensorMap mA, mB;
+    if (!A_MN) SAT_TRY(make_map(&mA, A, K, M, lda, 64, BM));
+    else       SAT_TRY(make_map(&mA, A, M, K, lda, 64, BK));
+    const int box_n = bn;
+    if (!B_MN) SAT_TRY(make_map(&mB, B, K, N, ldb, 64, box_n));
+    else       SAT_TRY(make_map(&mB, B, N, K, ldb, 64, BK));
+    switch (bn) {
+        case 256: return launch_bn<256, A_MN, B_MN, Epi>(stream, mA, mB, M, N, K, epi);
+        case 128: return launch_bn<128, A_MN, B_MN, Epi>(stream, mA, mB, M, N, K, epi);
+        case 64:  return launch_bn<64, A_MN, B_MN, Epi>(stream, mA, mB, M, N, K, epi);
+        case 32:
+            if constexpr (!B_MN) return launch_bn<32, A_MN, B_MN, Epi>(stream, mA, mB, M, N, K, epi);
+        default: break;
+    }
+    sat_set_error("bad BN %d", bn);
+    return SAT_ERR_ARG;
+}
+
+template <typename Epi>
+int launch(cudaStream_t stream, const bf16* A, int64_t lda, bool a_kmajor, const bf16* B, int64_t ldb, bool b_kmajor,
+           int M, int N, int K, const Epi& epi, int bn_override = 0) {
+    if (M <= 0 || N <= 0) return SAT_OK;
+    SAT_REQUIRE(K > 0, "tcgen05 GEMM needs K > 0");
+    const int bn = bn_override ? bn_override : pick_bn(M, N, !b_kmajor);
+    if (a_kmajor && b_kmajor) return launch_mn<false, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
+    if (a_kmajor && !b_kmajor) return launch_mn<false, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
+    if (!a_kmajor && b_kmajor) return launch_mn<true, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
+    return launch_mn<true, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
+}
+}  // namespace tc

@@ -1,0 +1,425 @@
+// Small data-movement / pointwise kernels around the three hot kernels (GEMM, attention step, LSTM epilogue).
+#pragma once
+#include "sat_common.cuh"
+
+namespace misc {
+
+// dst[perm(r), c] = (TO) src[r, c0 + c]; perm interleaves the four LSTM gate blocks when ilH > 0:
+// source row g*ilH + j  ->  destination row 4*j + g.
+template <typename TO>
+__global__ void pack_weight_kernel(TO* __restrict__ dst, int64_t ld_dst, const float* __restrict__ src, int64_t ld_src,
+                                   int rows, int cols, int c0, int ilH) {
+    const int r = blockIdx.y;
+    const int rd = ilH > 0 ? ((r % ilH) * 4 + r / ilH) : r;
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < cols; c += gridDim.x * blockDim.x)
+        dst[(int64_t)rd * ld_dst + c] = from_f32<TO>(src[(int64_t)r * ld_src + c0 + c]);
+}
+template <typename TO>
+int pack_weight(cudaStream_t s, TO* dst, int64_t ld_dst, const float* src, int64_t ld_src, int rows, int cols, int c0, int ilH) {
+    if (rows <= 0 || cols <= 0) return SAT_OK;
+    dim3 grid(min(sat_cdiv(cols, 256), 8), rows);
+    pack_weight_kernel<TO><<<grid, 256, 0, s>>>(dst, ld_dst, src, ld_src, rows, cols, c0, ilH);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+// dst[perm(i)] = a[i] + (b ? b[i] : 0)
+__global__ void pack_bias_kernel(float* dst, const float* a, const float* b, int n, int ilH) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int d = ilH > 0 ? ((i % ilH) * 4 + i / ilH) : i;
+    dst[d] = a[i] + (b ? b[i] : 0.0f);
+}
+inline int pack_bias(cudaStream_t s, float* dst, const float* a, const float* b, int n, int ilH) {
+    pack_bias_kernel<<<sat_cdiv(n, 256), 256, 0, s>>>(dst, a, b, n, ilH);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+// inverse of pack_weight for gradients: dst_fp32[r, c0 + c] = src[perm(r), c]   (dst row pitch ld_dst)
+__global__ void unpack_grad_kernel(float* __restrict__ dst, int64_t ld_dst, const float* __restrict__ src, int64_t ld_src,
+                                   int rows, int cols, int c0, int ilH) {
+    const int r = blockIdx.y;
+    const int rs = ilH > 0 ? ((r % ilH) * 4 + r / ilH) : r;
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < cols; c += gridDim.x * blockDim.x)
+        dst[(int64_t)r * ld_dst + c0 + c] = src[(int64_t)rs * ld_src + c];
+}
+inline int unpack_grad(cudaStream_t s, float* dst, int64_t ld_dst, const float* src, int64_t ld_src, int rows, int cols, int c0, int ilH) {
+    if (rows <= 0 || cols <= 0) return SAT_OK;
+    dim3 grid(min(sat_cdiv(cols, 256), 8), rows);
+    unpack_grad_kernel<<<grid, 256, 0, s>>>(dst, ld_dst, src, ld_src, rows, cols, c0, ilH);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+// strided (B,L,D) of TI -> contiguous (B,L,D) of TO   (Q20: encoder output is a permuted view)
+template <typename TI, typename TO>
+__global__ void cast3d_kernel(TO* __restrict__ dst, const TI* __restrict__ src, int B, int L, int D,
+                              int64_t sb, int64_t sl, int64_t sd) {
+    __shared__ float tile[32][33];
+    // tile over (l, d) so both the strided read (l fastest when sd > sl) and the write (d fastest) coalesce
+    const int b = blockIdx.z;
+    const int l0 = blockIdx.y * 32, d0 = blockIdx.x * 32;
+    const bool l_fast = (sl < sd);
+    if (l_fast) {
+        for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+            const int d = d0 + i, l = l0 + threadIdx.x;
+            if (d < D && l < L) tile[i][threadIdx.x] = to_f32<TI>(src[b * sb + l * sl + d * sd]);
+        }
+        __syncthreads();
+        for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+            const int l = l0 + i, d = d0 + threadIdx.x;
+            if (l < L && d < D) dst[((int64_t)b * L + l) * D + d] = from_f32<TO>(tile[threadIdx.x][i]);
+        }
+    } else {
+        for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+            const int l = l0 + i, d = d0 + threadIdx.x;
+            if (l < L && d < D) dst[((int64_t)b * L + l) * D + d] = from_f32<TO>(to_f32<TI>(src[b * sb + l * sl + d * sd]));
+        }
+    }
+}
+template <typename TI, typename TO>
+int cast3d(cudaStream_t s, TO* dst, const TI* src, int B, int L, int D, int64_t sb, int64_t sl, int64_t sd) {
+    dim3 grid(sat_cdiv(D, 32), sat_cdiv(L, 32), B), block(32, 8);
+    cast3d_kernel<TI, TO><<<grid, block, 0, s>>>(dst, src, B, L, D, sb, sl, sd);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+// flat cast / scale
+template <typename TI, typename TO>
+__global__ void cast_kernel(TO* __restrict__ dst, const TI* __restrict__ src, int64_t n, float scale) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = from_f32<TO>(to_f32<TI>(src[i]) * scale);
+}
+template <typename TI, typename TO>
+int cast(cudaStream_t s, TO* dst, const TI* src, int64_t n, float scale = 1.0f) {
+    if (n <= 0) return SAT_OK;
+    const int blocks = (int)(sat_cdiv64(n, 256) < (int64_t)(148 * 16) ? sat_cdiv64(n, 256) : (int64_t)(148 * 16));
+    cast_kernel<TI, TO><<<blocks, 256, 0, s>>>(dst, src, n, scale);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+// abar[b,d] = mean_l a[b,l,d]   (decoder.py:139 / :104)
+template <typename T>
+__global__ void mean_l_kernel(const T* __restrict__ a, float* __restrict__ out_f, T* __restrict__ out_t, int L, int D) {
+    const int b = blockIdx.y;
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= D) return;
+    const T* p = a + (size_t)b * L * D + d;
+    float s = 0.0f;
+    for (int l = 0; l < L; ++l) s += to_f32<T>(p[(size_t)l * D]);
+    s /= (float)L;
+    if (out_f) out_f[(size_t)b * D + d] = s;
+    if (out_t) out_t[(size_t)b * D + d] = from_f32<T>(s);
+}
+template <typename T>
+int mean_l(cudaStream_t s, const T* a, float* out_f, T* out_t, int B, int L, int D) {
+    dim3 grid(sat_cdiv(D, 128), B);
+    mean_l_kernel<T><<<grid, 128, 0, s>>>(a, out_f, out_t, L, D);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+// out[r, 0:H] = (TO) table[idx[r*idx_stride], 0:H]   (embedding gather, decoder.py:87/:89/:133/:183)
+template <typename TO>
+__global__ void gather_rows_kernel(TO* __restrict__ out, int64_t ld_out, const float* __restrict__ table, int H,
+                                   const int64_t* __restrict__ idx, int64_t idx_stride, int V) {
+    const int r = blockIdx.x;
+    int64_t tok = idx[(int64_t)r * idx_stride];
+    if (tok < 0) tok = 0;
+    if (tok >= V) tok = V - 1;
+    const float* src = table + (size_t)tok * H;
+    for (int h = threadIdx.x; h < H; h += blockDim.x) out[(int64_t)r * ld_out + h] = from_f32<TO>(src[h]);
+}
+template <typename TO>
+int gather_rows(cudaStream_t s, TO* out, int64_t ld_out, const float* table, int H, const int64_t* idx, int64_t idx_stride, int rows, int V) {
+    if (rows <= 0) return SAT_OK;
+    gather_rows_kernel<TO><<<rows, 128, 0, s>>>(out, ld_out, table, H, idx, idx_stride, V);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+// 2-D gather for (B, T) token grids written TIME-MAJOR to (T, B, H): row r = t*B + b reads cap[b*cap_stride + t]
+template <typename TO>
+__global__ void gather_bt_kernel(TO* __restrict__ out, const float* __restrict__ table, int H,
+                                 const int64_t* __restrict__ cap, int64_t cap_stride, int B, int V) {
+    const int r = blockIdx.x, t = r / B, b = r - t * B;
+    int64_t tok = cap[(int64_t)b * cap_stride + t];
+    if (tok < 0) tok = 0;
+    if (tok >= V) tok = V - 1;
+    const float* src = table + (size_t)tok * H;
+    for (int h = threadIdx.x; h < H; h += blockDim.x) out[(int64_t)r * H + h] = from_f32<TO>(src[h]);
+}
+// grad scatter: table_grad[tok, :] += dE[r, :], dE time-major (row r = t*B + b)
+template <typename TI>
+__global__ void scatter_add_bt_kernel(float* __restrict__ table_grad, int H, const TI* __restrict__ dE,
+                                      const int64_t* __restrict__ cap, int64_t cap_stride, int B, int V) {
+    const int r = blockIdx.x, t = r / B, b = r - t * B;
+    const int64_t tok = cap[(int64_t)b * cap_stride + t];
+    if (tok < 0 || tok >= V) return;
+    float* dst = table_grad + (size_t)tok * H;
+    for (int h = threadIdx.x; h < H; h += blockDim.x) atomicAdd(dst + h, to_f32<TI>(dE[(int64_t)r * H + h]));
+}
+
+// set every row (b, t) of a (B, T, ld) T tensor's first D columns to src[b, :]
+template <typename T>
+__global__ void bcast_rows_kernel(T* __restrict__ dst, int64_t ld_t, int64_t ld_b, const T* __restrict__ src, int D, int Tn) {
+    const int b = blockIdx.y, t = blockIdx.x;
+    for (int d = threadIdx.x; d < D; d += blockDim.x) dst[(int64_t)b * ld_b + (int64_t)t * ld_t + d] = src[(size_t)b * D + d];
+}
+
+// LSTM cell backward pointwise (interleaved gates).  dh = dh_carry + dhd*mask.
+template <typename T>
+__global__ void lstm_bwd_kernel(const T* __restrict__ gates, int64_t ld_g, const float* __restrict__ c_prev, int64_t ld_cp,
+                                const float* __restrict__ c_new, int64_t ld_cn, const float* __restrict__ dhd, int64_t ld_dhd,
+                                const float* __restrict__ mask, int64_t ld_mask, const float* __restrict__ dh_carry,
+                                float* __restrict__ dc_carry, T* __restrict__ dG, int64_t ld_dg, int B, int H) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (j >= H) return;
+    const T* g = gates + (int64_t)b * ld_g + 4 * j;
+    const float gi = to_f32<T>(g[0]), gf = to_f32<T>(g[1]), gg = to_f32<T>(g[2]), go = to_f32<T>(g[3]);
+    float dh = dh_carry[(size_t)b * H + j];
+    if (dhd) dh += dhd[(int64_t)b * ld_dhd + j] * (mask ? mask[(int64_t)b * ld_mask + j] : 1.0f);
+    const float cn = c_new[(int64_t)b * ld_cn + j];
+    const float tc = tanhf(cn);
+    const float d_o = dh * tc * go * (1.0f - go);
+    const float dc = dh * go * (1.0f - tc * tc) + dc_carry[(size_t)b * H + j];
+    const float d_i = dc * gg * gi * (1.0f - gi);
+    const float d_f = dc * c_prev[(int64_t)b * ld_cp + j] * gf * (1.0f - gf);
+    const float d_g = dc * gi * (1.0f - gg * gg);
+    dc_carry[(size_t)b * H + j] = dc * gf;
+    T* o = dG + (int64_t)b * ld_dg + 4 * j;
+    o[0] = from_f32<T>(d_i); o[1] = from_f32<T>(d_f); o[2] = from_f32<T>(d_g); o[3] = from_f32<T>(d_o);
+}
+
+// column sums: out[n] = sum_m X[m, n]  (two-stage, deterministic)
+template <typename T>
+__global__ void colsum_partial_kernel(const T* __restrict__ X, int64_t ld, int M, int N, float* __restrict__ part, int rows_per_split) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    const int s = blockIdx.y;
+    if (n >= N) return;
+    const int m0 = s * rows_per_split, m1 = min(M, m0 + rows_per_split);
+    float acc = 0.0f;
+    for (int m = m0; m < m1; ++m) acc += to_f32<T>(X[(int64_t)m * ld + n]);
+    part[(size_t)s * N + n] = acc;
+}
+__global__ void colsum_final_kernel(const float* __restrict__ part, int S, int N, float* __restrict__ out, int ilH) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= N) return;
+    float acc = 0.0f;
+    for (int s = 0; s < S; ++s) acc += part[(size_t)s * N + n];
+    // ilH > 0: column n of the interleaved gate axis belongs to source row (n%4)*ilH + n/4
+    const int d = ilH > 0 ? ((n % 4) * ilH + n / 4) : n;
+    out[d] = acc;
+}
+template <typename T>
+int colsum(cudaStream_t s, const T* X, int64_t ld, int M, int N, float* out, float* scratch, int64_t scratch_floats, int ilH = 0) {
+    int S = min(64, max(1, M / 64));
+    while ((int64_t)S * N > scratch_floats && S > 1) S /= 2;
+    SAT_REQUIRE((int64_t)S * N <= scratch_floats, "colsum scratch too small");
+    const int rps = sat_cdiv(M, S);
+    dim3 grid(sat_cdiv(N, 128), S);
+    colsum_partial_kernel<T><<<grid, 128, 0, s>>>(X, ld, M, N, scratch, rps);
+    colsum_final_kernel<<<sat_cdiv(N, 128), 128, 0, s>>>(scratch, S, N, out, ilH);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+// d(pre-tanh) of the initial state: dpre[b, j] = dh0 * (1 - h0^2), dpre[b, H + j] = dc0 * (1 - c0^2)
+template <typename T>
+__global__ void dinit_kernel(T* __restrict__ dpre, const float* __restrict__ dh0, const float* __restrict__ dc0,
+                             const float* __restrict__ hc0, int B, int H) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * H) return;
+    const int b = i / H, j = i - b * H;
+    const float h0 = hc0[(size_t)b * 2 * H + j], c0 = hc0[(size_t)b * 2 * H + H + j];
+    dpre[(size_t)b * 2 * H + j] = from_f32<T>(dh0[i] * (1.0f - h0 * h0));
+    dpre[(size_t)b * 2 * H + H + j] = from_f32<T>(dc0[i] * (1.0f - c0 * c0));
+}
+
+// split fp32 (B, 2H) [h0 | c0] into the state buffers
+template <typename T>
+__global__ void init_state_scatter_kernel(const float* __restrict__ hc0, T* __restrict__ h_dst, int64_t ld_h,
+                                          float* __restrict__ c_dst, int64_t ld_c, int B, int H) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * H) return;
+    const int b = i / H, j = i - b * H;
+    h_dst[(int64_t)b * ld_h + j] = from_f32<T>(hc0[(size_t)b * 2 * H + j]);
+    c_dst[(int64_t)b * ld_c + j] = hc0[(size_t)b * 2 * H + H + j];
+}
+
+// argmax over V per row (first maximum), output int64 index   (decoder.py:132)
+__global__ void argmax_rows_kernel(const float* __restrict__ x, int64_t ld, int V, int64_t* __restrict__ out, int64_t out_stride) {
+    __shared__ float sv[32];
+    __shared__ int si[32];
+    const int r = blockIdx.x;
+    const float* p = x + (int64_t)r * ld;
+    float best = -INFINITY; int bi = 0x7fffffff;
+    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+        const float f = p[v];
+        if (f > best || (f == best && v < bi)) { best = f; bi = v; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+    }
+    if ((threadIdx.x & 31) == 0) { sv[threadIdx.x >> 5] = best; si[threadIdx.x >> 5] = bi; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int nw = blockDim.x >> 5;
+        best = threadIdx.x < nw ? sv[threadIdx.x] : -INFINITY;
+        bi = threadIdx.x < nw ? si[threadIdx.x] : 0x7fffffff;
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+        }
+        if (threadIdx.x == 0) out[(int64_t)r * out_stride] = (bi == 0x7fffffff) ? 0 : bi;
+    }
+}
+
+// ---- cross entropy over logits rows (train.py:150-151,161; Q10) ------------------------------------
+// row r = b*T + t of logits (B*T, V).  Rows with t == T-1 are excluded.  rowloss[r] = lse - logit[target].
+// Optionally writes dlogits = (softmax - onehot) * scale (T dtype), zero rows for t == T-1.
+template <typename TO>
+__global__ void ce_rows_kernel(const float* __restrict__ logits, int64_t ld, int V, int Tn, const int64_t* __restrict__ cap,
+                               int64_t cap_stride, float* __restrict__ rowloss, TO* __restrict__ dlog, int64_t ld_d,
+                               const float* __restrict__ scale_ptr, float scale_mul) {
+    __shared__ float red[32];
+    const int r = blockIdx.x, b = r / Tn, t = r - b * Tn;
+    const int B = gridDim.x / Tn;
+    const int64_t ro = (int64_t)t * B + b;      // dlogits are stored time-major
+    const float* p = logits + (int64_t)r * ld;
+    const bool active = (t < Tn - 1);
+    if (!active) {
+        if (rowloss && threadIdx.x == 0) rowloss[r] = 0.0f;
+        if (dlog) for (int v = threadIdx.x; v < V; v += blockDim.x) dlog[ro * ld_d + v] = from_f32<TO>(0.0f);
+        return;
+    }
+    float m = -INFINITY;
+    for (int v = threadIdx.x; v < V; v += blockDim.x) m = fmaxf(m, p[v]);
+    m = warp_max(m);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    {
+        float x = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : -INFINITY;
+        if (threadIdx.x < 32) { x = warp_max(x); if (threadIdx.x == 0) red[0] = x; }
+    }
+    __syncthreads();
+    m = red[0];
+    __syncthreads();
+    float s = 0.0f;
+    for (int v = threadIdx.x; v < V; v += blockDim.x) s += expf(p[v] - m);
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    {
+        float x = (threadIdx.x < (blockDim.x >> 5)) ? red[threadIdx.x] : 0.0f;
+        if (threadIdx.x < 32) { x = warp_sum(x); if (threadIdx.x == 0) red[0] = x; }
+    }
+    __syncthreads();
+    s = red[0];
+    const int64_t tgt = cap[(int64_t)b * cap_stride + t + 1];
+    const float lse = m + logf(s);
+    if (rowloss && threadIdx.x == 0) rowloss[r] = lse - p[tgt];
+    if (dlog) {
+        const float sc = (scale_ptr ? scale_ptr[0] : 1.0f) * scale_mul;
+        const float inv = 1.0f / s;
+        for (int v = threadIdx.x; v < V; v += blockDim.x) {
+            float g = expf(p[v] - m) * inv;
+            if (v == tgt) g -= 1.0f;
+            dlog[ro * ld_d + v] = from_f32<TO>(g * sc);
+        }
+    }
+}
+
+// loss[0] = ce mean, loss[1] = alpha_c * mean_{b,l} (1 - sum_t alpha)^2, loss[2] = total   (single block)
+__global__ void loss_finalize_kernel(const float* __restrict__ rowloss, int rows, int n_active, const float* __restrict__ alphas,
+                                     int B, int Tn, int L, float alpha_c, float* __restrict__ loss) {
+    __shared__ float red[2][32];
+    float ce = 0.0f, reg = 0.0f;
+    for (int i = threadIdx.x; i < rows; i += blockDim.x) ce += rowloss[i];
+    if (alphas) {
+        for (int i = threadIdx.x; i < B * L; i += blockDim.x) {
+            const int b = i / L, l = i - b * L;
+            float s = 0.0f;
+            for (int t = 0; t < Tn; ++t) s += alphas[((size_t)b * Tn + t) * L + l];
+            reg += (1.0f - s) * (1.0f - s);
+        }
+    }
+    ce = warp_sum(ce); reg = warp_sum(reg);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = ce; red[1][threadIdx.x >> 5] = reg; }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        const int nw = blockDim.x >> 5;
+        ce = threadIdx.x < nw ? red[0][threadIdx.x] : 0.0f;
+        reg = threadIdx.x < nw ? red[1][threadIdx.x] : 0.0f;
+        ce = warp_sum(ce); reg = warp_sum(reg);
+        if (threadIdx.x == 0) {
+            loss[0] = n_active > 0 ? ce / (float)n_active : 0.0f;
+            loss[1] = alphas ? alpha_c * reg / (float)(B * L) : 0.0f;
+            loss[2] = loss[0] + loss[1];
+        }
+    }
+}
+
+// analytic grad of the doubly-stochastic regulariser: galpha[b,t,l] = 2 alpha_c (sum_t alpha - 1) / (B L) * scale  (Q11)
+__global__ void alpha_reg_grad_kernel(const float* __restrict__ alphas, float* __restrict__ galpha, int B, int Tn, int L,
+                                      float alpha_c, const float* __restrict__ scale_ptr) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * L) return;
+    const int b = i / L, l = i - b * L;
+    float s = 0.0f;
+    for (int t = 0; t < Tn; ++t) s += alphas[((size_t)b * Tn + t) * L + l];
+    const float g = 2.0f * alpha_c * (s - 1.0f) / (float)(B * L) * (scale_ptr ? scale_ptr[0] : 1.0f);
+    for (int t = 0; t < Tn; ++t) galpha[((size_t)b * Tn + t) * L + l] = g;
+}
+
+// out = relu'(ref) * x  (T)  ; used by the advanced-deep-output backward
+template <typename T>
+__global__ void relu_bwd_kernel(T* __restrict__ out, const float* __restrict__ x, const T* __restrict__ ref, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = from_f32<T>(to_f32<T>(ref[i]) > 0.0f ? x[i] : 0.0f);
+}
+// dlog[t*B+b, v] (T, pitch ld_d) = dpreds[b,t,v] (* relu'(preds[b,t,v]) when ref != null: final ReLU of ado, Q8)
+template <typename T>
+__global__ void dpreds_to_dlog_kernel(T* __restrict__ out, int64_t ld_d, const float* __restrict__ x, const float* __restrict__ ref,
+                                      int B, int Tn, int V) {
+    const int r = blockIdx.x, b = r / Tn, t = r - b * Tn;
+    const float* xr = x + (int64_t)r * V;
+    const float* rr = ref ? ref + (int64_t)r * V : nullptr;
+    T* o = out + ((int64_t)t * B + b) * ld_d;
+    for (int v = threadIdx.x; v < V; v += blockDim.x) o[v] = from_f32<T>((rr && !(rr[v] > 0.0f)) ? 0.0f : xr[v]);
+}
+__global__ void fill_tokens_kernel(int64_t* __restrict__ p, int n, int64_t val) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = val;
+}
+// grad scatter with a flat token list: table_grad[tok[r], :] += dE[r, :]
+template <typename TI>
+__global__ void scatter_add_rows_kernel(float* __restrict__ table_grad, int H, const TI* __restrict__ dE,
+                                        const int64_t* __restrict__ tok, int V) {
+    const int r = blockIdx.x;
+    const int64_t tk = tok[r];
+    if (tk < 0 || tk >= V) return;
+    float* dst = table_grad + (size_t)tk * H;
+    for (int h = threadIdx.x; h < H; h += blockDim.x) atomicAdd(dst + h, to_f32<TI>(dE[(int64_t)r * H + h]));
+}
+__global__ void fill_kernel(float* __restrict__ p, int64_t n, float val) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = val;
+}
+// y (T) = a (T) + b (T) + c (T)
+template <typename T>
+__global__ void add3_kernel(T* __restrict__ y, const T* __restrict__ a, const T* __restrict__ b, const T* __restrict__ c, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] = from_f32<T>(to_f32<T>(a[i]) + to_f32<T>(b[i]) + to_f32<T>(c[i]));
+}
+// y (T) += x (fp32)   elementwise into a T buffer
+template <typename T>
+__global__ void add_into_kernel(T* __restrict__ y, const float* __restrict__ x, int64_t n) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        y[i] = from_f32<T>(to_f32<T>(y[i]) + x[i]);
+}
+inline int grid_for(int64_t n) { return (int)(sat_cdiv64(n, 256) < (int64_t)(148 * 16) ? sat_cdiv64(n, 256) : (int64_t)(148 * 16)); }
+
+}  // namespace misc

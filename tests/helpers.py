@@ -51,3 +51,24 @@ def check_grad_summary(got, want, name, rtol=2e-4, atol=2e-6):
     # abs-sum and sum: scale tolerance by abs-sum
     np.testing.assert_allclose(got[1], want[1], rtol=rtol, atol=atol * want[2], err_msg=name + " abs-sum")
     assert abs(got[0] - want[0]) <= rtol * abs(want[1]) + atol * want[2], name + " sum"
+
+
+def stub_bert():
+    """Offline stand-in for BertModel/BertTokenizer.from_pretrained, same as make_golden.py."""
+    import torch.nn as nn
+    import transformers
+
+    class _Tok:
+        cls_token_id, sep_token_id, pad_token_id = 101, 102, 0
+
+    class _Cfg:
+        vocab_size, hidden_size = 30522, 768
+
+    class _Bert:
+        config = _Cfg()
+
+        def get_input_embeddings(self):
+            return nn.Embedding(30522, 768, padding_idx=0)
+
+    transformers.BertModel.from_pretrained = classmethod(lambda c, n: _Bert())
+    transformers.BertTokenizer.from_pretrained = classmethod(lambda c, n: _Tok())
