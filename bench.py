@@ -1,0 +1,332 @@
+#!/usr/bin/env python
+"""Benchmark of the decoder hot path on BASELINE.json config c2 (see DESIGN.md "Measurement").
+
+  python bench.py --gpus N --steps K --warmup W                 our arm (one process per GPU under torchrun for N>1)
+  python bench.py --impl reference --gpus N --steps K --warmup W  the reference algorithm on the host cores
+
+A "step" is one teacher-forced train step of the decoder: forward + train.py loss + backward (+ NCCL gradient
+all-reduce for N>1) + Adam, batch 256 per GPU (weak scaling), synthetic ResNet152-shaped features
+(L=196, D=2048), H=512, V=2531, T=20, bf16 compute.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+CFG = dict(B=256, L=196, D=2048, H=512, V=2531, T=20)
+WORKLOAD = ("c2: teacher-forced bf16 train step of the soft-attention LSTM decoder, ResNet152-shaped features "
+            "L=196 x D=2048, H=512, V=2531, T=20, batch 256 per GPU")
+METRIC, UNIT = "train_captions_per_s", "captions/s"
+
+
+def read_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 6:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_host_batches(n, B, seed0=42):
+    """n distinct synthetic batches in pinned host memory (bf16 features + int64 captions)."""
+    from sat_b200 import synth
+    out = []
+    for i in range(n):
+        g = torch.Generator().manual_seed(seed0 + i)
+        a = torch.relu(torch.randn(B, CFG["L"], CFG["D"], generator=g)).to(torch.bfloat16).pin_memory()
+        _, cap = synth.make_inputs(B, 1, 8, CFG["T"], CFG["V"], seed=seed0 + i)
+        out.append((a, cap.pin_memory()))
+    return out
+
+
+def oracle_cpu_train_step_rate(sample_B, steps, warmup, threads):
+    """The reference algorithm (oracle port, incl. its per-step W(a) recomputation, Q3) on the host cores:
+    forward + train.py loss + backward + Adam, fp32."""
+    from oracle import sat_oracle as O
+    from sat_b200 import synth
+    torch.set_num_threads(threads)
+    P = synth.make_params(CFG["V"], CFG["D"], CFG["H"], seed=42, emb_scale=1.0)
+    P = {k: v.clone().requires_grad_(True) for k, v in P.items()}
+    a, cap = synth.make_inputs(sample_B, CFG["L"], CFG["D"], CFG["T"], CFG["V"], seed=42)
+    masks = synth.make_dropout_masks(sample_B, CFG["T"], CFG["H"])
+    opt = torch.optim.Adam(list(P.values()), lr=1e-4)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        opt.zero_grad(set_to_none=True)
+        preds, alphas = O.decoder_forward(P, a, cap, tf=True, ado=False, attention=True, dropout_masks=masks)
+        loss = O.train_loss(preds, alphas, cap, 1.0)
+        loss.backward()
+        opt.step()
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    ms = 1e3 * sum(times) / len(times)
+    return sample_B / (ms / 1e3), ms
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample_B = 16
+    warm = max(1, min(args.warmup, 1))
+    val, ms = oracle_cpu_train_step_rate(sample_B, args.steps, warm, threads)
+    sample = (f"oracle port of attention.py/decoder.py/train.py loss on CPU (torch {torch.__version__}, fp32, {threads} threads); "
+              f"each step = one full train step on a {sample_B}-caption sample of the c2 batch (same L,D,H,V,T)")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": {"workload": WORKLOAD, "sample_batch": sample_B},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def count_my_launches(fn):
+    """Kernel launches of ONE step, counted with the CUDA profiler (kineto); all kernels in a step are ours or NCCL's."""
+    try:
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            fn()
+            torch.cuda.synchronize()
+        n = 0
+        for ev in prof.events():
+            if ev.device_type == torch.autograd.DeviceType.CUDA and "memcpy" not in ev.name.lower() and "memset" not in ev.name.lower():
+                n += 1
+        return n
+    except Exception:
+        return None
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch.distributed as dist
+    from sat_b200 import _lib, synth
+    from sat_b200.decoder import Decoder
+    from sat_b200.trainer import FusedTrainStep
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    L = _lib.lib()
+    B, T = CFG["B"], CFG["T"]
+    dec = Decoder(CFG["V"], CFG["D"], tf=True, ado=False, bert=False, attention=True, compute_dtype=torch.bfloat16)
+    dec.load_state_dict(synth.make_params(CFG["V"], CFG["D"], CFG["H"], seed=42))
+    dec = dec.to(dev).train()
+    trainer = FusedTrainStep(dec, lr=1e-4, alpha_c=1.0)
+    host = make_host_batches(2, B, seed0=42 + 10 * rank)
+    dev_batches = [(a.to(dev, non_blocking=True), c.to(dev, non_blocking=True)) for a, c in host]
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return t.item()
+        return ms
+
+    # ---- device-resident throughput ("value") -----------------------------------------------------
+    for i in range(args.warmup):
+        trainer.step(*dev_batches[i % 2])
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        loss = trainer.step(*dev_batches[i % 2])
+    e1.record()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    value = world * B / (ms_step / 1e3)
+    loss_val = loss[2].item()
+
+    # ---- end to end through the public API with host buffers ("e2e") ------------------------------
+    copy_stream = torch.cuda.Stream(dev)
+    bufs = [(torch.empty_like(dev_batches[0][0]), torch.empty_like(dev_batches[0][1])) for _ in range(2)]
+    ready = [torch.cuda.Event(), torch.cuda.Event()]
+    freed = [torch.cuda.Event(), torch.cuda.Event()]
+    loss_host = torch.zeros(3).pin_memory()
+
+    def prefetch(i):
+        s = i % 2
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(freed[s])
+            bufs[s][0].copy_(host[s][0], non_blocking=True)
+            bufs[s][1].copy_(host[s][1], non_blocking=True)
+            ready[s].record(copy_stream)
+
+    def e2e_loop(n):
+        cur = torch.cuda.current_stream(dev)
+        for s in range(2):
+            freed[s].record(cur)
+        prefetch(0)
+        for i in range(n):
+            s = i % 2
+            if i + 1 < n:
+                prefetch(i + 1)
+            cur.wait_event(ready[s])
+            l = trainer.step(bufs[s][0], bufs[s][1])
+            freed[s].record(cur)
+            loss_host.copy_(l, non_blocking=True)
+            cur.synchronize()                                  # the step's loss is on the host (train.py:179)
+        return float(loss_host[2])
+
+    e2e_loop(max(2, args.warmup))
+    barrier()
+    e0.record()
+    e2e_loop(args.steps)
+    e1.record()
+    barrier()
+    e2e_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    e2e_val = world * B / (e2e_ms / 1e3)
+    h2d = host[0][0].numel() * host[0][0].element_size() + host[0][1].numel() * 8
+    d2h = 12
+
+    # ---- kernel-level roofline (CUDA events around every attention-step launch, on its own stream) -------
+    ms = (ctypes.c_float * 3)()
+    cnt = (ctypes.c_int * 3)()
+    L.sat_profile(1)
+    nprof = 2
+    for i in range(nprof):
+        trainer.step(*dev_batches[i % 2])
+    torch.cuda.synchronize()
+    _lib.check(L.sat_profile_read(ms, cnt))
+    L.sat_profile(0)
+    s = 2  # bf16
+    Lc, D, H = CFG["L"], CFG["D"], CFG["H"]
+    bytes_fwd = B * Lc * (H + D) * s
+    bytes_bwd = B * (Lc * (H + D) * s + 2 * Lc * H * 4)
+    peak, peak_src = read_peaks()
+    kern = {}
+    for name, idx, nbytes in (("attn_step_fwd", 0, bytes_fwd), ("attn_step_bwd", 1, bytes_bwd)):
+        if cnt[idx] > 0:
+            avg_ms = ms[idx] / cnt[idx]
+            kern[name] = {"avg_ms": avg_ms, "launches_per_step": cnt[idx] // nprof, "ms_per_step": ms[idx] / nprof,
+                          "algorithmic_bytes": nbytes, "achieved_gbs": nbytes / avg_ms / 1e6}
+    kern["gemm_all"] = {"ms_per_step": ms[2] / nprof, "launches_per_step": cnt[2] // nprof}
+    dom = max(("attn_step_fwd", "attn_step_bwd"), key=lambda k: kern.get(k, {}).get("ms_per_step", 0.0))
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(dom)
+    except Exception:
+        pass
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                "frac": kern[dom]["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
+                "share_of_step": kern[dom]["ms_per_step"] / ms_step, "kernels": kern}
+
+    launches = count_my_launches(lambda: trainer.step(*dev_batches[0]))
+    if rank != 0:
+        return
+    cpu = None
+    if world == 1:
+        threads = os.cpu_count() or 1
+        sb = 8
+        v, cms = oracle_cpu_train_step_rate(sb, 2, 1, threads)
+        cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"oracle port on CPU, fp32, {threads} threads, 2 timed train steps on a {sb}-caption sample of the c2 batch "
+                         f"({cms:.0f} ms/step)"}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "global_batch": world * B, "parallelism": f"dp{world}",
+                       "l2": "inputs larger than L2 (a+Wa = 257 MB per step > 126 MB), two alternating batches",
+                       "optimizer": "fused Adam inside the timed step", "dropout": "train mode (p=0.5)", "loss": loss_val},
+            "clocks": clocks,
+            "e2e": {"value": e2e_val, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": None if launches is None else launches * args.steps,
+            "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    args.warmup = max(args.warmup, 3)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    try:
+        run_ours(args, rank, world, local_rank)
+    finally:
+        if world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -25,6 +25,11 @@ int sat_version(void);
 /* debug knob: 1 = run bf16 GEMMs on the SIMT kernel (bring-up cross-check of the tcgen05 kernel) */
 int sat_set_force_simt(int on);
 
+/* Bench instrumentation: CUDA-event pairs around every attention-step (fwd = category 0, bwd = 1) and GEMM (2) launch,
+ * recorded on the launching stream.  sat_profile_read fills ms[3] / counts[3] and resets. */
+int sat_profile(int on);
+int sat_profile_read(float* ms, int* counts);
+
 /* Generic GEMM  C[M,N] = act(A[M,K] * B[N,K]^T + bias[N])  (nn.Linear: attention.py:15-16, decoder.py:99,125,139-145).
  * a_kmajor: A[m*lda+k] (1) or A[k*lda+m] (0); same for B.  Cf (fp32) and/or Ct (dtype) outputs, either may be NULL. */
 int sat_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, int a_kmajor, const void* B, int64_t ldb,

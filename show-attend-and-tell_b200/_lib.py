@@ -74,7 +74,7 @@ _LIB = None
 
 EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_bwd",
            "sat_decoder_workspace_bytes", "sat_decoder_forward", "sat_decoder_backward", "sat_beam_workspace_bytes",
-           "sat_beam_search", "sat_adam_step"]
+           "sat_beam_search", "sat_adam_step", "sat_profile", "sat_profile_read"]
 
 
 def lib():

@@ -587,6 +587,7 @@ int launch_fwd_t(FwdParams p, cudaStream_t stream) {
         configured = 227 * 1024;
     }
     void* args[] = {&p, &sl};
+    SatProfScope prof(SAT_PROF_ATTN_FWD, stream);
     return launch_cluster(kern, dim3(p.C, p.NI), p.C, sl.total, stream, args);
 }
 
@@ -614,6 +615,7 @@ int launch_bwd(BwdParams p, cudaStream_t stream) {
         configured = 227 * 1024;
     }
     void* args[] = {&p, &sl};
+    SatProfScope prof(SAT_PROF_ATTN_BWD, stream);
     return launch_cluster(kern, dim3(p.C, p.B), p.C, sl.total, stream, args);
 }
 }  // namespace attn

@@ -13,6 +13,30 @@ void sat_set_error(const char* fmt, ...) {
     va_end(ap);
 }
 
+// ---- event profiling -------------------------------------------------------------------------------
+#include <vector>
+static int g_prof_on = 0;
+static std::vector<cudaEvent_t> g_prof_ev;      // pairs (start, stop)
+static std::vector<int> g_prof_cat;
+static size_t g_prof_used = 0;
+
+SatProfScope::SatProfScope(int c, cudaStream_t s) : cat(c), st(s), slot(-1) {
+    if (!g_prof_on) return;
+    if (g_prof_used + 2 > g_prof_ev.size()) {
+        cudaEvent_t a, b;
+        if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return;
+        g_prof_ev.push_back(a); g_prof_ev.push_back(b);
+    }
+    slot = (int)g_prof_used;
+    g_prof_used += 2;
+    g_prof_cat.resize(g_prof_used / 2);
+    g_prof_cat[slot / 2] = cat;
+    cudaEventRecord(g_prof_ev[slot], st);
+}
+SatProfScope::~SatProfScope() {
+    if (slot >= 0) cudaEventRecord(g_prof_ev[slot + 1], st);
+}
+
 static int require_sm100() {
     static int ok = -1;
     if (ok < 0) {
@@ -34,6 +58,22 @@ extern "C" {
 const char* sat_last_error(void) { return g_err; }
 int sat_version(void) { return 100; }
 int sat_set_force_simt(int on) { g_force_simt = on ? 1 : 0; return SAT_OK; }
+
+/* profiling: sat_profile(1) starts recording CUDA-event pairs around attention-step and GEMM launches on their own
+ * stream; sat_profile_read() synchronises and returns per-category total ms and launch counts, then resets. */
+int sat_profile(int on) { g_prof_on = on ? 1 : 0; g_prof_used = 0; return SAT_OK; }
+int sat_profile_read(float* ms, int* counts) {
+    for (int c = 0; c < SAT_PROF_NCAT; ++c) { ms[c] = 0.0f; counts[c] = 0; }
+    for (size_t i = 0; i + 1 < g_prof_used; i += 2) {
+        SAT_CHECK_CUDA(cudaEventSynchronize(g_prof_ev[i + 1]));
+        float t = 0.0f;
+        SAT_CHECK_CUDA(cudaEventElapsedTime(&t, g_prof_ev[i], g_prof_ev[i + 1]));
+        const int c = g_prof_cat[i / 2];
+        ms[c] += t; counts[c] += 1;
+    }
+    g_prof_used = 0;
+    return SAT_OK;
+}
 
 int sat_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, int a_kmajor, const void* B, int64_t ldb,
              int b_kmajor, const float* bias, int act, float* Cf, int64_t ldcf, void* Ct, int64_t ldct, int bn_override,

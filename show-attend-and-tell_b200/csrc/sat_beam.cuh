@@ -1,12 +1,396 @@
-// Batched beam search (Decoder.caption, decoder.py:160-269).  Stub until the training path is verified.
+// Batched beam search: Decoder.caption (decoder.py:160-269) for NI images at once, each with its own
+// shrinking beam (Q16), raw-logit cumulative scores (Q13), step-1 row-0 rule (Q14), the reference's stop
+// tokens (Q15), 51-iteration cap (Q17) and the "no completed sentence" fallback (Q18).
+// Rows r = img*beam + slot share the image's staged features in the attention kernel (NB = beam).
+// All bookkeeping (top-k over beam x V, completion, parent gather, back-pointers) stays on the device.
 #pragma once
 #include "sat_decoder.cuh"
 
-template <typename T> struct BeamWs { int64_t total; };
+namespace beam {
+
+// K5: per image, the `n` best of (live rows x V) cumulative scores, sorted (score desc, flat index asc),
+// followed by the reference's bookkeeping (decoder.py:206-250).
+struct StepParams {
+    const float* logits;     // (R, V)
+    float* top_preds;        // (R)  cumulative score per live slot (in/out)
+    int64_t* prev_word;      // (R)  word fed to the next step (out)
+    int* live;               // (NI) current beam size (in/out)
+    int* done;               // (NI)
+    int* n_active;           // (1) images still running
+    int* parent;             // (R)  for the state gather: slot j of the next step continues row parent[j] (out)
+    int* cand_word;          // (S, NI, beam)
+    int* cand_parent;        // (S, NI, beam)
+    int* slot_cand;          // (S, NI, beam)
+    float* comp_score;       // (NI, beam)
+    int* comp_step;          // (NI, beam)
+    int* comp_cand;          // (NI, beam)
+    int* ncomp;              // (NI)
+    int* last_step;          // (NI) last executed step
+    int* last_n;             // (NI) rows alive at the start of the last executed step
+    int NI, beam, V, step, max_steps, stop_a, stop_b;
+};
+
+constexpr int TOPK_THREADS = 512;
+constexpr int MAXBEAM = 16;
+
+__global__ void __launch_bounds__(TOPK_THREADS)
+topk_step_kernel(StepParams p) {
+    __shared__ float s_val[TOPK_THREADS / 32];
+    __shared__ int s_idx[TOPK_THREADS / 32];
+    __shared__ float pick_val[MAXBEAM];
+    __shared__ int pick_idx[MAXBEAM];
+    __shared__ float s_tp[MAXBEAM];
+    const int img = blockIdx.x;
+    if (p.done[img]) return;
+    const int n = p.live[img];
+    const int rows = (p.step == 1) ? 1 : n;                    // decoder.py:206-209 (Q14)
+    const int total = rows * p.V;
+    const float* lg = p.logits + (size_t)img * p.beam * p.V;
+    if (threadIdx.x < MAXBEAM) s_tp[threadIdx.x] = (threadIdx.x < n) ? p.top_preds[img * p.beam + threadIdx.x] : 0.0f;
+    __syncthreads();
+    float last_v = INFINITY;
+    int last_i = -1;
+    for (int k = 0; k < n; ++k) {
+        float bv = -INFINITY;
+        int bi = 0x7fffffff;
+        for (int i = threadIdx.x; i < total; i += TOPK_THREADS) {
+            const int r = i / p.V;
+            const float sc = s_tp[r] + lg[i];                  // decoder.py:204
+            const bool after = (sc < last_v) || (sc == last_v && i > last_i);
+            if (after && (sc > bv || (sc == bv && i < bi))) { bv = sc; bi = i; }
+        }
+        for (int o = 16; o > 0; o >>= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+        }
+        if ((threadIdx.x & 31) == 0) { s_val[threadIdx.x >> 5] = bv; s_idx[threadIdx.x >> 5] = bi; }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            bv = threadIdx.x < TOPK_THREADS / 32 ? s_val[threadIdx.x] : -INFINITY;
+            bi = threadIdx.x < TOPK_THREADS / 32 ? s_idx[threadIdx.x] : 0x7fffffff;
+            for (int o = 16; o > 0; o >>= 1) {
+                const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+            }
+            if (threadIdx.x == 0) { pick_val[k] = bv; pick_idx[k] = bi; }
+        }
+        __syncthreads();
+        last_v = pick_val[k];
+        last_i = pick_idx[k];
+    }
+    if (threadIdx.x == 0) {
+        const size_t hb = ((size_t)p.step * p.NI + img) * p.beam;
+        int nl = 0;
+        int nc = p.ncomp[img];
+        for (int k = 0; k < n; ++k) {
+            const int flat = pick_idx[k];
+            const int prev = flat / p.V, word = flat - prev * p.V;       // decoder.py:210-211
+            p.cand_word[hb + k] = word;
+            p.cand_parent[hb + k] = prev;
+            const bool complete = (word == p.stop_a) || (word == p.stop_b);   // decoder.py:224-229 (Q15)
+            if (complete) {
+                p.comp_score[img * p.beam + nc] = pick_val[k];
+                p.comp_step[img * p.beam + nc] = p.step;
+                p.comp_cand[img * p.beam + nc] = k;
+                ++nc;
+            } else {
+                p.slot_cand[hb + nl] = k;
+                p.top_preds[img * p.beam + nl] = pick_val[k];
+                p.prev_word[img * p.beam + nl] = word;
+                p.parent[img * p.beam + nl] = prev;
+                ++nl;
+            }
+        }
+        p.ncomp[img] = nc;
+        p.last_step[img] = p.step;
+        p.last_n[img] = n;
+        p.live[img] = nl;                                                 // decoder.py:238
+        if (nl == 0 || p.step > p.max_steps) {                            // decoder.py:240-241, 252-253 (Q17)
+            p.done[img] = 1;
+            atomicSub(p.n_active, 1);
+        }
+    }
+}
+
+// h = h[prev_word_idxs[incomplete]], c = c[...]  (decoder.py:246-247) into the next step's operand rows
+template <typename T>
+__global__ void gather_state_kernel(T* __restrict__ X, int64_t ldx, int hoff, const T* __restrict__ Hn,
+                                    float* __restrict__ Cc, const float* __restrict__ Cn, const int* __restrict__ parent,
+                                    const int* __restrict__ live, const int* __restrict__ done, int beam, int H) {
+    const int r = blockIdx.x, img = r / beam, slot = r - img * beam;
+    if (done[img] || slot >= live[img]) return;
+    const int src = img * beam + parent[r];
+    for (int j = threadIdx.x; j < H; j += blockDim.x) {
+        X[(int64_t)r * ldx + hoff + j] = Hn[(size_t)src * H + j];
+        Cc[(size_t)r * H + j] = Cn[(size_t)src * H + j];
+    }
+}
+
+// every beam row of an image starts from the image's initial state
+template <typename T>
+__global__ void init_rows_kernel(T* __restrict__ X, int64_t ldx, int hoff, int zoff, float* __restrict__ Cc,
+                                 const float* __restrict__ hc0, const T* __restrict__ abar, int write_z, int beam, int H, int D) {
+    const int r = blockIdx.x, img = r / beam;
+    for (int j = threadIdx.x; j < H; j += blockDim.x) {
+        X[(int64_t)r * ldx + hoff + j] = from_f32<T>(hc0[(size_t)img * 2 * H + j]);
+        Cc[(size_t)r * H + j] = hc0[(size_t)img * 2 * H + H + j];
+    }
+    if (write_z)
+        for (int d = threadIdx.x; d < D; d += blockDim.x) X[(int64_t)r * ldx + zoff + d] = abar[(size_t)img * D + d];
+}
+
+struct FinalParams {
+    const int* cand_word; const int* cand_parent; const int* slot_cand;
+    const float* comp_score; const int* comp_step; const int* comp_cand; const int* ncomp;
+    const int* last_step; const int* last_n;
+    const float* alpha_hist;   // (S, R, L)
+    int32_t* out_len; int32_t* out_status; int64_t* out_tokens; float* out_alphas; float* out_last_alpha; int32_t* out_live;
+    int NI, beam, L, maxlen, start_token, attention;
+};
+
+__global__ void finalize_kernel(FinalParams p) {
+    __shared__ int s_k[64], s_par[64];
+    __shared__ int s_len;
+    const int img = blockIdx.x;
+    const int R = p.NI * p.beam;
+    const int nc = p.ncomp[img];
+    if (nc == 0) {                                                        // decoder.py:256-258 (Q18)
+        const int ls = p.last_step[img], n = p.last_n[img];
+        if (threadIdx.x == 0) { p.out_status[img] = 1; p.out_len[img] = 1; p.out_tokens[(size_t)img * p.maxlen] = 0; p.out_live[img] = n; }
+        for (int i = threadIdx.x; i < n * p.L; i += blockDim.x) {
+            const int s = i / p.L, l = i - s * p.L;
+            p.out_last_alpha[((size_t)img * p.beam + s) * p.L + l] =
+                p.attention ? p.alpha_hist[((size_t)ls * R + img * p.beam + s) * p.L + l] : 1.0f / (float)p.L;
+        }
+        return;
+    }
+    if (threadIdx.x == 0) {
+        int best = 0;                                                     // first maximum (decoder.py:265)
+        for (int i = 1; i < nc; ++i) if (p.comp_score[img * p.beam + i] > p.comp_score[img * p.beam + best]) best = i;
+        const int s_end = p.comp_step[img * p.beam + best];
+        int k = p.comp_cand[img * p.beam + best];
+        for (int u = s_end; u >= 1; --u) {
+            const size_t hb = ((size_t)u * p.NI + img) * p.beam;
+            s_k[u] = k;
+            const int par = p.cand_parent[hb + k];
+            s_par[u] = par;
+            p.out_tokens[(size_t)img * p.maxlen + u] = p.cand_word[hb + k];
+            if (u > 1) k = p.slot_cand[((size_t)(u - 1) * p.NI + img) * p.beam + par];
+        }
+        p.out_tokens[(size_t)img * p.maxlen] = p.start_token;
+        p.out_len[img] = s_end + 1;
+        p.out_status[img] = 0;
+        p.out_live[img] = 0;
+        s_len = s_end;
+    }
+    __syncthreads();
+    const int s_end = s_len;
+    for (int l = threadIdx.x; l < p.L; l += blockDim.x) p.out_alphas[((size_t)img * p.maxlen) * p.L + l] = 1.0f;   // decoder.py:173
+    for (int i = threadIdx.x; i < s_end * p.L; i += blockDim.x) {
+        const int u = 1 + i / p.L, l = i % p.L;
+        p.out_alphas[((size_t)img * p.maxlen + u) * p.L + l] =
+            p.attention ? p.alpha_hist[((size_t)u * R + img * p.beam + s_par[u]) * p.L + l] : 1.0f / (float)p.L;
+    }
+}
+}  // namespace beam
+
+// comb[r, :] = p1[r, :] + p2[r, :] + emb[r, :] with emb rows strided inside X (decoder.py:155)
+template <typename T>
+__global__ void beam_add3_kernel(T* __restrict__ comb, const T* __restrict__ p1, const T* __restrict__ p2,
+                                 const T* __restrict__ X, int64_t ldx, int H) {
+    const int r = blockIdx.x;
+    for (int j = threadIdx.x; j < H; j += blockDim.x)
+        comb[(size_t)r * H + j] = from_f32<T>(to_f32<T>(p1[(size_t)r * H + j]) + to_f32<T>(p2[(size_t)r * H + j]) +
+                                              to_f32<T>(X[(int64_t)r * ldx + j]));
+}
+
+template <typename T>
+struct BeamWs {
+    T *w_att, *w_uf, *w_gall, *w_init, *w_out, *w_fh, *w_fz;
+    float *b_uf, *b_g, *b_init;
+    T *a_c, *wa, *abar;
+    float* abar_f;
+    float* hc0;
+    T* X;          // (R, H + D + H): [emb | z | h]
+    T* Hn;         // (R, H)
+    float *Cc, *Cn;
+    float* UF;     // (R, H + D)
+    T* Ctx;        // (R, D)
+    T *P1, *P2, *Comb;
+    float* logits; // (R, V)
+    float* alpha_hist;   // (S, R, L)
+    float* top_preds;
+    int64_t* prev_word;
+    int *live, *done, *n_active, *parent, *cand_word, *cand_parent, *slot_cand, *comp_step, *comp_cand, *ncomp, *last_step, *last_n;
+    float* comp_score;
+    int64_t total;
+};
+
 static inline int beam_check_args(const sat_beam_args* a) {
     SAT_REQUIRE(a != nullptr, "null args");
-    SAT_REQUIRE(a->struct_bytes == (int32_t)sizeof(sat_beam_args), "sat_beam_args size mismatch");
+    SAT_REQUIRE(a->struct_bytes == (int32_t)sizeof(sat_beam_args), "sat_beam_args size mismatch: got %d, library expects %zu",
+                a->struct_bytes, sizeof(sat_beam_args));
+    SAT_REQUIRE(a->dtype == SAT_DTYPE_F32 || a->dtype == SAT_DTYPE_BF16, "bad dtype %d", a->dtype);
+    SAT_REQUIRE(a->NI > 0 && a->L > 0 && a->D > 0 && a->H > 0 && a->V > 0, "bad dims");
+    SAT_REQUIRE(a->beam >= 1 && a->beam <= beam::MAXBEAM, "beam must be in [1, %d]", beam::MAXBEAM);
+    SAT_REQUIRE(a->beam <= a->V, "beam larger than the vocabulary");
+    SAT_REQUIRE(a->max_steps >= 1 && a->max_steps + 1 < 64, "max_steps must be in [1, 62]");
+    SAT_REQUIRE(a->D % 8 == 0 && a->H % 8 == 0, "D and H must be multiples of 8");
     return SAT_OK;
 }
-template <typename T> int64_t beam_carve(const sat_beam_args&, BeamWs<T>& w, uint8_t*) { w.total = 0; return 0; }
-template <typename T> int beam_search_t(const sat_beam_args&) { sat_set_error("beam search not built yet"); return SAT_ERR_UNSUPPORTED; }
+
+template <typename T>
+int64_t beam_carve(const sat_beam_args& a, BeamWs<T>& w, uint8_t* base) {
+    int64_t off = 0;
+    auto take = [&](int64_t bytes) -> void* {
+        void* p = base ? base + off : nullptr;
+        off += (bytes + 255) & ~(int64_t)255;
+        return p;
+    };
+    const int64_t NI = a.NI, L = a.L, D = a.D, H = a.H, V = a.V, R = NI * a.beam, S = a.max_steps + 2;
+#define TK(field, count, type) w.field = reinterpret_cast<type*>(take((int64_t)(count) * (int64_t)sizeof(type)))
+    TK(w_att, H * D, T); TK(w_uf, (H + D) * H, T); TK(w_gall, 4 * H * (2 * H + D), T); TK(w_init, 2 * H * D, T); TK(w_out, V * H, T);
+    TK(w_fh, a.ado ? H * H : 0, T); TK(w_fz, a.ado ? H * D : 0, T);
+    TK(b_uf, H + D, float); TK(b_g, 4 * H, float); TK(b_init, 2 * H, float);
+    const bool a_alias = (a.a_dtype == a.dtype) && a.a_stride_d == 1 && a.a_stride_l == D && a.a_stride_b == L * D && al16(a.img_features);
+    TK(a_c, a_alias ? 0 : NI * L * D, T);
+    if (a_alias) w.a_c = reinterpret_cast<T*>(const_cast<void*>(a.img_features));
+    TK(wa, a.attention ? NI * L * H : 0, T); TK(abar, NI * D, T); TK(abar_f, NI * D, float); TK(hc0, NI * 2 * H, float);
+    TK(X, R * (2 * H + D), T); TK(Hn, R * H, T); TK(Cc, R * H, float); TK(Cn, R * H, float); TK(UF, R * (H + D), float);
+    TK(Ctx, R * D, T); TK(P1, a.ado ? R * H : 0, T); TK(P2, a.ado ? R * H : 0, T); TK(Comb, a.ado ? R * H : 0, T);
+    TK(logits, R * V, float); TK(alpha_hist, a.attention ? S * R * L : 0, float);
+    TK(top_preds, R, float); TK(prev_word, R, int64_t);
+    TK(live, NI, int); TK(done, NI, int); TK(n_active, 1, int); TK(parent, R, int);
+    TK(cand_word, S * R, int); TK(cand_parent, S * R, int); TK(slot_cand, S * R, int);
+    TK(comp_score, R, float); TK(comp_step, R, int); TK(comp_cand, R, int); TK(ncomp, NI, int); TK(last_step, NI, int); TK(last_n, NI, int);
+#undef TK
+    w.total = off;
+    return off;
+}
+
+__global__ void beam_init_state_kernel(int* live, int* done, int* n_active, int* ncomp, int* last_step, int* last_n,
+                                       float* top_preds, int64_t* prev_word, int NI, int beam, int64_t start) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) *n_active = NI;
+    if (i < NI) { live[i] = beam; done[i] = 0; ncomp[i] = 0; last_step[i] = 0; last_n[i] = beam; }
+    if (i < NI * beam) { top_preds[i] = 0.0f; prev_word[i] = start; }     // decoder.py:166-171
+}
+
+template <typename T>
+int beam_search_t(const sat_beam_args& a) {
+    constexpr bool PRECISE = IsF32<T>::value;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(a.stream);
+    BeamWs<T> w;
+    const int64_t need = beam_carve<T>(a, w, reinterpret_cast<uint8_t*>(a.workspace));
+    SAT_REQUIRE(a.workspace && a.workspace_bytes >= need, "beam workspace too small: %lld < %lld", (long long)a.workspace_bytes, (long long)need);
+    const int NI = a.NI, L = a.L, D = a.D, H = a.H, V = a.V, NB = a.beam, R = NI * NB;
+    const int64_t xw = 2 * (int64_t)H + D;
+    // ---- weights ----
+    if (a.attention) {
+        SAT_TRY(misc::pack_weight<T>(st, w.w_att, D, a.att_W_w, D, H, D, 0, 0));
+        SAT_TRY(misc::pack_weight<T>(st, w.w_uf, H, a.att_U_w, H, H, H, 0, 0));
+        SAT_TRY(misc::pack_weight<T>(st, w.w_uf + (size_t)H * H, H, a.f_beta_w, H, D, H, 0, 0));
+        SAT_TRY(misc::pack_bias(st, w.b_uf, a.att_U_b, nullptr, H, 0));
+        SAT_TRY(misc::pack_bias(st, w.b_uf + H, a.f_beta_b, nullptr, D, 0));
+    }
+    SAT_TRY(misc::pack_weight<T>(st, w.w_gall, xw, a.lstm_w_ih, H + D, 4 * H, H + D, 0, H));      // cols [0,H+D): [emb | ctx]
+    SAT_TRY(misc::pack_weight<T>(st, w.w_gall + H + D, xw, a.lstm_w_hh, H, 4 * H, H, 0, H));      // cols [H+D, 2H+D): h
+    SAT_TRY(misc::pack_bias(st, w.b_g, a.lstm_b_ih, a.lstm_b_hh, 4 * H, H));
+    SAT_TRY(misc::pack_weight<T>(st, w.w_init, D, a.init_h_w, D, H, D, 0, 0));
+    SAT_TRY(misc::pack_weight<T>(st, w.w_init + (size_t)H * D, D, a.init_c_w, D, H, D, 0, 0));
+    SAT_TRY(misc::pack_bias(st, w.b_init, a.init_h_b, nullptr, H, 0));
+    SAT_TRY(misc::pack_bias(st, w.b_init + H, a.init_c_b, nullptr, H, 0));
+    const float* out_b = a.ado ? a.f_out_b : a.deep_b;
+    if (a.ado) {
+        SAT_REQUIRE(a.f_h_w && a.f_z_w && a.f_out_w, "ado=1 needs f_h/f_z/f_out parameters");
+        SAT_TRY(misc::pack_weight<T>(st, w.w_fh, H, a.f_h_w, H, H, H, 0, 0));
+        SAT_TRY(misc::pack_weight<T>(st, w.w_fz, D, a.f_z_w, D, H, D, 0, 0));
+        SAT_TRY(misc::pack_weight<T>(st, w.w_out, H, a.f_out_w, H, V, H, 0, 0));
+    } else {
+        SAT_TRY(misc::pack_weight<T>(st, w.w_out, H, a.deep_w, H, V, H, 0, 0));
+    }
+    // ---- per-image precompute ----
+    if (reinterpret_cast<const void*>(w.a_c) != a.img_features) {
+        if (a.a_dtype == SAT_DTYPE_F32)
+            SAT_TRY((misc::cast3d<float, T>(st, w.a_c, reinterpret_cast<const float*>(a.img_features), NI, L, D, a.a_stride_b, a.a_stride_l, a.a_stride_d)));
+        else
+            SAT_TRY((misc::cast3d<bf16, T>(st, w.a_c, reinterpret_cast<const bf16*>(a.img_features), NI, L, D, a.a_stride_b, a.a_stride_l, a.a_stride_d)));
+    }
+    SAT_TRY(misc::mean_l<T>(st, w.a_c, w.abar_f, w.abar, NI, L, D));
+    {
+        auto e = lin<T>(NI, 2 * H, w.b_init, SAT_ACT_TANH, w.hc0, 2 * H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.abar, D, true, w.w_init, D, true, NI, 2 * H, D, e));
+    }
+    if (a.attention) {
+        auto e = lin<T>(NI * L, H, a.att_W_b, SAT_ACT_NONE, nullptr, 0, w.wa, H);
+        SAT_TRY(gemm<T>(st, w.a_c, D, true, w.w_att, D, true, NI * L, H, D, e));
+    }
+    beam::init_rows_kernel<T><<<R, 128, 0, st>>>(w.X, xw, H + D, H, w.Cc, w.hc0, w.abar, a.attention ? 0 : 1, NB, H, D);
+    beam_init_state_kernel<<<sat_cdiv(R, 128), 128, 0, st>>>(w.live, w.done, w.n_active, w.ncomp, w.last_step, w.last_n, w.top_preds,
+                                                             w.prev_word, NI, NB, (int64_t)a.start_token);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    const int S = a.max_steps + 1;        // iterations 1..max_steps+1 (Q17)
+    for (int step = 1; step <= S; ++step) {
+        SAT_TRY(misc::gather_rows<T>(st, w.X, xw, a.embedding, H, w.prev_word, 1, R, V));                  // decoder.py:183
+        if (a.attention) {
+            auto e = lin<T>(R, H + D, w.b_uf, SAT_ACT_NONE, w.UF, H + D, nullptr, 0);
+            SAT_TRY(gemm<T>(st, w.X + H + D, xw, true, w.w_uf, H, true, R, H + D, H, e));
+            attn::FwdParams p;
+            memset(&p, 0, sizeof(p));
+            p.a = w.a_c; p.wa = w.wa; p.uf = w.UF; p.ld_uf = H + D; p.v = a.att_v_w; p.bv = a.att_v_b;
+            p.alpha = w.alpha_hist + (size_t)step * R * L; p.ld_alpha = L;
+            p.ctx = w.Ctx; p.ld_ctx = D; p.z = w.X + H; p.ld_z = xw;
+            p.NI = NI; p.NB = NB; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
+            SAT_TRY((attn::launch_fwd<T, PRECISE>(p, st)));
+        }
+        EpiLstm<T, PRECISE> e;
+        memset(&e, 0, sizeof(e));
+        e.bias = w.b_g; e.c_prev = w.Cc; e.ld_cp = H; e.c_out = w.Cn; e.ld_co = H; e.h_next = w.Hn; e.ld_hn = H;
+        e.M = R; e.H = H;
+        SAT_TRY(gemm<T>(st, w.X, xw, true, w.w_gall, xw, true, R, 4 * H, (int)xw, e));                     // decoder.py:196-197
+        if (!a.ado) {
+            auto eo = lin<T>(R, V, out_b, SAT_ACT_NONE, w.logits, V, nullptr, 0);
+            eo.vec_ok = eo.vec_ok && (V % 8 == 0);
+            SAT_TRY(gemm<T>(st, w.Hn, H, true, w.w_out, H, true, R, V, H, eo));                            // decoder.py:203
+        } else {
+            auto e1 = lin<T>(R, H, a.f_h_b, SAT_ACT_RELU, nullptr, 0, w.P1, H);
+            SAT_TRY(gemm<T>(st, w.Hn, H, true, w.w_fh, H, true, R, H, H, e1));
+            auto e2 = lin<T>(R, H, a.f_z_b, SAT_ACT_RELU, nullptr, 0, w.P2, H);
+            if (a.attention) SAT_TRY(gemm<T>(st, w.Ctx, D, true, w.w_fz, D, true, R, H, D, e2));
+            else SAT_TRY(gemm<T>(st, w.X + H, xw, true, w.w_fz, D, true, R, H, D, e2));
+            // comb = P1 + P2 + emb (emb = X[:, :H], strided rows)
+            beam_add3_kernel<T><<<R, 128, 0, st>>>(w.Comb, w.P1, w.P2, w.X, xw, H);
+            SAT_CHECK_CUDA(cudaGetLastError());
+            auto e3 = lin<T>(R, V, out_b, SAT_ACT_RELU, w.logits, V, nullptr, 0);
+            e3.vec_ok = e3.vec_ok && (V % 8 == 0);
+            SAT_TRY(gemm<T>(st, w.Comb, H, true, w.w_out, H, true, R, V, H, e3));                          // decoder.py:199-201
+        }
+        beam::StepParams sp;
+        sp.logits = w.logits; sp.top_preds = w.top_preds; sp.prev_word = w.prev_word; sp.live = w.live; sp.done = w.done;
+        sp.n_active = w.n_active; sp.parent = w.parent; sp.cand_word = w.cand_word; sp.cand_parent = w.cand_parent;
+        sp.slot_cand = w.slot_cand; sp.comp_score = w.comp_score; sp.comp_step = w.comp_step; sp.comp_cand = w.comp_cand;
+        sp.ncomp = w.ncomp; sp.last_step = w.last_step; sp.last_n = w.last_n;
+        sp.NI = NI; sp.beam = NB; sp.V = V; sp.step = step; sp.max_steps = a.max_steps;
+        sp.stop_a = 1; sp.stop_b = a.bert ? 0 : 102;
+        beam::topk_step_kernel<<<NI, beam::TOPK_THREADS, 0, st>>>(sp);
+        beam::gather_state_kernel<T><<<R, 128, 0, st>>>(w.X, xw, H + D, w.Hn, w.Cc, w.Cn, w.parent, w.live, w.done, NB, H);
+        SAT_CHECK_CUDA(cudaGetLastError());
+        if ((step % 4) == 0 && step < S) {     // early exit once every image has finished (no effect on results)
+            int active = 1;
+            SAT_CHECK_CUDA(cudaMemcpyAsync(&active, w.n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
+            SAT_CHECK_CUDA(cudaStreamSynchronize(st));
+            if (active <= 0) break;
+        }
+    }
+    beam::FinalParams fp;
+    fp.cand_word = w.cand_word; fp.cand_parent = w.cand_parent; fp.slot_cand = w.slot_cand; fp.comp_score = w.comp_score;
+    fp.comp_step = w.comp_step; fp.comp_cand = w.comp_cand; fp.ncomp = w.ncomp; fp.last_step = w.last_step; fp.last_n = w.last_n;
+    fp.alpha_hist = w.alpha_hist; fp.out_len = a.out_len; fp.out_status = a.out_status; fp.out_tokens = a.out_tokens;
+    fp.out_alphas = a.out_alphas; fp.out_last_alpha = a.out_last_alpha; fp.out_live = a.out_live;
+    fp.NI = NI; fp.beam = NB; fp.L = L; fp.maxlen = a.max_steps + 2; fp.start_token = a.start_token; fp.attention = a.attention;
+    beam::finalize_kernel<<<NI, 256, 0, st>>>(fp);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}

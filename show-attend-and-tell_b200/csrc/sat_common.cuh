@@ -206,3 +206,13 @@ __device__ __forceinline__ bool elect_one() {
         : "=r"(pred));
     return pred != 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// optional in-stream event profiling of kernel categories (bench.py roofline section)
+// ---------------------------------------------------------------------------------------------
+enum { SAT_PROF_ATTN_FWD = 0, SAT_PROF_ATTN_BWD = 1, SAT_PROF_GEMM = 2, SAT_PROF_NCAT = 3 };
+struct SatProfScope {
+    int cat; cudaStream_t st; int slot;
+    SatProfScope(int cat, cudaStream_t st);
+    ~SatProfScope();
+};

@@ -17,6 +17,7 @@ template <typename T> struct IsF32 { static constexpr bool value = std::is_same<
 template <typename T, typename Epi>
 int gemm(cudaStream_t s, const T* A, int64_t lda, bool a_k, const T* B, int64_t ldb, bool b_k, int M, int N, int K,
          const Epi& epi, int bn = 0) {
+    SatProfScope prof(SAT_PROF_GEMM, s);
     if constexpr (IsF32<T>::value) {
         return simt::launch<float, Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi);
     } else {

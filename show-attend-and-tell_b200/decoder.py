@@ -44,13 +44,12 @@ class _DecoderFn(torch.autograd.Function):
     """autograd bridge: forward = sat_decoder_forward, backward = sat_decoder_backward."""
 
     @staticmethod
-    def forward(ctx, module, img_features, captions, dropout_mask, fused, alpha_c, *params):
+    def forward(ctx, module, img_features, captions, dropout_mask, fused, alpha_c, need_grad, *params):
         L = _lib.lib()
         dev = img_features.device
         B, Lloc, D = img_features.shape
         T = captions.shape[1] - 1
         H, V = module.embedding_size, module.vocabulary_size
-        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
         a = _lib.DecoderArgs()
         a.struct_bytes = C.sizeof(_lib.DecoderArgs)
         a.dtype = _lib.dtype_code(module.compute_dtype)
@@ -85,7 +84,9 @@ class _DecoderFn(torch.autograd.Function):
         ctx.module = module
         ctx.param_list = params
         ctx.fused = fused
-        ctx.mark_non_differentiable(*([] if not fused else [preds]))
+        ctx.set_materialize_grads(False)
+        if fused:
+            ctx.mark_non_differentiable(preds, alphas)    # the regulariser on alphas is already inside the fused loss
         if fused:
             return loss[2], preds, alphas
         return preds, alphas
@@ -100,13 +101,13 @@ class _DecoderFn(torch.autograd.Function):
         g.struct_bytes = C.sizeof(_lib.DecoderGrads)
         hold = []
         if ctx.fused:
-            dloss, _, dalphas = gouts
+            dloss = gouts[0]
+            if dloss is None:
+                dloss = torch.zeros(1, device=dev)
             dloss = dloss.to(torch.float32).contiguous().reshape(1)
             hold.append(dloss)
             g.dloss = dloss.data_ptr()
             g.dpreds = None
-            if dalphas is not None:
-                raise RuntimeError("sat_b200: forward_loss already folds the alpha regulariser; do not backprop through alphas")
         else:
             dpreds, dalphas = gouts
             if dpreds is None:
@@ -135,7 +136,7 @@ class _DecoderFn(torch.autograd.Function):
         out = []
         for name, p in module.named_parameters():
             out.append(grads.get(name))       # None reproduces the reference's grad=None pattern (Q6, Q7)
-        return (None, None, None, None, None, None, *out)
+        return (None, None, None, None, None, None, None, *out)
 
 
 class Decoder(nn.Module):
@@ -227,7 +228,8 @@ class Decoder(nn.Module):
         B, T = img_features.shape[0], captions.shape[1] - 1
         mask = self._dropout_mask(B, T, img_features.device, dropout_masks)
         params = tuple(p for _, p in self.named_parameters())
-        return _DecoderFn.apply(self, img_features.detach(), captions, mask, False, 0.0, *params)
+        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        return _DecoderFn.apply(self, img_features.detach(), captions, mask, False, 0.0, need_grad, *params)
 
     def forward_loss(self, img_features, captions, alpha_c=1.0, *, dropout_masks=None):
         """Extension: forward + the train.py:150-162 loss fused on device.  Returns (loss, preds, alphas)."""
@@ -235,7 +237,8 @@ class Decoder(nn.Module):
         B, T = img_features.shape[0], captions.shape[1] - 1
         mask = self._dropout_mask(B, T, img_features.device, dropout_masks)
         params = tuple(p for _, p in self.named_parameters())
-        return _DecoderFn.apply(self, img_features.detach(), captions, mask, True, float(alpha_c), *params)
+        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        return _DecoderFn.apply(self, img_features.detach(), captions, mask, True, float(alpha_c), need_grad, *params)
 
     # ------------------------------------------------------------------------------------------
     def get_init_lstm_state(self, img_features):

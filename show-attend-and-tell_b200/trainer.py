@@ -1,0 +1,121 @@
+"""Train step driver for the decoder hot path (what train.py:128-164 does around `decoder(...)`):
+
+    loss = trainer.step(img_features, captions)
+
+= sat_decoder_forward (with the train.py:150-162 loss fused) -> sat_decoder_backward writing gradients straight
+into one flat fp32 buffer -> (world > 1) one NCCL all-reduce of that buffer over NVLink -> fused Adam
+(sat_adam_step) on the flat parameter buffer.  It bypasses autograd: no tape, no per-tensor optimizer launches.
+Data parallelism is one process per GPU, batch-sharded, gradients averaged; parameters the
+reference leaves with grad=None (Q6, Q7) are simply not part of the flat buffer.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+class FusedTrainStep:
+    def __init__(self, decoder, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, alpha_c=1.0, process_group=None,
+                 distributed=None):
+        self.dec = decoder
+        self.lr, self.betas, self.eps, self.alpha_c = lr, betas, eps, alpha_c
+        self.distributed = dist.is_initialized() if distributed is None else distributed
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if self.distributed else 1
+        unused = decoder.unused_parameter_keys()
+        self.train_keys = [n for n, p in decoder.named_parameters() if p.requires_grad and n not in unused]
+        named = dict(decoder.named_parameters())
+        dev = next(decoder.parameters()).device
+        offsets, off = {}, 0
+        for k in self.train_keys:
+            offsets[k] = off
+            off = (off + named[k].numel() + 3) & ~3          # keep every tensor 16-byte aligned
+        n = off
+        # flat buffers; each parameter becomes a view into `flat_param` (state_dict keys/shapes unchanged)
+        self.flat_param = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.flat_grad = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.exp_avg = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.exp_avg_sq = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.grad_views = {}
+        for k in self.train_keys:
+            p, o = named[k], offsets[k]
+            m = p.numel()
+            self.flat_param[o:o + m].copy_(p.data.reshape(-1))
+            p.data = self.flat_param[o:o + m].view_as(p)
+            self.grad_views[k] = self.flat_grad[o:o + m].view_as(p)
+        self.n = off
+        self.step_count = 0
+        self._ws = None
+        self._ws_key = None
+        self.last_alphas = None
+
+    def _args(self, img_features, captions, dropout_mask):
+        dec = self.dec
+        L = _lib.lib()
+        dev = img_features.device
+        B, Lloc, D = img_features.shape
+        T = captions.shape[1] - 1
+        a = _lib.DecoderArgs()
+        a.struct_bytes = C.sizeof(_lib.DecoderArgs)
+        a.dtype = _lib.dtype_code(dec.compute_dtype)
+        a.B, a.L, a.D, a.H, a.V, a.T = B, Lloc, D, dec.embedding_size, dec.vocabulary_size, T
+        a.tf, a.ado, a.attention, a.gate = (int(dec.use_tf), int(dec.use_advanced_deep_output), int(dec.use_attention),
+                                            int(dec.use_gate))
+        a.start_token = int(dec.start_token)
+        a.need_grad, a.fused_loss = 1, 1
+        a.alpha_c = float(self.alpha_c)
+        a.a_dtype = _lib.dtype_code(img_features.dtype)
+        a.img_features = img_features.data_ptr()
+        a.a_stride_b, a.a_stride_l, a.a_stride_d = img_features.stride()
+        a.captions = captions.data_ptr()
+        a.cap_stride = captions.stride(0)
+        a.dropout_mask = None if dropout_mask is None else dropout_mask.data_ptr()
+        named = dict(dec.named_parameters())
+        for field in _lib.PARAM_FIELDS:
+            p = named.get(_lib.PARAM_KEYS[field])
+            setattr(a, field, None if p is None else p.data_ptr())
+        key = (B, Lloc, D, T, a.a_dtype)
+        if self._ws_key != key:
+            self.preds = torch.empty(B, T, a.V, device=dev, dtype=torch.float32)
+            self.alphas = torch.empty(B, T, Lloc, device=dev, dtype=torch.float32)
+            self.loss = torch.zeros(3, device=dev, dtype=torch.float32)
+            a.preds, a.alphas, a.loss = self.preds.data_ptr(), self.alphas.data_ptr(), self.loss.data_ptr()
+            nbytes = C.c_int64(0)
+            _lib.check(L.sat_decoder_workspace_bytes(C.byref(a), C.byref(nbytes)), "sat_decoder_workspace_bytes")
+            self._ws = torch.empty(nbytes.value + 256, device=dev, dtype=torch.uint8)
+            self._ws_bytes = nbytes.value
+            self._ws_key = key
+        a.preds, a.alphas, a.loss = self.preds.data_ptr(), self.alphas.data_ptr(), self.loss.data_ptr()
+        a.workspace = self._ws.data_ptr() + ((-self._ws.data_ptr()) % 256)
+        a.workspace_bytes = self._ws_bytes
+        a.stream = torch.cuda.current_stream(dev).cuda_stream
+        return a
+
+    def step(self, img_features, captions, dropout_mask=None, optimizer_step=True):
+        """One training step; returns the device tensor [ce, alpha_reg, total] (no host sync)."""
+        dec = self.dec
+        L = _lib.lib()
+        captions = dec._check_inputs(img_features, captions)
+        if dropout_mask is None and dec.training:
+            dropout_mask = dec._dropout_mask(img_features.shape[0], captions.shape[1] - 1, img_features.device, None)
+        a = self._args(img_features, captions, dropout_mask)
+        _lib.check(L.sat_decoder_forward(C.byref(a)), "sat_decoder_forward")
+        g = _lib.DecoderGrads()
+        g.struct_bytes = C.sizeof(_lib.DecoderGrads)
+        for field in _lib.PARAM_FIELDS:
+            v = self.grad_views.get(_lib.PARAM_KEYS[field])
+            setattr(g, field, None if v is None else v.data_ptr())
+        _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(g)), "sat_decoder_backward")
+        if self.world > 1:
+            dist.all_reduce(self.flat_grad, group=self.pg)                  # NCCL sum over NVLink
+        if optimizer_step:
+            self.step_count += 1
+            _lib.check(L.sat_adam_step(self.flat_param.data_ptr(), self.flat_grad.data_ptr(), self.exp_avg.data_ptr(),
+                                       self.exp_avg_sq.data_ptr(), self.n, self.lr, self.betas[0], self.betas[1], self.eps,
+                                       0.0, self.step_count, 1.0 / self.world, a.stream), "sat_adam_step")
+        self.last_alphas = self.alphas
+        return self.loss
