@@ -101,7 +101,10 @@ def test_decoder_vs_oracle(case, dt):
         got = p.grad.cpu()
         scale = ref.abs().max().item() + 1e-12
         err = (got - ref).abs().max().item()
-        if dt == torch.float32:
+        if n == "attention.v.bias":
+            # softmax is shift invariant: the true gradient is 0 and both sides hold only rounding noise
+            assert ref.abs().max().item() < 1e-6 and got.abs().max().item() < 1e-5, (n, got, ref)
+        elif dt == torch.float32:
             assert err <= 2e-3 * scale + 1e-7, (n, err, scale)
         elif cfg["ado"]:
             # bf16 vs the fp32 oracle through ReLUs: a pre-activation within bf16 noise of 0 flips its mask and changes a
