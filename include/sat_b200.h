@@ -24,6 +24,8 @@ const char* sat_last_error(void);
 int sat_version(void);
 /* debug knob: 1 = run bf16 GEMMs on the SIMT kernel (bring-up cross-check of the tcgen05 kernel) */
 int sat_set_force_simt(int on);
+/* debug knob: 1 = run the attention step on the generic cluster kernels even where the streaming kernels apply */
+int sat_set_attn_generic(int on);
 
 /* Bench instrumentation: CUDA-event pairs around every attention-step (fwd = category 0, bwd = 1) and GEMM (2) launch,
  * recorded on the launching stream.  sat_profile_read fills ms[3] / counts[3] and resets. */
@@ -43,12 +45,15 @@ int sat_attn_step_fwd(int dtype, int NI, int NB, int L, int D, int H, const void
                       int64_t ld_uf, const float* v, const float* bv, int gate, float* alpha, int64_t ld_alpha,
                       void* ctx, int64_t ld_ctx, void* z, int64_t ld_z, void* stream);
 
-/* K2 backward (autograd of the lines above inside loss.backward(), train.py:163). */
+/* K2 backward (autograd of the lines above inside loss.backward(), train.py:163).
+ * The gradient wrt the hoisted projection Wa is produced in one of two ways: dpre_out != NULL -> this step's
+ * dpre (B,L,H) is written once in the compute dtype (streaming kernel; the caller sums the steps afterwards);
+ * dpre_out == NULL -> it is accumulated into the fp32 buffer dwa_acc (first != 0 overwrites). */
 int sat_attn_step_bwd(int dtype, int B, int L, int D, int H, const void* a, const void* wa, const float* uf, int64_t ld_uf,
                       const float* v, const float* alpha, int64_t ld_alpha, const void* ctx, int64_t ld_ctx,
                       const float* dz, int64_t ld_dz, const float* dctx_extra, int64_t ld_dce, const float* galpha,
                       int64_t ld_ga, int gate, void* duf, int64_t ld_duf, float* dwa_acc, float* dv_acc, float* dbv_acc,
-                      float* da_acc, int first, void* stream);
+                      float* da_acc, int first, void* dpre_out, void* stream);
 
 /* Arguments of the sequence drivers: Decoder.forward (decoder.py:69-135) and its backward.  Parameter pointers are
  * the fp32 tensors of the reference state_dict; NULL where a module does not exist (f_* without ado). */

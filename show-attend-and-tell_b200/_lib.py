@@ -72,7 +72,7 @@ class BeamArgs(C.Structure):
 
 _LIB = None
 
-EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_bwd",
+EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_set_attn_generic", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_bwd",
            "sat_decoder_workspace_bytes", "sat_decoder_forward", "sat_decoder_backward", "sat_beam_workspace_bytes",
            "sat_beam_search", "sat_adam_step", "sat_profile", "sat_profile_read"]
 
@@ -92,7 +92,7 @@ def lib():
         L.sat_attn_step_fwd.argtypes = [C.c_int] * 6 + [_vp, _vp, _vp, _i64, _vp, _vp, C.c_int, _vp, _i64, _vp, _i64,
                                                         _vp, _i64, _vp]
         L.sat_attn_step_bwd.argtypes = ([C.c_int] * 5 + [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp,
-                                                         _i64, _vp, _i64, C.c_int, _vp, _i64, _vp, _vp, _vp, _vp, C.c_int, _vp])
+                                                         _i64, _vp, _i64, C.c_int, _vp, _i64, _vp, _vp, _vp, _vp, C.c_int, _vp, _vp])
         L.sat_decoder_workspace_bytes.argtypes = [C.POINTER(DecoderArgs), C.POINTER(_i64)]
         L.sat_decoder_forward.argtypes = [C.POINTER(DecoderArgs)]
         L.sat_decoder_backward.argtypes = [C.POINTER(DecoderArgs), C.POINTER(DecoderGrads)]

@@ -73,7 +73,7 @@ class _AttentionFn(torch.autograd.Function):
                                        vflat.data_ptr(), alpha.data_ptr(), Lloc, ctxv.data_ptr(), D, dz.data_ptr(), D,
                                        None, 0, None if ga is None else ga.data_ptr(), Lloc, 0, duf.data_ptr(), H + D,
                                        dwa.data_ptr(), dv.data_ptr(), dbv.data_ptr(), None if da is None else da.data_ptr(),
-                                       1, st), "sat_attn_step_bwd")
+                                       1, None, st), "sat_attn_step_bwd")
         dUh = duf[:, :H].contiguous()
         dwa_t = dwa.reshape(B * Lloc, H).to(dt)
         gUw = torch.empty(H, H, device=dev, dtype=torch.float32)

@@ -314,6 +314,7 @@ struct BwdParams {
     float* dv_acc;          // (B, H) fp32
     float* dbv_acc;         // (B)   fp32
     float* da_acc;          // (B, L, D) fp32 or null
+    void* dpre_out;         // T (B, L, H): this step's dpre written once (streaming kernel); null -> accumulate into dwa_acc
     int first;              // first backward step: overwrite the accumulators
     int B, L, D, H, gate;
     int C, Lc, Ds, Hs, G2;

@@ -4,6 +4,7 @@
 #include "sat_beam.cuh"
 
 int g_force_simt = 0;
+int g_attn_generic = 0;
 static thread_local char g_err[1024] = "";
 
 void sat_set_error(const char* fmt, ...) {
@@ -58,6 +59,7 @@ extern "C" {
 const char* sat_last_error(void) { return g_err; }
 int sat_version(void) { return 100; }
 int sat_set_force_simt(int on) { g_force_simt = on ? 1 : 0; return SAT_OK; }
+int sat_set_attn_generic(int on) { g_attn_generic = on ? 1 : 0; return SAT_OK; }
 
 /* profiling: sat_profile(1) starts recording CUDA-event pairs around attention-step and GEMM launches on their own
  * stream; sat_profile_read() synchronises and returns per-category total ms and launch counts, then resets. */
@@ -103,8 +105,8 @@ int sat_attn_step_fwd(int dtype, int NI, int NB, int L, int D, int H, const void
     p.ctx = ctx; p.ld_ctx = ld_ctx; p.z = z; p.ld_z = ld_z;
     p.NI = NI; p.NB = NB; p.L = L; p.D = D; p.H = H; p.gate = gate;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (dtype == SAT_DTYPE_F32) return attn::launch_fwd<float, true>(p, st);
-    if (dtype == SAT_DTYPE_BF16) return attn::launch_fwd<bf16, false>(p, st);
+    if (dtype == SAT_DTYPE_F32) return attn_step_fwd<float, true>(p, st);
+    if (dtype == SAT_DTYPE_BF16) return attn_step_fwd<bf16, false>(p, st);
     sat_set_error("bad dtype %d", dtype);
     return SAT_ERR_ARG;
 }
@@ -113,18 +115,18 @@ int sat_attn_step_bwd(int dtype, int B, int L, int D, int H, const void* a, cons
                       const float* v, const float* alpha, int64_t ld_alpha, const void* ctx, int64_t ld_ctx,
                       const float* dz, int64_t ld_dz, const float* dctx_extra, int64_t ld_dce, const float* galpha,
                       int64_t ld_ga, int gate, void* duf, int64_t ld_duf, float* dwa_acc, float* dv_acc, float* dbv_acc,
-                      float* da_acc, int first, void* stream) {
+                      float* da_acc, int first, void* dpre_out, void* stream) {
     SAT_TRY(require_sm100());
     attn::BwdParams p;
     memset(&p, 0, sizeof(p));
     p.a = a; p.wa = wa; p.uf = uf; p.ld_uf = ld_uf; p.v = v; p.alpha = alpha; p.ld_alpha = ld_alpha;
     p.ctx = ctx; p.ld_ctx = ld_ctx; p.dz = dz; p.ld_dz = ld_dz; p.dctx_extra = dctx_extra; p.ld_dce = ld_dce;
     p.galpha = galpha; p.ld_ga = ld_ga; p.duf = duf; p.ld_duf = ld_duf; p.dwa_acc = dwa_acc; p.dv_acc = dv_acc;
-    p.dbv_acc = dbv_acc; p.da_acc = da_acc; p.first = first;
+    p.dbv_acc = dbv_acc; p.da_acc = da_acc; p.first = first; p.dpre_out = dpre_out;
     p.B = B; p.L = L; p.D = D; p.H = H; p.gate = gate;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (dtype == SAT_DTYPE_F32) return attn::launch_bwd<float, true>(p, st);
-    if (dtype == SAT_DTYPE_BF16) return attn::launch_bwd<bf16, false>(p, st);
+    if (dtype == SAT_DTYPE_F32) return attn_step_bwd<float, true>(p, st);
+    if (dtype == SAT_DTYPE_BF16) return attn_step_bwd<bf16, false>(p, st);
     sat_set_error("bad dtype %d", dtype);
     return SAT_ERR_ARG;
 }

@@ -343,7 +343,7 @@ int beam_search_t(const sat_beam_args& a) {
             p.alpha = w.alpha_hist + (size_t)step * R * L; p.ld_alpha = L;
             p.ctx = w.Ctx; p.ld_ctx = D; p.z = w.X + H; p.ld_z = xw;
             p.NI = NI; p.NB = NB; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
-            SAT_TRY((attn::launch_fwd<T, PRECISE>(p, st)));
+            SAT_TRY((attn_step_fwd<T, PRECISE>(p, st)));
         }
         EpiLstm<T, PRECISE> e;
         memset(&e, 0, sizeof(e));

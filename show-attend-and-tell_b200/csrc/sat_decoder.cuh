@@ -7,7 +7,7 @@
 #include "sat_epilogue.cuh"
 #include "sat_gemm_simt.cuh"
 #include "sat_gemm_tc.cuh"
-#include "sat_attn.cuh"
+#include "sat_attn_stream.cuh"
 #include "sat_misc.cuh"
 
 extern int g_force_simt;
@@ -69,7 +69,9 @@ struct DecWs {
     float* dZH;      // (B,D+H)
     T* dUF;          // (T,B,H+D)
     float *dh_carry, *dc_carry;
-    float* dwa_acc;  // (B,L,H)
+    float* dwa_acc;  // (B,L,H)      generic attention backward: fp32 accumulator over time
+    T* dpre_all;     // (T,B,L,H)    streaming attention backward: each step's dpre written once
+    bool bwd_stream;
     T* dwa_t;        // (B,L,H)
     float *dv_acc, *dbv_acc;
     T* dE;           // (T,B,H)
@@ -115,7 +117,9 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
     if (a.need_grad) {
         TK(dlog, B * Tn * w.Vp, T); TK(dHd, B * Tn * H, float); TK(dG, B * Tn * 4 * H, T); TK(dZH, B * (D + H), float);
         TK(dUF, B * Tn * (H + D), T); TK(dh_carry, B * H, float); TK(dc_carry, B * H, float);
-        TK(dwa_acc, a.attention ? B * L * H : 0, float); TK(dwa_t, a.attention ? B * L * H : 0, T);
+        w.bwd_stream = a.attention && attn_s::bwd_shape_eligible<T>(a.B, a.L, a.D, a.H);
+        TK(dwa_acc, (a.attention && !w.bwd_stream) ? B * L * H : 0, float); TK(dwa_t, a.attention ? B * L * H : 0, T);
+        TK(dpre_all, w.bwd_stream ? Tn * B * L * H : 0, T);
         TK(dv_acc, B * H, float); TK(dbv_acc, B, float);
         TK(dE, B * Tn * H, T); TK(dpre0, B * 2 * H, T); TK(galpha, B * Tn * L, float);
         int64_t gs = 4 * H * (D + H);
@@ -277,7 +281,7 @@ int decoder_forward_t(const sat_decoder_args& a) {
             p.ctx = w.Ctx + (size_t)t * B * D; p.ld_ctx = D;
             p.z = zh_t; p.ld_z = zw;
             p.NI = B; p.NB = 1; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
-            SAT_TRY((attn::launch_fwd<T, PRECISE>(p, st)));
+            SAT_TRY((attn_step_fwd<T, PRECISE>(p, st)));
         }
         // K3: gates = Xg[t] + [z | h] [W_ih[:,H:] | W_hh]^T, LSTM cell in the epilogue (decoder.py:108-115)
         EpiLstm<T, PRECISE> e;
@@ -400,9 +404,10 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
             p.galpha = galpha ? galpha + (size_t)t * L : nullptr; p.ld_ga = (int64_t)Tn * L;
             p.duf = w.dUF + (size_t)t * B * (H + D); p.ld_duf = H + D;
             p.dwa_acc = w.dwa_acc; p.dv_acc = w.dv_acc; p.dbv_acc = w.dbv_acc; p.da_acc = nullptr;
+            p.dpre_out = w.bwd_stream ? w.dpre_all + (size_t)t * B * L * H : nullptr;
             p.first = (t == Tn - 1);
             p.B = B; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
-            SAT_TRY((attn::launch_bwd<T, PRECISE>(p, st)));
+            SAT_TRY((attn_step_bwd<T, PRECISE>(p, st)));
             // dh_prev = dZH[:, D:] + [dUh | dfb] [U ; f_beta]
             auto e = lin<T>(B, H, nullptr, SAT_ACT_NONE, w.dh_carry, H, nullptr, 0, w.dZH + D, zw);
             SAT_TRY(gemm<T>(st, w.dUF + (size_t)t * B * (H + D), H + D, true, w.w_uf, H, false, B, H, H + D, e));
@@ -458,12 +463,16 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         if (g.att_U_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
         if (g.f_beta_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_b, w.gscratch + H, (size_t)D * 4, cudaMemcpyDeviceToDevice, st));
         // encoder projection: dW (H x D) = (sum_t dpre)^T a ; db_W = colsum ; dv, db_v
-        SAT_TRY((misc::cast<float, T>(st, w.dwa_t, w.dwa_acc, (int64_t)B * L * H)));
+        if (w.bwd_stream) SAT_TRY(misc::sum_over_t<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L * H, Tn));
+        else SAT_TRY((misc::cast<float, T>(st, w.dwa_t, w.dwa_acc, (int64_t)B * L * H)));
         if (g.att_W_w) {
             auto e2 = lin<T>(H, D, nullptr, SAT_ACT_NONE, g.att_W_w, D, nullptr, 0);
             SAT_TRY(gemm<T>(st, w.dwa_t, H, false, w.a_c, D, false, H, D, B * L, e2));
         }
-        if (g.att_W_b) SAT_TRY(misc::colsum<float>(st, w.dwa_acc, H, B * L, H, g.att_W_b, w.csum, w.csum_floats));
+        if (g.att_W_b) {
+            if (w.bwd_stream) SAT_TRY(misc::colsum<T>(st, w.dwa_t, H, B * L, H, g.att_W_b, w.csum, w.csum_floats));
+            else SAT_TRY(misc::colsum<float>(st, w.dwa_acc, H, B * L, H, g.att_W_b, w.csum, w.csum_floats));
+        }
         if (g.att_v_w) SAT_TRY(misc::colsum<float>(st, w.dv_acc, H, B, H, g.att_v_w, w.csum, w.csum_floats));
         if (g.att_v_b) SAT_TRY(misc::colsum<float>(st, w.dbv_acc, 1, B, 1, g.att_v_b, w.csum, w.csum_floats));
     }

@@ -99,6 +99,35 @@ int cast(cudaStream_t s, TO* dst, const TI* src, int64_t n, float scale = 1.0f) 
     return SAT_OK;
 }
 
+// out[i] = sum_t src[t*n + i]  (fp32 accumulation; 16-byte vectors; n % (16/sizeof(T)) == 0)
+template <typename T>
+__global__ void sum_over_t_kernel(T* __restrict__ out, const T* __restrict__ src, int64_t nvec, int64_t n, int Tn) {
+    constexpr int VEC = Vec16<T>::N;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+        float acc[VEC];
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) acc[k] = 0.0f;
+#pragma unroll 4
+        for (int t = 0; t < Tn; ++t) {
+            float f[VEC];
+            Vec16<T>::unpack(ldg_stream16(src + (size_t)t * n + i * VEC), f);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) acc[k] += f[k];
+        }
+        *reinterpret_cast<uint4*>(out + i * VEC) = Vec16<T>::pack(acc);
+    }
+}
+template <typename T>
+int sum_over_t(cudaStream_t s, T* out, const T* src, int64_t n, int Tn) {
+    constexpr int VEC = Vec16<T>::N;
+    SAT_REQUIRE(n % VEC == 0, "sum_over_t: n must be a multiple of %d", VEC);
+    const int64_t nvec = n / VEC;
+    const int blocks = (int)(sat_cdiv64(nvec, 256) < (int64_t)(148 * 8) ? sat_cdiv64(nvec, 256) : (int64_t)(148 * 8));
+    sum_over_t_kernel<T><<<blocks, 256, 0, s>>>(out, src, nvec, n, Tn);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
 // abar[b,d] = mean_l a[b,l,d]   (decoder.py:139 / :104)
 template <typename T>
 __global__ void mean_l_kernel(const T* __restrict__ a, float* __restrict__ out_f, T* __restrict__ out_t, int L, int D) {

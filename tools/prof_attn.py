@@ -1,4 +1,10 @@
-"""Tiny driver for ncu: a few attention-step fwd/bwd launches at the c2 shape through the C ABI."""
+"""Micro-benchmark / ncu driver of the attention-step kernels through the C ABI.
+
+  python tools/prof_attn.py [--B 256] [--D 2048] [--H 512] [--L 196] [--NB 1] [--dtype bf16|f32] [--iters 20] [--generic]
+
+Prints CUDA-event times per launch, achieved algorithmic GB/s, and the max difference between the streaming and
+the generic kernels on the same inputs (a self-check; the parity tests proper live in tests/)."""
+import argparse
 import os
 import sys
 
@@ -7,37 +13,100 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from sat_b200 import _lib  # noqa: E402
 
-B, L, D, H = 256, 196, 2048, 512
-dt = torch.bfloat16
+ap = argparse.ArgumentParser()
+ap.add_argument("--B", type=int, default=256)
+ap.add_argument("--L", type=int, default=196)
+ap.add_argument("--D", type=int, default=2048)
+ap.add_argument("--H", type=int, default=512)
+ap.add_argument("--NB", type=int, default=1)
+ap.add_argument("--dtype", default="bf16")
+ap.add_argument("--iters", type=int, default=20)
+ap.add_argument("--generic", action="store_true")
+ap.add_argument("--nocheck", action="store_true")
+args = ap.parse_args()
+B, L, D, H, NB = args.B, args.L, args.D, args.H, args.NB
+dt = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+code = 1 if args.dtype == "bf16" else 0
+es = 2 if code else 4
 Lb = _lib.lib()
 g = torch.Generator(device="cuda").manual_seed(0)
-a = torch.relu(torch.randn(B, L, D, device="cuda", generator=g)).to(dt)
-wa = torch.randn(B, L, H, device="cuda", generator=g).to(dt)
-uf = torch.randn(B, H + D, device="cuda", generator=g)
+R = B * NB
+# two input sets so that consecutive launches never hit the same lines in L2
+sets = []
+for i in range(2):
+    a = torch.relu(torch.randn(B, L, D, device="cuda", generator=g)).to(dt)
+    wa = torch.randn(B, L, H, device="cuda", generator=g).to(dt)
+    sets.append((a, wa))
+uf = torch.randn(R, H + D, device="cuda", generator=g)
 v = torch.randn(H, device="cuda", generator=g) * 0.05
 bv = torch.zeros(1, device="cuda")
-alpha = torch.empty(B, L, device="cuda")
-ctx = torch.empty(B, D, device="cuda", dtype=dt)
-z = torch.empty(B, D, device="cuda", dtype=dt)
+alpha = torch.empty(R, L, device="cuda")
+ctx = torch.empty(R, D, device="cuda", dtype=dt)
+z = torch.empty(R, D, device="cuda", dtype=dt)
 dz = torch.randn(B, D, device="cuda", generator=g)
+galpha = torch.randn(B, L, device="cuda", generator=g) * 0.01
 duf = torch.empty(B, H + D, device="cuda", dtype=dt)
 dwa = torch.zeros(B, L, H, device="cuda")
+dpre = torch.zeros(B, L, H, device="cuda", dtype=dt)
 dv = torch.zeros(B, H, device="cuda")
 dbv = torch.zeros(B, device="cuda")
 st = torch.cuda.current_stream().cuda_stream
-n = int(sys.argv[1]) if len(sys.argv) > 1 else 4
-e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-for it in range(n):
-    if it == n - 1:
-        e[0].record()
-    _lib.check(Lb.sat_attn_step_fwd(1, B, 1, L, D, H, a.data_ptr(), wa.data_ptr(), uf.data_ptr(), H + D, v.data_ptr(), bv.data_ptr(),
+
+
+def fwd(s):
+    a, wa = sets[s]
+    _lib.check(Lb.sat_attn_step_fwd(code, B, NB, L, D, H, a.data_ptr(), wa.data_ptr(), uf.data_ptr(), H + D, v.data_ptr(), bv.data_ptr(),
                                     1, alpha.data_ptr(), L, ctx.data_ptr(), D, z.data_ptr(), D, st))
-    if it == n - 1:
-        e[1].record()
-    _lib.check(Lb.sat_attn_step_bwd(1, B, L, D, H, a.data_ptr(), wa.data_ptr(), uf.data_ptr(), H + D, v.data_ptr(), alpha.data_ptr(), L,
-                                    ctx.data_ptr(), D, dz.data_ptr(), D, None, 0, None, 0, 1, duf.data_ptr(), H + D, dwa.data_ptr(),
-                                    dv.data_ptr(), dbv.data_ptr(), None, 0, st))
-    if it == n - 1:
-        e[2].record()
-torch.cuda.synchronize()
-print("fwd ms %.4f  bwd ms %.4f" % (e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2])))
+
+
+def bwd(s, stream_mode):
+    a, wa = sets[s]
+    _lib.check(Lb.sat_attn_step_bwd(code, B, L, D, H, a.data_ptr(), wa.data_ptr(), uf.data_ptr(), H + D, v.data_ptr(), alpha.data_ptr(), L,
+                                    ctx.data_ptr(), D, dz.data_ptr(), D, None, 0, galpha.data_ptr(), L, 1, duf.data_ptr(), H + D,
+                                    dwa.data_ptr(), dv.data_ptr(), dbv.data_ptr(), None, 1,
+                                    dpre.data_ptr() if stream_mode else None, st))
+
+
+def timeit(fn, n):
+    for i in range(3):
+        fn(i % 2)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(n):
+        fn(i % 2)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+if not args.nocheck:
+    Lb.sat_set_attn_generic(1)
+    fwd(0); torch.cuda.synchronize()
+    ref = (alpha.clone(), ctx.float().clone(), z.float().clone())
+    if NB == 1:
+        bwd(0, False); torch.cuda.synchronize()
+        refb = (duf.float().clone(), dwa.clone(), dv.clone(), dbv.clone())
+    Lb.sat_set_attn_generic(0)
+    alpha.zero_(); ctx.zero_(); z.zero_()
+    fwd(0); torch.cuda.synchronize()
+    print("fwd  max|d alpha| %.3e  max|d ctx| %.3e (scale %.3e)  max|d z| %.3e  rowsum err %.2e" % (
+        (alpha - ref[0]).abs().max().item(), (ctx.float() - ref[1]).abs().max().item(), ref[1].abs().max().item(),
+        (z.float() - ref[2]).abs().max().item(), (alpha.sum(1) - 1).abs().max().item()))
+    if NB == 1:
+        duf.zero_(); dv.zero_(); dbv.zero_()
+        bwd(0, True); torch.cuda.synchronize()
+        print("bwd  max|d duf| %.3e (scale %.3e)  max|d dpre| %.3e (scale %.3e)  max|d dv| %.3e (scale %.3e)  max|d dbv| %.3e" % (
+            (duf.float() - refb[0]).abs().max().item(), refb[0].abs().max().item(),
+            (dpre.float() - refb[1]).abs().max().item(), refb[1].abs().max().item(),
+            (dv - refb[2]).abs().max().item(), refb[2].abs().max().item(), (dbv - refb[3]).abs().max().item()))
+
+Lb.sat_set_attn_generic(1 if args.generic else 0)
+tf = timeit(fwd, args.iters)
+bytes_f = B * L * (H + D) * es
+print("fwd  %.2f us  %.0f GB/s (algorithmic %d MB)" % (tf * 1e3, bytes_f / tf / 1e6, bytes_f >> 20))
+if NB == 1:
+    smode = not args.generic
+    tb = timeit(lambda s: bwd(s, smode), args.iters)
+    bytes_b = B * (L * (H + D) * es + 2 * L * H * 4)
+    print("bwd  %.2f us  %.0f GB/s (algorithmic %d MB, SURVEY 8(d) figure)" % (tb * 1e3, bytes_b / tb / 1e6, bytes_b >> 20))
