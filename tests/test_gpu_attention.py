@@ -86,3 +86,117 @@ def test_attn_step_shared_features_rows(dt, NB):
         torch.testing.assert_close(alpha[r].cpu(), al, **(dict(rtol=2e-4, atol=1e-6) if dt == torch.float32 else dict(rtol=5e-2, atol=2e-3)))
         torch.testing.assert_close(ctx[r].float().cpu(), c, **TOL[dt])
         torch.testing.assert_close(z[r].float().cpu(), zz, **TOL[dt])
+
+
+# ---- streaming kernels (NI * groups >= 64, D in {512, 2048}, H in {512, 768}) -------------------------------------
+def _ref_step(P, a_used, wa_used, uh, fb, gate=True):
+    """fp32 reference of one attention step on already-projected features (rows share image r // NB)."""
+    v = P["attention.v.weight"].reshape(-1)
+    e = torch.tanh(wa_used + uh[:, None, :]) @ v + P["attention.v.bias"]
+    al = torch.softmax(e, 1)
+    c = (a_used * al[:, :, None]).sum(1)
+    return al, c, (torch.sigmoid(fb) * c if gate else c)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("NI,NB,L,D,H", [(70, 1, 196, 512, 512), (64, 1, 196, 2048, 512), (66, 1, 49, 2048, 768), (65, 1, 197, 512, 768),
+                                         (64, 5, 196, 512, 512), (33, 3, 196, 512, 512), (16, 10, 196, 512, 512)])
+def test_streaming_fwd_vs_oracle_and_generic(dt, NI, NB, L, D, H):
+    from sat_b200 import _lib
+    L_ = _lib.lib()
+    P, a, _ = _setup(NI, L, D, H, seed=7)
+    g = torch.Generator().manual_seed(13)
+    R = NI * NB
+    h = torch.tanh(torch.randn(R, H, generator=g))
+    ad = a.cuda().to(dt).contiguous()
+    af = ad.float().cpu()
+    Wad = (af @ P["attention.W.weight"].t() + P["attention.W.bias"]).cuda().to(dt).contiguous()
+    uh = h @ P["attention.U.weight"].t() + P["attention.U.bias"]
+    fb = h @ P["f_beta.weight"].t() + P["f_beta.bias"]
+    uf = torch.cat((uh, fb), 1).cuda().contiguous()
+    v = P["attention.v.weight"].reshape(-1).cuda().contiguous()
+    bv = P["attention.v.bias"].cuda()
+    out = {}
+    for mode in (0, 1):
+        alpha = torch.zeros(R, L, device="cuda")
+        ctx = torch.zeros(R, D, device="cuda", dtype=dt)
+        z = torch.zeros(R, D, device="cuda", dtype=dt)
+        L_.sat_set_attn_generic(mode)
+        try:
+            _lib.check(L_.sat_attn_step_fwd(_lib.dtype_code(dt), NI, NB, L, D, H, ad.data_ptr(), Wad.data_ptr(), uf.data_ptr(), H + D,
+                                            v.data_ptr(), bv.data_ptr(), 1, alpha.data_ptr(), L, ctx.data_ptr(), D, z.data_ptr(), D,
+                                            torch.cuda.current_stream().cuda_stream))
+            torch.cuda.synchronize()
+        finally:
+            L_.sat_set_attn_generic(0)
+        out[mode] = (alpha.cpu(), ctx.float().cpu(), z.float().cpu())
+    rows = torch.arange(R) // NB
+    al, c, zz = _ref_step(P, af[rows], Wad.float().cpu()[rows], uh, fb)
+    ta = dict(rtol=2e-4, atol=1e-6) if dt == torch.float32 else dict(rtol=5e-2, atol=2e-3)
+    for mode in (0, 1):
+        alpha, ctx, z = out[mode]
+        torch.testing.assert_close(alpha, al, **ta)
+        torch.testing.assert_close(ctx, c, **TOL[dt])
+        torch.testing.assert_close(z, zz, **TOL[dt])
+        assert (alpha.sum(1) - 1).abs().max().item() < 1e-5
+    # the two kernels agree with each other far inside the oracle tolerance
+    torch.testing.assert_close(out[0][0], out[1][0], rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("B,L,D,H,gate", [(70, 196, 512, 512, 1), (64, 196, 2048, 512, 1), (66, 49, 2048, 768, 0), (65, 197, 512, 768, 1)])
+def test_streaming_bwd_vs_autograd(dt, B, L, D, H, gate):
+    """sat_attn_step_bwd with dpre_out (streaming kernel) vs torch autograd of the same step in fp32."""
+    from sat_b200 import _lib
+    L_ = _lib.lib()
+    P, a, _ = _setup(B, L, D, H, seed=8)
+    g = torch.Generator().manual_seed(17)
+    h = torch.tanh(torch.randn(B, H, generator=g))
+    ad = a.cuda().to(dt).contiguous()
+    af = ad.float().cpu()
+    wa_f = (af @ P["attention.W.weight"].t() + P["attention.W.bias"]).cuda().to(dt).contiguous()
+    uh = (h @ P["attention.U.weight"].t() + P["attention.U.bias"])
+    fb = (h @ P["f_beta.weight"].t() + P["f_beta.bias"])
+    dz = torch.randn(B, D, generator=g)
+    dce = torch.randn(B, D, generator=g) * 0.5
+    ga = torch.randn(B, L, generator=g) * 0.1
+    # autograd reference on the rounded operands
+    wa_r = wa_f.float().cpu().requires_grad_(True)
+    uh_r, fb_r = uh.clone().requires_grad_(True), fb.clone().requires_grad_(True)
+    v_r = P["attention.v.weight"].reshape(-1).clone().requires_grad_(True)
+    bv_r = P["attention.v.bias"].clone().requires_grad_(True)
+    e = torch.tanh(wa_r + uh_r[:, None, :]) @ v_r + bv_r
+    al = torch.softmax(e, 1)
+    c = (af * al[:, :, None]).sum(1)
+    zz = torch.sigmoid(fb_r) * c if gate else c
+    ((zz * dz).sum() + (c * dce).sum() + (al * ga).sum()).backward()
+    # device
+    uf = torch.cat((uh, fb), 1).cuda().contiguous()
+    alpha_d = al.detach().cuda().contiguous()
+    ctx_d = c.detach().cuda().to(dt).contiguous()
+    duf = torch.zeros(B, H + D, device="cuda", dtype=dt)
+    dpre = torch.zeros(B, L, H, device="cuda", dtype=dt)
+    dv = torch.zeros(B, H, device="cuda")
+    dbv = torch.zeros(B, device="cuda")
+    vd = P["attention.v.weight"].reshape(-1).cuda().contiguous()
+    dzd, dced, gad = dz.cuda(), dce.cuda(), ga.cuda()
+    _lib.check(L_.sat_attn_step_bwd(_lib.dtype_code(dt), B, L, D, H, ad.data_ptr(), wa_f.data_ptr(), uf.data_ptr(), H + D, vd.data_ptr(),
+                                    alpha_d.data_ptr(), L, ctx_d.data_ptr(), D, dzd.data_ptr(), D, dced.data_ptr(), D, gad.data_ptr(), L,
+                                    gate, duf.data_ptr(), H + D, None, dv.data_ptr(), dbv.data_ptr(), None, 1, dpre.data_ptr(),
+                                    torch.cuda.current_stream().cuda_stream))
+    torch.cuda.synchronize()
+
+    def close(got, ref, name, rel):
+        scale = ref.abs().max().item() + 1e-12
+        err = (got - ref).abs().max().item()
+        assert err <= rel * scale, (name, err, scale)
+
+    rel = 2e-4 if dt == torch.float32 else 2e-2
+    close(dpre.float().cpu(), wa_r.grad, "dpre", rel)
+    close(duf[:, :H].float().cpu(), uh_r.grad, "dUh", rel)
+    if gate:
+        close(duf[:, H:].float().cpu(), fb_r.grad, "dfb", rel)
+    else:
+        assert duf[:, H:].float().abs().max().item() == 0.0
+    close(dv.sum(0).cpu(), v_r.grad, "dv", rel)
+    assert abs(dbv.sum().item() - bv_r.grad.item()) < 1e-4 * max(1.0, wa_r.grad.abs().sum().item() ** 0.5)

@@ -71,3 +71,31 @@ def test_caption_bf16_runs_and_alphas_normalised():
         if not torch.is_tensor(alpha):
             al = np.array(alpha)[1:]
             assert np.abs(al.sum(1) - 1).max() < 1e-5
+
+
+@pytest.mark.parametrize("beam", [5, 10])
+def test_caption_batch_streaming_kernels_64_images(beam):
+    """NI = 64 images take the streaming attention kernel (rows of an image share the staged features); the tokens must
+    equal the generic-kernel run and, on a sample of images, the oracle's per-image beam search (fp32: bit-exact tokens)."""
+    from sat_b200 import _lib
+    V, D, L, NI = 900, 512, 196, 64
+    P = synth.make_params(V, D, 512, seed=23, emb_scale=0.5)
+    P["deep_output.bias"] = P["deep_output.bias"].clone()
+    P["deep_output.bias"][1] += 0.15
+    a, _ = synth.make_inputs(NI, L, D, 4, V, seed=23)
+    dec = _decoder(dict(V=V, D=D, ado=False, attention=True), P)
+    res = dec.caption_batch(a.cuda(), beam)
+    _lib.lib().sat_set_attn_generic(1)
+    try:
+        res_g = dec.caption_batch(a.cuda(), beam)
+    finally:
+        _lib.lib().sat_set_attn_generic(0)
+    for i in range(NI):
+        assert res[i][0] == res_g[i][0], i
+    with torch.no_grad():
+        for i in (0, 17, 40, 63):
+            sent, alpha, fb = O.caption(P, a[i], beam, ado=False, attention=True)
+            assert res[i][0] == sent, (i, res[i][0], sent)
+            got = res[i][1].cpu().numpy() if fb else np.array(res[i][1], dtype=np.float32)
+            ref = alpha.numpy() if fb else np.array(alpha, dtype=np.float32)
+            np.testing.assert_allclose(got, ref, rtol=2e-4, atol=2e-6)

@@ -56,11 +56,15 @@ CASES = [
     dict(V=777, D=512, B=5, L=49, T=4, tf=False, ado=False, attention=True),
     dict(V=500, D=512, B=4, L=196, T=4, tf=True, ado=False, attention=False),
     dict(V=640, D=512, B=33, L=196, T=5, tf=True, ado=False, attention=True, gate=False),
+    # B >= 64 runs the streaming attention kernels (fwd + bwd with the per-step dpre buffer)
+    dict(V=640, D=512, B=66, L=196, T=4, tf=True, ado=False, attention=True),
+    dict(V=520, D=2048, B=64, L=196, T=3, tf=True, ado=True, attention=True),
+    dict(V=520, D=512, B=65, L=49, T=3, tf=True, ado=False, attention=True, gate=False),
 ]
 
 
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
-@pytest.mark.parametrize("case", CASES, ids=lambda c: "V%d_D%d_tf%d_ado%d_att%d" % (c["V"], c["D"], c["tf"], c["ado"], c["attention"]))
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "V%d_D%d_B%d_tf%d_ado%d_att%d" % (c["V"], c["D"], c["B"], c["tf"], c["ado"], c["attention"]))
 def test_decoder_vs_oracle(case, dt):
     cfg = dict(case)
     cfg.setdefault("gate", True)
