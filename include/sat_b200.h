@@ -26,6 +26,10 @@ int sat_version(void);
 int sat_set_force_simt(int on);
 /* debug knob: 1 = run the attention step on the generic cluster kernels even where the streaming kernels apply */
 int sat_set_attn_generic(int on);
+/* debug knob: work partition of the streaming attention kernels. 0 = auto, 1 = whole items per CTA, 2 = equal slot counts */
+int sat_set_attn_partition(int mode);
+/* tuning knob: bytes of a / Wa per attention launch loaded with the L2 evict_last hint (default 0: everything evict_first) */
+int sat_set_attn_l2_pin_bytes(int64_t bytes);
 
 /* Bench instrumentation: CUDA-event pairs around every attention-step (fwd = category 0, bwd = 1) and GEMM (2) launch,
  * recorded on the launching stream.  sat_profile_read fills ms[3] / counts[3] and resets. */
@@ -43,17 +47,26 @@ int sat_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, int a_k
  * caption).  uf[r] = [U h + b_U (H) | f_beta h + b (D)] fp32.  Outputs alpha fp32, ctx / z (gated ctx) in dtype. */
 int sat_attn_step_fwd(int dtype, int NI, int NB, int L, int D, int H, const void* a, const void* wa, const float* uf,
                       int64_t ld_uf, const float* v, const float* bv, int gate, float* alpha, int64_t ld_alpha,
-                      void* ctx, int64_t ld_ctx, void* z, int64_t ld_z, void* stream);
+                      void* ctx, int64_t ld_ctx, void* z, int64_t ld_z, float* ctx_f32, int64_t ld_c32, void* scratch,
+                      int64_t scratch_bytes, void* stream);
+
+/* Scratch of the streaming attention kernels (persistent CTAs over an equal split of all locations; an image cut by
+ * the split is finished by the last of its CTAs).  0 bytes = this shape runs on the generic cluster kernels, which
+ * need none.  The caller zeroes the buffer once; the kernels leave it zeroed.  Without scratch (NULL) the generic
+ * kernels run.  ctx_f32 (optional, streaming only) receives the fp32 un-gated context the streaming backward needs. */
+int sat_attn_scratch_bytes(int NI, int NB, int L, int D, int H, int64_t* bytes);
 
 /* K2 backward (autograd of the lines above inside loss.backward(), train.py:163).
  * The gradient wrt the hoisted projection Wa is produced in one of two ways: dpre_out != NULL -> this step's
  * dpre (B,L,H) is written once in the compute dtype (streaming kernel; the caller sums the steps afterwards);
- * dpre_out == NULL -> it is accumulated into the fp32 buffer dwa_acc (first != 0 overwrites). */
+ * dpre_out == NULL -> it is accumulated into the fp32 buffer dwa_acc (first != 0 overwrites).  The streaming kernel
+ * also needs ctx_f32 (saved by sat_attn_step_fwd) and the same scratch buffer. */
 int sat_attn_step_bwd(int dtype, int B, int L, int D, int H, const void* a, const void* wa, const float* uf, int64_t ld_uf,
                       const float* v, const float* alpha, int64_t ld_alpha, const void* ctx, int64_t ld_ctx,
                       const float* dz, int64_t ld_dz, const float* dctx_extra, int64_t ld_dce, const float* galpha,
                       int64_t ld_ga, int gate, void* duf, int64_t ld_duf, float* dwa_acc, float* dv_acc, float* dbv_acc,
-                      float* da_acc, int first, void* dpre_out, void* stream);
+                      float* da_acc, int first, void* dpre_out, const float* ctx_f32, int64_t ld_c32, void* scratch,
+                      int64_t scratch_bytes, void* stream);
 
 /* Arguments of the sequence drivers: Decoder.forward (decoder.py:69-135) and its backward.  Parameter pointers are
  * the fp32 tensors of the reference state_dict; NULL where a module does not exist (f_* without ado). */

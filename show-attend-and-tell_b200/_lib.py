@@ -72,7 +72,7 @@ class BeamArgs(C.Structure):
 
 _LIB = None
 
-EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_set_attn_generic", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_bwd",
+EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_set_attn_generic", "sat_set_attn_partition", "sat_set_attn_l2_pin_bytes", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_bwd", "sat_attn_scratch_bytes",
            "sat_decoder_workspace_bytes", "sat_decoder_forward", "sat_decoder_backward", "sat_beam_workspace_bytes",
            "sat_beam_search", "sat_adam_step", "sat_profile", "sat_profile_read"]
 
@@ -90,9 +90,11 @@ def lib():
         L.sat_gemm.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _vp, _i64, C.c_int, _vp, _i64, C.c_int, _vp, C.c_int,
                                _vp, _i64, _vp, _i64, C.c_int, _vp]
         L.sat_attn_step_fwd.argtypes = [C.c_int] * 6 + [_vp, _vp, _vp, _i64, _vp, _vp, C.c_int, _vp, _i64, _vp, _i64,
-                                                        _vp, _i64, _vp]
+                                                        _vp, _i64, _vp, _i64, _vp, _i64, _vp]
+        L.sat_set_attn_l2_pin_bytes.argtypes = [_i64]
+        L.sat_attn_scratch_bytes.argtypes = [C.c_int] * 5 + [C.POINTER(_i64)]
         L.sat_attn_step_bwd.argtypes = ([C.c_int] * 5 + [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp,
-                                                         _i64, _vp, _i64, C.c_int, _vp, _i64, _vp, _vp, _vp, _vp, C.c_int, _vp, _vp])
+                                                         _i64, _vp, _i64, C.c_int, _vp, _i64, _vp, _vp, _vp, _vp, C.c_int, _vp, _vp, _i64, _vp, _i64, _vp])
         L.sat_decoder_workspace_bytes.argtypes = [C.POINTER(DecoderArgs), C.POINTER(_i64)]
         L.sat_decoder_forward.argtypes = [C.POINTER(DecoderArgs)]
         L.sat_decoder_backward.argtypes = [C.POINTER(DecoderArgs), C.POINTER(DecoderGrads)]
@@ -101,6 +103,16 @@ def lib():
         L.sat_adam_step.argtypes = [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, C.c_int, _f32, _vp]
         _LIB = L
     return _LIB
+
+
+def attn_scratch(NI, NB, L, D, H, device):
+    """Scratch tensor for the streaming attention kernels (no initialisation needed), or None when the shape runs on
+    the generic kernels."""
+    n = _i64(0)
+    check(lib().sat_attn_scratch_bytes(NI, NB, L, D, H, C.byref(n)), "sat_attn_scratch_bytes")
+    if n.value == 0:
+        return None
+    return torch.empty(n.value, device=device, dtype=torch.uint8)
 
 
 def check(rc: int, what: str = "sat_b200"):

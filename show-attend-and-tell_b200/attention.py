@@ -43,10 +43,16 @@ class _AttentionFn(torch.autograd.Function):
         alpha = torch.empty(B, Lloc, device=dev, dtype=torch.float32)
         ctxv = torch.empty(B, D, device=dev, dtype=dt)
         vflat = vw.detach().reshape(-1).contiguous()
+        # streaming kernels (scratch + fp32 context for their backward) unless d/d img_features is wanted,
+        # which only the generic backward kernel produces
+        scratch = None if a_in.requires_grad else _lib.attn_scratch(B, 1, Lloc, D, H, dev)
+        ctx32 = torch.empty(B, D, device=dev, dtype=torch.float32) if scratch is not None else None
         _lib.check(L.sat_attn_step_fwd(_lib.dtype_code(dt), B, 1, Lloc, D, H, a.data_ptr(), wa.data_ptr(), uf.data_ptr(), H,
                                        vflat.data_ptr(), vb.detach().data_ptr(), 0, alpha.data_ptr(), Lloc,
-                                       ctxv.data_ptr(), D, None, 0, st), "sat_attn_step_fwd")
+                                       ctxv.data_ptr(), D, None, 0, _lib.ptr(ctx32), D, _lib.ptr(scratch),
+                                       0 if scratch is None else scratch.numel(), st), "sat_attn_step_fwd")
         ctx.saved = (a, h, Wc, Uc, wa, uf, alpha, ctxv, vflat)
+        ctx.stream_state = (scratch, ctx32)
         ctx.module = module
         ctx.a_needs_grad = a_in.requires_grad
         ctx.in_dtypes = (a_in.dtype, h_in.dtype)
@@ -65,17 +71,22 @@ class _AttentionFn(torch.autograd.Function):
         dz = (torch.zeros(B, D, device=dev) if dctx is None else dctx.to(torch.float32)).contiguous()
         ga = None if dalpha is None else dalpha.to(torch.float32).contiguous()
         duf = torch.zeros(B, H + D, device=dev, dtype=dt)
-        dwa = torch.empty(B, Lloc, H, device=dev, dtype=torch.float32)
+        scratch, ctx32 = ctx.stream_state
+        streaming = scratch is not None
+        dwa = torch.empty(B, Lloc, H, device=dev, dtype=dt if streaming else torch.float32)
         dv = torch.empty(B, H, device=dev, dtype=torch.float32)
         dbv = torch.empty(B, device=dev, dtype=torch.float32)
         da = torch.empty(B, Lloc, D, device=dev, dtype=torch.float32) if ctx.a_needs_grad else None
         _lib.check(L.sat_attn_step_bwd(_lib.dtype_code(dt), B, Lloc, D, H, a.data_ptr(), wa.data_ptr(), uf.data_ptr(), H,
                                        vflat.data_ptr(), alpha.data_ptr(), Lloc, ctxv.data_ptr(), D, dz.data_ptr(), D,
                                        None, 0, None if ga is None else ga.data_ptr(), Lloc, 0, duf.data_ptr(), H + D,
-                                       dwa.data_ptr(), dv.data_ptr(), dbv.data_ptr(), None if da is None else da.data_ptr(),
-                                       1, None, st), "sat_attn_step_bwd")
+                                       None if streaming else dwa.data_ptr(), dv.data_ptr(), dbv.data_ptr(),
+                                       None if da is None else da.data_ptr(), 1, dwa.data_ptr() if streaming else None,
+                                       _lib.ptr(ctx32), D, _lib.ptr(scratch), 0 if scratch is None else scratch.numel(), st),
+                   "sat_attn_step_bwd")
         dUh = duf[:, :H].contiguous()
         dwa_t = dwa.reshape(B * Lloc, H).to(dt)
+        dwa = dwa.float()
         gUw = torch.empty(H, H, device=dev, dtype=torch.float32)
         _gemm(dt, H, H, B, dUh, H, False, h, H, False, Cf=gUw, ldcf=H, stream=st)                 # dU = dUh^T h
         gWw = torch.empty(H, D, device=dev, dtype=torch.float32)

@@ -39,6 +39,10 @@ struct FwdParams {
     int NI, NB, L, D, H;
     int gate;             // apply sigmoid gate
     int C, Lc, Ds, G;
+    // streaming kernels only (sat_attn_stream.cuh)
+    float* ctx32;         // fp32 (NR, ld_c32) un-gated context saved for the backward pass, or null
+    int64_t ld_c32;
+    float* s_part;        // cross-CTA partial records (scratch)
 };
 
 struct SmemLayout {
@@ -315,6 +319,11 @@ struct BwdParams {
     float* dbv_acc;         // (B)   fp32
     float* da_acc;          // (B, L, D) fp32 or null
     void* dpre_out;         // T (B, L, H): this step's dpre written once (streaming kernel); null -> accumulate into dwa_acc
+    const float* ctx32;     // streaming kernel: fp32 (B, ld_c32) un-gated context saved by the forward kernel
+    int64_t ld_c32;
+    float* s_part;          // streaming kernel scratch (see FwdParams)
+    float* s_dctx;          // streaming kernel scratch: (B, D) fp32 gated upstream gradient (when !dz_is_dctx)
+    int dz_is_dctx;         // streaming kernel: dz already holds dctx = dz*gate + extra and d f_beta is already written
     int first;              // first backward step: overwrite the accumulators
     int B, L, D, H, gate;
     int C, Lc, Ds, Hs, G2;

@@ -5,6 +5,8 @@
 
 int g_force_simt = 0;
 int g_attn_generic = 0;
+int g_attn_part = 0;
+long long g_attn_pin_bytes = 0;
 static thread_local char g_err[1024] = "";
 
 void sat_set_error(const char* fmt, ...) {
@@ -60,6 +62,8 @@ const char* sat_last_error(void) { return g_err; }
 int sat_version(void) { return 100; }
 int sat_set_force_simt(int on) { g_force_simt = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_generic(int on) { g_attn_generic = on ? 1 : 0; return SAT_OK; }
+int sat_set_attn_l2_pin_bytes(int64_t bytes) { g_attn_pin_bytes = bytes > 0 ? bytes : 0; return SAT_OK; }
+int sat_set_attn_partition(int mode) { g_attn_part = (mode == 1 || mode == 2) ? mode : 0; return SAT_OK; }
 
 /* profiling: sat_profile(1) starts recording CUDA-event pairs around attention-step and GEMM launches on their own
  * stream; sat_profile_read() synchronises and returns per-category total ms and launch counts, then resets. */
@@ -97,13 +101,18 @@ int sat_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, int a_k
 
 int sat_attn_step_fwd(int dtype, int NI, int NB, int L, int D, int H, const void* a, const void* wa, const float* uf,
                       int64_t ld_uf, const float* v, const float* bv, int gate, float* alpha, int64_t ld_alpha,
-                      void* ctx, int64_t ld_ctx, void* z, int64_t ld_z, void* stream) {
+                      void* ctx, int64_t ld_ctx, void* z, int64_t ld_z, float* ctx_f32, int64_t ld_c32, void* scratch,
+                      int64_t scratch_bytes, void* stream) {
     SAT_TRY(require_sm100());
     attn::FwdParams p;
     memset(&p, 0, sizeof(p));
     p.a = a; p.wa = wa; p.uf = uf; p.ld_uf = ld_uf; p.v = v; p.bv = bv; p.alpha = alpha; p.ld_alpha = ld_alpha;
     p.ctx = ctx; p.ld_ctx = ld_ctx; p.z = z; p.ld_z = ld_z;
     p.NI = NI; p.NB = NB; p.L = L; p.D = D; p.H = H; p.gate = gate;
+    p.ctx32 = ctx_f32; p.ld_c32 = ld_c32;
+    if (scratch && attn_s::fwd_shape_ok(NB, L, D, H) && scratch_bytes >= attn_s::scratch_bytes(NI, NB, D, H)) {
+        p.s_part = reinterpret_cast<float*>(scratch);
+    }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (dtype == SAT_DTYPE_F32) return attn_step_fwd<float, true>(p, st);
     if (dtype == SAT_DTYPE_BF16) return attn_step_fwd<bf16, false>(p, st);
@@ -115,7 +124,8 @@ int sat_attn_step_bwd(int dtype, int B, int L, int D, int H, const void* a, cons
                       const float* v, const float* alpha, int64_t ld_alpha, const void* ctx, int64_t ld_ctx,
                       const float* dz, int64_t ld_dz, const float* dctx_extra, int64_t ld_dce, const float* galpha,
                       int64_t ld_ga, int gate, void* duf, int64_t ld_duf, float* dwa_acc, float* dv_acc, float* dbv_acc,
-                      float* da_acc, int first, void* dpre_out, void* stream) {
+                      float* da_acc, int first, void* dpre_out, const float* ctx_f32, int64_t ld_c32, void* scratch,
+                      int64_t scratch_bytes, void* stream) {
     SAT_TRY(require_sm100());
     attn::BwdParams p;
     memset(&p, 0, sizeof(p));
@@ -124,11 +134,23 @@ int sat_attn_step_bwd(int dtype, int B, int L, int D, int H, const void* a, cons
     p.galpha = galpha; p.ld_ga = ld_ga; p.duf = duf; p.ld_duf = ld_duf; p.dwa_acc = dwa_acc; p.dv_acc = dv_acc;
     p.dbv_acc = dbv_acc; p.da_acc = da_acc; p.first = first; p.dpre_out = dpre_out;
     p.B = B; p.L = L; p.D = D; p.H = H; p.gate = gate;
+    p.ctx32 = ctx_f32; p.ld_c32 = ld_c32;
+    if (scratch && attn_s::shape_ok(L, D, H) && scratch_bytes >= attn_s::scratch_bytes(B, 1, D, H)) {
+        p.s_part = reinterpret_cast<float*>(scratch);
+        p.s_dctx = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(scratch) + attn_s::scratch_rec_bytes(1, D, H));
+    }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     if (dtype == SAT_DTYPE_F32) return attn_step_bwd<float, true>(p, st);
     if (dtype == SAT_DTYPE_BF16) return attn_step_bwd<bf16, false>(p, st);
     sat_set_error("bad dtype %d", dtype);
     return SAT_ERR_ARG;
+}
+
+int sat_attn_scratch_bytes(int NI, int NB, int L, int D, int H, int64_t* bytes) {
+    SAT_REQUIRE(bytes != nullptr, "null out pointer");
+    SAT_TRY(require_sm100());
+    *bytes = attn_s::fwd_shape_ok(NB, L, D, H) ? attn_s::scratch_bytes(NI, NB, D, H) : 0;
+    return SAT_OK;
 }
 
 int sat_decoder_workspace_bytes(const sat_decoder_args* args, int64_t* bytes) {

@@ -221,6 +221,8 @@ struct BeamWs {
     T *P1, *P2, *Comb;
     float* logits; // (R, V)
     float* alpha_hist;   // (S, R, L)
+    uint8_t* attn_scratch;
+    bool attn_stream;
     float* top_preds;
     int64_t* prev_word;
     int *live, *done, *n_active, *parent, *cand_word, *cand_parent, *slot_cand, *comp_step, *comp_cand, *ncomp, *last_step, *last_n;
@@ -261,6 +263,8 @@ int64_t beam_carve(const sat_beam_args& a, BeamWs<T>& w, uint8_t* base) {
     TK(X, R * (2 * H + D), T); TK(Hn, R * H, T); TK(Cc, R * H, float); TK(Cn, R * H, float); TK(UF, R * (H + D), float);
     TK(Ctx, R * D, T); TK(P1, a.ado ? R * H : 0, T); TK(P2, a.ado ? R * H : 0, T); TK(Comb, a.ado ? R * H : 0, T);
     TK(logits, R * V, float); TK(alpha_hist, a.attention ? S * R * L : 0, float);
+    w.attn_stream = a.attention && attn_s::fwd_shape_ok(a.beam, a.L, a.D, a.H);
+    TK(attn_scratch, w.attn_stream ? attn_s::scratch_bytes(a.NI, a.beam, a.D, a.H) : 0, uint8_t);
     TK(top_preds, R, float); TK(prev_word, R, int64_t);
     TK(live, NI, int); TK(done, NI, int); TK(n_active, 1, int); TK(parent, R, int);
     TK(cand_word, S * R, int); TK(cand_parent, S * R, int); TK(slot_cand, S * R, int);
@@ -343,6 +347,9 @@ int beam_search_t(const sat_beam_args& a) {
             p.alpha = w.alpha_hist + (size_t)step * R * L; p.ld_alpha = L;
             p.ctx = w.Ctx; p.ld_ctx = D; p.z = w.X + H; p.ld_z = xw;
             p.NI = NI; p.NB = NB; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
+            if (w.attn_stream) {
+                p.s_part = reinterpret_cast<float*>(w.attn_scratch);
+            }
             SAT_TRY((attn_step_fwd<T, PRECISE>(p, st)));
         }
         EpiLstm<T, PRECISE> e;

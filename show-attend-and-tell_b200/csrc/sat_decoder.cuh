@@ -71,7 +71,10 @@ struct DecWs {
     float *dh_carry, *dc_carry;
     float* dwa_acc;  // (B,L,H)      generic attention backward: fp32 accumulator over time
     T* dpre_all;     // (T,B,L,H)    streaming attention backward: each step's dpre written once
-    bool bwd_stream;
+    float* Ctx32;    // (T,B,D)      fp32 un-gated context saved by the streaming forward kernel for its backward
+    uint8_t* attn_scratch;   // streaming attention kernels: arrival counters + partial records
+    int64_t attn_scratch_bytes;
+    bool attn_stream;
     T* dwa_t;        // (B,L,H)
     float *dv_acc, *dbv_acc;
     T* dE;           // (T,B,H)
@@ -107,6 +110,10 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
     TK(a_c, a_alias ? 0 : B * L * D, T);
     if (a_alias) w.a_c = reinterpret_cast<T*>(const_cast<void*>(a.img_features));
     TK(wa, a.attention ? B * L * H : 0, T);
+    w.attn_stream = a.attention && attn_s::fwd_shape_ok(1, a.L, a.D, a.H);
+    w.attn_scratch_bytes = w.attn_stream ? attn_s::scratch_bytes(a.B, 1, a.D, a.H) : 0;
+    TK(attn_scratch, w.attn_scratch_bytes, uint8_t);
+    TK(Ctx32, (w.attn_stream && a.need_grad) ? B * Tn * D : 0, float);
     TK(abar, B * D, T); TK(abar_f, B * D, float);
     TK(E, B * Tn * H, T); TK(Xg, B * Tn * 4 * H, float); TK(UF, B * Tn * (H + D), float);
     TK(ZH, B * (Tn + 1) * (D + H), T); TK(Cst, B * (Tn + 1) * H, float);
@@ -117,9 +124,8 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
     if (a.need_grad) {
         TK(dlog, B * Tn * w.Vp, T); TK(dHd, B * Tn * H, float); TK(dG, B * Tn * 4 * H, T); TK(dZH, B * (D + H), float);
         TK(dUF, B * Tn * (H + D), T); TK(dh_carry, B * H, float); TK(dc_carry, B * H, float);
-        w.bwd_stream = a.attention && attn_s::bwd_shape_eligible<T>(a.B, a.L, a.D, a.H);
-        TK(dwa_acc, (a.attention && !w.bwd_stream) ? B * L * H : 0, float); TK(dwa_t, a.attention ? B * L * H : 0, T);
-        TK(dpre_all, w.bwd_stream ? Tn * B * L * H : 0, T);
+        TK(dwa_acc, (a.attention && !w.attn_stream) ? B * L * H : 0, float); TK(dwa_t, a.attention ? B * L * H : 0, T);
+        TK(dpre_all, w.attn_stream ? Tn * B * L * H : 0, T);
         TK(dv_acc, B * H, float); TK(dbv_acc, B, float);
         TK(dE, B * Tn * H, T); TK(dpre0, B * 2 * H, T); TK(galpha, B * Tn * L, float);
         int64_t gs = 4 * H * (D + H);
@@ -281,6 +287,10 @@ int decoder_forward_t(const sat_decoder_args& a) {
             p.ctx = w.Ctx + (size_t)t * B * D; p.ld_ctx = D;
             p.z = zh_t; p.ld_z = zw;
             p.NI = B; p.NB = 1; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
+            if (w.attn_stream) {
+                if (a.need_grad) { p.ctx32 = w.Ctx32 + (size_t)t * B * D; p.ld_c32 = D; }
+                p.s_part = reinterpret_cast<float*>(w.attn_scratch);
+            }
             SAT_TRY((attn_step_fwd<T, PRECISE>(p, st)));
         }
         // K3: gates = Xg[t] + [z | h] [W_ih[:,H:] | W_hh]^T, LSTM cell in the epilogue (decoder.py:108-115)
@@ -404,7 +414,12 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
             p.galpha = galpha ? galpha + (size_t)t * L : nullptr; p.ld_ga = (int64_t)Tn * L;
             p.duf = w.dUF + (size_t)t * B * (H + D); p.ld_duf = H + D;
             p.dwa_acc = w.dwa_acc; p.dv_acc = w.dv_acc; p.dbv_acc = w.dbv_acc; p.da_acc = nullptr;
-            p.dpre_out = w.bwd_stream ? w.dpre_all + (size_t)t * B * L * H : nullptr;
+            if (w.attn_stream) {
+                p.dpre_out = w.dpre_all + (size_t)t * B * L * H;
+                p.ctx32 = w.Ctx32 + (size_t)t * B * D; p.ld_c32 = D;
+                p.s_part = reinterpret_cast<float*>(w.attn_scratch);
+                p.s_dctx = reinterpret_cast<float*>(w.attn_scratch + attn_s::scratch_rec_bytes(1, D, H));
+            }
             p.first = (t == Tn - 1);
             p.B = B; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
             SAT_TRY((attn_step_bwd<T, PRECISE>(p, st)));
@@ -463,14 +478,14 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         if (g.att_U_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
         if (g.f_beta_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_b, w.gscratch + H, (size_t)D * 4, cudaMemcpyDeviceToDevice, st));
         // encoder projection: dW (H x D) = (sum_t dpre)^T a ; db_W = colsum ; dv, db_v
-        if (w.bwd_stream) SAT_TRY(misc::sum_over_t<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L * H, Tn));
+        if (w.attn_stream) SAT_TRY(misc::sum_over_t<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L * H, Tn));
         else SAT_TRY((misc::cast<float, T>(st, w.dwa_t, w.dwa_acc, (int64_t)B * L * H)));
         if (g.att_W_w) {
             auto e2 = lin<T>(H, D, nullptr, SAT_ACT_NONE, g.att_W_w, D, nullptr, 0);
             SAT_TRY(gemm<T>(st, w.dwa_t, H, false, w.a_c, D, false, H, D, B * L, e2));
         }
         if (g.att_W_b) {
-            if (w.bwd_stream) SAT_TRY(misc::colsum<T>(st, w.dwa_t, H, B * L, H, g.att_W_b, w.csum, w.csum_floats));
+            if (w.attn_stream) SAT_TRY(misc::colsum<T>(st, w.dwa_t, H, B * L, H, g.att_W_b, w.csum, w.csum_floats));
             else SAT_TRY(misc::colsum<float>(st, w.dwa_acc, H, B * L, H, g.att_W_b, w.csum, w.csum_floats));
         }
         if (g.att_v_w) SAT_TRY(misc::colsum<float>(st, w.dv_acc, H, B, H, g.att_v_w, w.csum, w.csum_floats));

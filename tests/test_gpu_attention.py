@@ -74,7 +74,7 @@ def test_attn_step_shared_features_rows(dt, NB):
     bv = P["attention.v.bias"].cuda()
     _lib.check(L_.sat_attn_step_fwd(_lib.dtype_code(dt), NI, NB, L, D, H, ad.data_ptr(), Wad.data_ptr(), uf.data_ptr(), H + D,
                                     v.data_ptr(), bv.data_ptr(), 1, alpha.data_ptr(), L, ctx.data_ptr(), D, z.data_ptr(), D,
-                                    torch.cuda.current_stream().cuda_stream))
+                                    None, 0, None, 0, torch.cuda.current_stream().cuda_stream))
     torch.cuda.synchronize()
     Wa_used = Wad.float().cpu()
     for r in range(NI * NB):
@@ -100,7 +100,8 @@ def _ref_step(P, a_used, wa_used, uh, fb, gate=True):
 
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
 @pytest.mark.parametrize("NI,NB,L,D,H", [(70, 1, 196, 512, 512), (64, 1, 196, 2048, 512), (66, 1, 49, 2048, 768), (65, 1, 197, 512, 768),
-                                         (64, 5, 196, 512, 512), (33, 3, 196, 512, 512), (16, 10, 196, 512, 512)])
+                                         (64, 5, 196, 512, 512), (33, 3, 196, 512, 512), (16, 10, 196, 512, 512),
+                                         (1, 1, 196, 2048, 512), (3, 1, 5, 512, 512), (7, 5, 196, 512, 768), (300, 1, 196, 512, 512)])
 def test_streaming_fwd_vs_oracle_and_generic(dt, NI, NB, L, D, H):
     from sat_b200 import _lib
     L_ = _lib.lib()
@@ -117,35 +118,47 @@ def test_streaming_fwd_vs_oracle_and_generic(dt, NI, NB, L, D, H):
     v = P["attention.v.weight"].reshape(-1).cuda().contiguous()
     bv = P["attention.v.bias"].cuda()
     out = {}
-    for mode in (0, 1):
+    scratch = _lib.attn_scratch(NI, NB, L, D, H, "cuda")
+    assert scratch is not None                      # these shapes are served by the streaming kernels
+    scratch.fill_(0xFF)                             # the scratch needs no initialisation (NaN bit patterns here)
+    # mode 1 / 2: streaming kernels with whole-item / equal-slot-count partition (cut items + combine kernel); 0: generic
+    for mode in (1, 2, 0):
         alpha = torch.zeros(R, L, device="cuda")
         ctx = torch.zeros(R, D, device="cuda", dtype=dt)
         z = torch.zeros(R, D, device="cuda", dtype=dt)
-        L_.sat_set_attn_generic(mode)
+        c32 = torch.zeros(R, D, device="cuda")
+        extra = (c32.data_ptr(), D, scratch.data_ptr(), scratch.numel()) if mode else (None, 0, None, 0)
+        L_.sat_set_attn_partition(mode)
         try:
-            _lib.check(L_.sat_attn_step_fwd(_lib.dtype_code(dt), NI, NB, L, D, H, ad.data_ptr(), Wad.data_ptr(), uf.data_ptr(), H + D,
-                                            v.data_ptr(), bv.data_ptr(), 1, alpha.data_ptr(), L, ctx.data_ptr(), D, z.data_ptr(), D,
-                                            torch.cuda.current_stream().cuda_stream))
-            torch.cuda.synchronize()
+            for rep in range(2 if mode else 1):     # twice: a launch must not depend on what the previous one left behind
+                _lib.check(L_.sat_attn_step_fwd(_lib.dtype_code(dt), NI, NB, L, D, H, ad.data_ptr(), Wad.data_ptr(), uf.data_ptr(), H + D,
+                                                v.data_ptr(), bv.data_ptr(), 1, alpha.data_ptr(), L, ctx.data_ptr(), D, z.data_ptr(), D,
+                                                *extra, torch.cuda.current_stream().cuda_stream))
+                torch.cuda.synchronize()
         finally:
-            L_.sat_set_attn_generic(0)
+            L_.sat_set_attn_partition(0)
+        if mode:
+            torch.testing.assert_close(c32.cpu(), ctx.float().cpu(), **TOL[dt])
         out[mode] = (alpha.cpu(), ctx.float().cpu(), z.float().cpu())
     rows = torch.arange(R) // NB
     al, c, zz = _ref_step(P, af[rows], Wad.float().cpu()[rows], uh, fb)
     ta = dict(rtol=2e-4, atol=1e-6) if dt == torch.float32 else dict(rtol=5e-2, atol=2e-3)
-    for mode in (0, 1):
+    for mode in (0, 1, 2):
         alpha, ctx, z = out[mode]
         torch.testing.assert_close(alpha, al, **ta)
         torch.testing.assert_close(ctx, c, **TOL[dt])
         torch.testing.assert_close(z, zz, **TOL[dt])
         assert (alpha.sum(1) - 1).abs().max().item() < 1e-5
-    # the two kernels agree with each other far inside the oracle tolerance
+    # the kernels agree with each other far inside the oracle tolerance
     torch.testing.assert_close(out[0][0], out[1][0], rtol=1e-5, atol=1e-7)
+    torch.testing.assert_close(out[2][0], out[1][0], rtol=1e-5, atol=1e-7)
 
 
+@pytest.mark.parametrize("part", [1, 2], ids=["whole", "cut"])
 @pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
-@pytest.mark.parametrize("B,L,D,H,gate", [(70, 196, 512, 512, 1), (64, 196, 2048, 512, 1), (66, 49, 2048, 768, 0), (65, 197, 512, 768, 1)])
-def test_streaming_bwd_vs_autograd(dt, B, L, D, H, gate):
+@pytest.mark.parametrize("B,L,D,H,gate", [(70, 196, 512, 512, 1), (64, 196, 2048, 512, 1), (66, 49, 2048, 768, 0), (65, 197, 512, 768, 1),
+                                          (1, 196, 2048, 512, 1), (3, 5, 512, 512, 1), (200, 196, 512, 512, 1)])
+def test_streaming_bwd_vs_autograd(dt, B, L, D, H, gate, part):
     """sat_attn_step_bwd with dpre_out (streaming kernel) vs torch autograd of the same step in fp32."""
     from sat_b200 import _lib
     L_ = _lib.lib()
@@ -174,17 +187,25 @@ def test_streaming_bwd_vs_autograd(dt, B, L, D, H, gate):
     uf = torch.cat((uh, fb), 1).cuda().contiguous()
     alpha_d = al.detach().cuda().contiguous()
     ctx_d = c.detach().cuda().to(dt).contiguous()
+    c32 = c.detach().cuda().contiguous()
+    scratch = _lib.attn_scratch(B, 1, L, D, H, "cuda")
+    assert scratch is not None
+    scratch.fill_(0xFF)                             # no initialisation needed
     duf = torch.zeros(B, H + D, device="cuda", dtype=dt)
     dpre = torch.zeros(B, L, H, device="cuda", dtype=dt)
     dv = torch.zeros(B, H, device="cuda")
     dbv = torch.zeros(B, device="cuda")
     vd = P["attention.v.weight"].reshape(-1).cuda().contiguous()
     dzd, dced, gad = dz.cuda(), dce.cuda(), ga.cuda()
-    _lib.check(L_.sat_attn_step_bwd(_lib.dtype_code(dt), B, L, D, H, ad.data_ptr(), wa_f.data_ptr(), uf.data_ptr(), H + D, vd.data_ptr(),
-                                    alpha_d.data_ptr(), L, ctx_d.data_ptr(), D, dzd.data_ptr(), D, dced.data_ptr(), D, gad.data_ptr(), L,
-                                    gate, duf.data_ptr(), H + D, None, dv.data_ptr(), dbv.data_ptr(), None, 1, dpre.data_ptr(),
-                                    torch.cuda.current_stream().cuda_stream))
-    torch.cuda.synchronize()
+    L_.sat_set_attn_partition(part)
+    try:
+        _lib.check(L_.sat_attn_step_bwd(_lib.dtype_code(dt), B, L, D, H, ad.data_ptr(), wa_f.data_ptr(), uf.data_ptr(), H + D, vd.data_ptr(),
+                                        alpha_d.data_ptr(), L, ctx_d.data_ptr(), D, dzd.data_ptr(), D, dced.data_ptr(), D, gad.data_ptr(), L,
+                                        gate, duf.data_ptr(), H + D, None, dv.data_ptr(), dbv.data_ptr(), None, 1, dpre.data_ptr(),
+                                        c32.data_ptr(), D, scratch.data_ptr(), scratch.numel(), torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+    finally:
+        L_.sat_set_attn_partition(0)
 
     def close(got, ref, name, rel):
         scale = ref.abs().max().item() + 1e-12
