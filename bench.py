@@ -257,7 +257,7 @@ def run_ours(args, rank, world, local_rank):
     s = 2  # bf16
     Lc, D, H = CFG["L"], CFG["D"], CFG["H"]
     bytes_fwd = B * Lc * (H + D) * s
-    bytes_bwd = B * (Lc * (H + D) * s + 2 * Lc * H * 4)
+    bytes_bwd = B * (Lc * (H + D) * s + Lc * H * s)      # a, Wa read once + this step's dpre written once
     peak, peak_src = read_peaks()
     kern = {}
     for name, idx, nbytes in (("attn_step_fwd", 0, bytes_fwd), ("attn_step_bwd", 1, bytes_bwd)):

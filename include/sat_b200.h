@@ -28,6 +28,9 @@ int sat_set_force_simt(int on);
 int sat_set_attn_generic(int on);
 /* debug knob: work partition of the streaming attention kernels. 0 = auto, 1 = whole items per CTA, 2 = equal slot counts */
 int sat_set_attn_partition(int mode);
+/* debug knob: 1 (default) = PDL-aware kernels are launched with programmatic stream serialization (their prologue overlaps
+ * the previous kernel's tail), 0 = ordinary launches */
+int sat_set_pdl(int on);
 /* tuning knob: bytes of a / Wa per attention launch loaded with the L2 evict_last hint (default 0: everything evict_first) */
 int sat_set_attn_l2_pin_bytes(int64_t bytes);
 

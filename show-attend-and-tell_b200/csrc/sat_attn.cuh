@@ -43,6 +43,8 @@ struct FwdParams {
     float* ctx32;         // fp32 (NR, ld_c32) un-gated context saved for the backward pass, or null
     int64_t ld_c32;
     float* s_part;        // cross-CTA partial records (scratch)
+    int static_inputs;    // a / wa were NOT written by the kernel launched just before this one: the producers may
+                          // start streaming them before the programmatic-dependent-launch wait
 };
 
 struct SmemLayout {
@@ -324,6 +326,7 @@ struct BwdParams {
     float* s_part;          // streaming kernel scratch (see FwdParams)
     float* s_dctx;          // streaming kernel scratch: (B, D) fp32 gated upstream gradient (when !dz_is_dctx)
     int dz_is_dctx;         // streaming kernel: dz already holds dctx = dz*gate + extra and d f_beta is already written
+    int static_inputs;      // see FwdParams
     int first;              // first backward step: overwrite the accumulators
     int B, L, D, H, gate;
     int C, Lc, Ds, Hs, G2;

@@ -111,7 +111,7 @@ inline Smem make_smem(int slot_bytes, size_t red_bytes, size_t es_bytes, size_t 
 // one producer and one consumer, neither of which can run a whole phase ahead of the barrier it waits on (the parity wait
 // would otherwise pass on stale data).
 template <typename T, int D, int H, typename SideFn>
-__device__ __forceinline__ void produce(int pidx, const void* wa, const void* a, int L, int ngroups, long long q0, long long q1, int pin, int spi,
+__device__ __forceinline__ void produce(int pidx, bool static_inputs, const void* wa, const void* a, int L, int ngroups, long long q0, long long q1, int pin, int spi,
                                         uint8_t* ring, uint64_t* full, uint64_t* empty, int nslots, uint64_t* sfull,
                                         uint64_t* sempty, SideFn side) {
     using G = Geo<T, D, H>;
@@ -143,8 +143,19 @@ __device__ __forceinline__ void produce(int pidx, const void* wa, const void* a,
         }
     };
     (void)item0;
-    for (long long q = q0 + pidx; q < q1; q += PWARPS) {
-        if (pidx == 0) side_upto(q);
+    // Programmatic dependent launch: this kernel may have started while the previous one is still running.  The side
+    // blocks are the previous kernel's output and must wait for it; a / wa are older when the caller says so, and then
+    // the first ring-full of slots is requested right away (producer 0: as many slots as it can issue without needing a
+    // consumer, then the wait, then the side blocks the consumers are blocked on).
+    bool waited = !static_inputs;
+    if (!static_inputs) pdl_wait();
+    const int prefill = (int)((endc - basec) >> 3) + (int)((endn - basen) >> 3);
+    int issued = 0;
+    for (long long q = q0 + pidx; q < q1; q += PWARPS, ++issued) {
+        if (pidx == 0 && (waited || issued >= prefill)) {
+            if (!waited) { pdl_wait(); waited = true; }
+            side_upto(q);
+        }
         const uint32_t rr = rc;
         mbar_wait(&empty[rr], phc ^ 1);
         const int l0 = k * LS, nloc = min(LS, L - l0);
@@ -159,7 +170,10 @@ __device__ __forceinline__ void produce(int pidx, const void* wa, const void* a,
         k += PWARPS;
         while (k >= spi) { k -= spi; if (++grp == ngroups) { grp = 0; ++img; } }
     }
-    if (pidx == 0) side_upto(q1 - 1);
+    if (pidx == 0) {
+        if (!waited) pdl_wait();
+        side_upto(q1 - 1);
+    }
 }
 
 // ---- items cut by the partition ----------------------------------------------------------------------------------
@@ -250,6 +264,8 @@ fwd_stream_kernel(FwdParams p, Smem sl, Part pt, int ngroups) {
 
     if (warp < CWARPS) {
         reg_inc<REGS_CONSUMER>();
+        pdl_wait();                                   // everything this kernel reads besides a / wa, and all it writes
+        if (tid == 0) pdl_launch_dependents();
 
         float vreg[HPL * VEC];
 #pragma unroll
@@ -478,7 +494,7 @@ fwd_stream_kernel(FwdParams p, Smem sl, Part pt, int ngroups) {
                     bulk_g2s(side + (size_t)sb * SIDE_F + (size_t)nb * (H + D), p.uf + row * p.ld_uf, (uint32_t)((H + D) * 4), bar);
                 }
             };
-            produce<T, D, H>(warp - CWARPS, p.wa, p.a, L, ngroups, q0, q1, pt.pin, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
+            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, ngroups, q0, q1, pt.pin, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
         }
     }
 }
@@ -607,6 +623,8 @@ bwd_stream_kernel(BwdParams p, Smem sl, Part pt) {
 
     if (warp < CWARPS) {
         reg_inc<REGS_CONSUMER>();
+        pdl_wait();                                   // everything this kernel reads besides a / wa, and all it writes
+        if (tid == 0) pdl_launch_dependents();
 
         float vreg[HPL * VEC];
 #pragma unroll
@@ -800,7 +818,7 @@ bwd_stream_kernel(BwdParams p, Smem sl, Part pt) {
                 bulk_g2s(dst + D, p.ctx32 + b * p.ld_c32, (uint32_t)(D * 4), bar);
                 bulk_g2s(dst + 2 * D, p.uf + b * p.ld_uf, (uint32_t)(H * 4), bar);
             };
-            produce<T, D, H>(warp - CWARPS, p.wa, p.a, L, 1, q0, q1, pt.pin, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
+            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, 1, q0, q1, pt.pin, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
         }
     }
 }
@@ -910,8 +928,10 @@ int launch_fwd_inst(const FwdParams& p, cudaStream_t stream) {
     int grid = 1;
     const Part pt = pick_part((long long)p.NI * ngroups, spi, G::SLOT, ngroups, &grid);
     SatProfScope prof(SAT_PROF_ATTN_FWD, stream);
-    kern<<<grid, THREADS, sl.total, stream>>>(p, sl, pt, ngroups);
-    SAT_CHECK_CUDA(cudaGetLastError());
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    pdl_config(&cfg, attr, dim3(grid), dim3(THREADS), sl.total, stream);
+    SAT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, p, sl, pt, ngroups));
     if (pt.align == 1 && grid > 1) {
         fwd_combine_kernel<T, D, H, NBG, PRECISE><<<grid - 1, 256, 0, stream>>>(p, pt, grid, ngroups);
         SAT_CHECK_CUDA(cudaGetLastError());
@@ -966,8 +986,10 @@ int launch_bwd_inst(const BwdParams& p_in, cudaStream_t stream) {
     const int spi = (p.L + G::LS - 1) / G::LS;
     int grid = 1;
     const Part pt = pick_part(p.B, spi, G::SLOT, 1, &grid);
-    kern<<<grid, THREADS, sl.total, stream>>>(p, sl, pt);
-    SAT_CHECK_CUDA(cudaGetLastError());
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    pdl_config(&cfg, attr, dim3(grid), dim3(THREADS), sl.total, stream);
+    SAT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, p, sl, pt));
     if (pt.align == 1 && grid > 1) {
         bwd_combine_kernel<T, D, H><<<grid - 1, 256, 0, stream>>>(p, pt, grid);
         SAT_CHECK_CUDA(cudaGetLastError());

@@ -7,6 +7,7 @@ int g_force_simt = 0;
 int g_attn_generic = 0;
 int g_attn_part = 0;
 long long g_attn_pin_bytes = 0;
+int g_pdl = 1;
 static thread_local char g_err[1024] = "";
 
 void sat_set_error(const char* fmt, ...) {
@@ -63,6 +64,7 @@ int sat_version(void) { return 100; }
 int sat_set_force_simt(int on) { g_force_simt = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_generic(int on) { g_attn_generic = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_l2_pin_bytes(int64_t bytes) { g_attn_pin_bytes = bytes > 0 ? bytes : 0; return SAT_OK; }
+int sat_set_pdl(int on) { g_pdl = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_partition(int mode) { g_attn_part = (mode == 1 || mode == 2) ? mode : 0; return SAT_OK; }
 
 /* profiling: sat_profile(1) starts recording CUDA-event pairs around attention-step and GEMM launches on their own

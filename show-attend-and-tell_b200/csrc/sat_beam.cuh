@@ -349,6 +349,7 @@ int beam_search_t(const sat_beam_args& a) {
             p.NI = NI; p.NB = NB; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
             if (w.attn_stream) {
                 p.s_part = reinterpret_cast<float*>(w.attn_scratch);
+                p.static_inputs = 1;
             }
             SAT_TRY((attn_step_fwd<T, PRECISE>(p, st)));
         }

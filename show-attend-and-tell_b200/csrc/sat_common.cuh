@@ -196,6 +196,20 @@ __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
 
+// Programmatic dependent launch (PDL).  A kernel launched through pdl_config() may start while its predecessor in the
+// stream is still running; it must execute pdl_wait() before its first access to global memory the predecessor (or any
+// earlier kernel) wrote or still reads.  Both instructions are no-ops in a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+extern int g_pdl;              // sat_set_pdl: 1 (default) = launch PDL-aware kernels with programmatic stream serialization
+inline void pdl_config(cudaLaunchConfig_t* cfg, cudaLaunchAttribute* attr, dim3 grid, dim3 block, size_t smem, cudaStream_t stream) {
+    memset(cfg, 0, sizeof(*cfg));
+    cfg->gridDim = grid; cfg->blockDim = block; cfg->dynamicSmemBytes = smem; cfg->stream = stream;
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = g_pdl ? 1 : 0;
+    cfg->attrs = attr; cfg->numAttrs = 1;
+}
+
 // clusters / DSMEM
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r;

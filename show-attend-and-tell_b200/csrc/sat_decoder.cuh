@@ -61,6 +61,7 @@ struct DecWs {
     T *P1, *P2, *Comb;   // ado (T,B,H)
     int64_t* tok_in; // (T,B) token fed to each step (free-running mode)
     float* rowloss;  // (B*T)
+    float* loss_part; // (2 * LOSS_PARTS) partial sums of the loss reduction
     float* logits_tmp;   // (B,T,V) when preds == NULL
     // backward
     T* dlog;         // (T,B,Vp)
@@ -119,7 +120,7 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
     TK(ZH, B * (Tn + 1) * (D + H), T); TK(Cst, B * (Tn + 1) * H, float);
     TK(Gates, B * Tn * 4 * H, T); TK(Ctx, B * Tn * D, T); TK(Hdrop, B * Tn * H, T); TK(hc0, B * 2 * H, float);
     TK(P1, a.ado ? B * Tn * H : 0, T); TK(P2, a.ado ? B * Tn * H : 0, T); TK(Comb, a.ado ? B * Tn * H : 0, T);
-    TK(tok_in, B * Tn, int64_t); TK(rowloss, B * Tn, float);
+    TK(tok_in, B * Tn, int64_t); TK(rowloss, B * Tn, float); TK(loss_part, 2 * misc::LOSS_PARTS, float);
     TK(logits_tmp, a.preds ? 0 : B * Tn * V, float);
     if (a.need_grad) {
         TK(dlog, B * Tn * w.Vp, T); TK(dHd, B * Tn * H, float); TK(dG, B * Tn * 4 * H, T); TK(dZH, B * (D + H), float);
@@ -289,6 +290,7 @@ int decoder_forward_t(const sat_decoder_args& a) {
             p.NI = B; p.NB = 1; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
             if (w.attn_stream) {
                 if (a.need_grad) { p.ctx32 = w.Ctx32 + (size_t)t * B * D; p.ld_c32 = D; }
+                p.static_inputs = 1;         // a_c / wa were written before the loop
                 p.s_part = reinterpret_cast<float*>(w.attn_scratch);
             }
             SAT_TRY((attn_step_fwd<T, PRECISE>(p, st)));
@@ -318,7 +320,8 @@ int decoder_forward_t(const sat_decoder_args& a) {
         SAT_REQUIRE(a.loss != nullptr, "fused_loss needs a loss output");
         const float* logits = a.preds ? a.preds : w.logits_tmp;
         misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, V, V, Tn, a.captions, a.cap_stride, w.rowloss, (T*)nullptr, 0, nullptr, 1.0f);
-        misc::loss_finalize_kernel<<<1, 1024, 0, st>>>(w.rowloss, B * Tn, B * (Tn - 1), a.alphas, B, Tn, L, a.alpha_c, a.loss);
+        misc::loss_partial_kernel<<<misc::LOSS_PARTS, 256, 0, st>>>(w.rowloss, B * Tn, a.alphas, B, Tn, L, w.loss_part);
+        misc::loss_finalize_kernel<<<1, 256, 0, st>>>(w.loss_part, misc::LOSS_PARTS, B * (Tn - 1), a.alphas != nullptr, B, L, a.alpha_c, a.loss);
         SAT_CHECK_CUDA(cudaGetLastError());
     }
     return SAT_OK;
@@ -392,14 +395,24 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     SAT_CHECK_CUDA(cudaMemsetAsync(w.dh_carry, 0, (size_t)B * H * 4, st));
     SAT_CHECK_CUDA(cudaMemsetAsync(w.dc_carry, 0, (size_t)B * H * 4, st));
     for (int t = Tn - 1; t >= 0; --t) {
+        // (the cell backward stays a kernel of its own: fused into the 16-CTA dh GEMM below it ran 3x slower)
         dim3 lg(sat_cdiv(H, 128), B);
         misc::lstm_bwd_kernel<T><<<lg, 128, 0, st>>>(
             w.Gates + (size_t)t * B * 4 * H, 4 * H, w.Cst + (size_t)t * B * H, H, w.Cst + (size_t)(t + 1) * B * H, H,
             w.dHd + (size_t)t * B * H, H, a.dropout_mask ? a.dropout_mask + (size_t)t * H : nullptr, (int64_t)Tn * H,
             w.dh_carry, w.dc_carry, w.dG + (size_t)t * B * 4 * H, 4 * H, B, H);
         SAT_CHECK_CUDA(cudaGetLastError());
-        // d[z | h_prev] = dG [W_ih[:,H:] | W_hh]
-        {
+        // d[z | h_prev] = dG [W_ih[:,H:] | W_hh]   (streaming attention: with the context gate's backward in the epilogue)
+        if (a.attention && w.attn_stream) {
+            EpiDzGate<T, PRECISE> e;
+            e.out = w.dZH; e.ld_out = zw;
+            e.uf = w.UF + (size_t)t * B * (H + D); e.ld_uf = H + D;
+            e.ctx32 = w.Ctx32 + (size_t)t * B * D; e.ld_c32 = D;
+            e.extra = a.ado ? w.dctx_all + (size_t)t * B * D : nullptr; e.ld_ex = D;
+            e.duf = w.dUF + (size_t)t * B * (H + D); e.ld_duf = H + D;
+            e.M = B; e.D = D; e.H = H; e.gate = a.gate;
+            SAT_TRY(gemm<T>(st, w.dG + (size_t)t * B * 4 * H, 4 * H, true, w.w_gzh, zw, false, B, D + H, 4 * H, e));
+        } else {
             auto e = lin<T>(B, D + H, nullptr, SAT_ACT_NONE, w.dZH, zw, nullptr, 0);
             SAT_TRY(gemm<T>(st, w.dG + (size_t)t * B * 4 * H, 4 * H, true, w.w_gzh, zw, false, B, D + H, 4 * H, e));
         }
@@ -418,7 +431,8 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
                 p.dpre_out = w.dpre_all + (size_t)t * B * L * H;
                 p.ctx32 = w.Ctx32 + (size_t)t * B * D; p.ld_c32 = D;
                 p.s_part = reinterpret_cast<float*>(w.attn_scratch);
-                p.s_dctx = reinterpret_cast<float*>(w.attn_scratch + attn_s::scratch_rec_bytes(1, D, H));
+                p.dz_is_dctx = 1;            // EpiDzGate above already turned dz into dctx and wrote d f_beta
+                p.static_inputs = 1;
             }
             p.first = (t == Tn - 1);
             p.B = B; p.L = L; p.D = D; p.H = H; p.gate = a.gate;

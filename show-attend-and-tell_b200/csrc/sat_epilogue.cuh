@@ -75,6 +75,55 @@ struct EpiLinear {
     }
 };
 
+// Epilogue of the BPTT GEMM  d[z | h_prev] = dG [W_ih[:, H:] | W_hh]  with the backward of the context gate
+// (decoder.py:99-100: z = sigmoid(f_beta h) * ctx) fused in, so no separate kernel runs between this GEMM and the
+// attention backward:
+//   columns n <  D:  dz  ->  dctx = dz * g (+ extra), stored fp32 where dz would have gone;
+//                            d(f_beta pre-activation) = dz * ctx * g (1 - g)  ->  duf[:, H + n]       (g = sigmoid(pre))
+//   columns n >= D:  d h_prev, stored as is.
+template <typename T, bool PRECISE>
+struct EpiDzGate {
+    float* out;              // fp32 [M, ld_out], D + H columns
+    int64_t ld_out;
+    const float* uf;         // fp32 [M, ld_uf] = [U h | f_beta h] pre-activations of this step (gate at column H + n)
+    int64_t ld_uf;
+    const float* ctx32;      // fp32 [M, ld_c32] un-gated context saved by the forward attention kernel
+    int64_t ld_c32;
+    const float* extra;      // optional fp32 [M, ld_ex]: gradient reaching the UN-gated context (ado, decoder.py:120)
+    int64_t ld_ex;
+    T* duf;                  // [M, ld_duf]: d[U h | f_beta h]; this epilogue writes columns H .. H + D
+    int64_t ld_duf;
+    int M, D, H, gate;
+
+    template <int NV>
+    __device__ __forceinline__ void apply(int m, int n0, const float* acc) const {
+        if (m >= M) return;
+#pragma unroll
+        for (int q = 0; q < NV / 4; ++q) {
+            const int n = n0 + 4 * q;
+            if (n >= D + H) return;
+            float v[4] = {acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]};
+            if (n < D) {
+                float dfb[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+                if (gate) {
+                    const float4 gp = *reinterpret_cast<const float4*>(uf + (int64_t)m * ld_uf + H + n);
+                    const float4 cx = *reinterpret_cast<const float4*>(ctx32 + (int64_t)m * ld_c32 + n);
+                    const float g[4] = {sat_sigmoid<PRECISE>(gp.x), sat_sigmoid<PRECISE>(gp.y), sat_sigmoid<PRECISE>(gp.z), sat_sigmoid<PRECISE>(gp.w)};
+                    const float c[4] = {cx.x, cx.y, cx.z, cx.w};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) { dfb[i] = v[i] * c[i] * g[i] * (1.0f - g[i]); v[i] *= g[i]; }
+                }
+                store4<T>(duf + (int64_t)m * ld_duf + H + n, dfb);
+                if (extra) {
+                    const float4 e = *reinterpret_cast<const float4*>(extra + (int64_t)m * ld_ex + n);
+                    v[0] += e.x; v[1] += e.y; v[2] += e.z; v[3] += e.w;
+                }
+            }
+            *reinterpret_cast<float4*>(out + (int64_t)m * ld_out + n) = make_float4(v[0], v[1], v[2], v[3]);
+        }
+    }
+};
+
 // LSTM cell epilogue (a7: decoder.py:115 nn.LSTMCell).  The gate GEMM's N axis is gate-interleaved:
 // column n = 4*j + g with g in (i,f,g,o) for hidden unit j, so one group of 4 columns is one unit.
 template <typename T, bool PRECISE>
@@ -96,32 +145,66 @@ struct EpiLstm {
     int64_t ld_g;
     int M, H;
 
+    // one hidden unit: 4 gate pre-activations -> (c, h, activated gates)
+    __device__ __forceinline__ void cell(float* p, float cp, float& c, float& h) const {
+        p[0] = sat_sigmoid<true>(p[0]);
+        p[1] = sat_sigmoid<true>(p[1]);
+        p[2] = sat_tanh<true>(p[2]);
+        p[3] = sat_sigmoid<true>(p[3]);
+        c = p[1] * cp + p[0] * p[2];
+        h = p[3] * sat_tanh<true>(c);
+    }
+
     template <int NV>
     __device__ __forceinline__ void apply(int m, int n0, const float* acc) const {
         if (m >= M) return;
+        if constexpr (NV >= 16) {
+            // the tensor-core GEMM hands one thread NV consecutive columns of ONE row = NV/4 consecutive units: work on
+            // groups of 4 units so that every global access is a 16-byte (fp32) or 8-byte (bf16) vector
 #pragma unroll
-        for (int q = 0; q < NV / 4; ++q) {
-            const int n = n0 + 4 * q;
-            const int j = n >> 2;
-            if (j >= H) return;
-            float p[4] = {acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]};
-            if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + (int64_t)m * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
-            if (bias) { float4 x = *reinterpret_cast<const float4*>(bias + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
-            const float gi = sat_sigmoid<true>(p[0]);
-            const float gf = sat_sigmoid<true>(p[1]);
-            const float gg = sat_tanh<true>(p[2]);
-            const float go = sat_sigmoid<true>(p[3]);
-            const float c = gf * c_prev[(int64_t)m * ld_cp + j] + gi * gg;
-            const float h = go * sat_tanh<true>(c);
-            c_out[(int64_t)m * ld_co + j] = c;
-            if (h_next) h_next[(int64_t)m * ld_hn + j] = from_f32<T>(h);
-            if (h_out) {
-                const float mk = mask ? mask[(int64_t)m * ld_mask + j] : 1.0f;
-                h_out[(int64_t)m * ld_ho + j] = from_f32<T>(h * mk);
+            for (int u0 = 0; u0 < NV / 4; u0 += 4) {
+                const int j0 = (n0 >> 2) + u0;
+                if (j0 >= H) return;
+                const float4 cp4 = *reinterpret_cast<const float4*>(c_prev + (int64_t)m * ld_cp + j0);
+                const float cp[4] = {cp4.x, cp4.y, cp4.z, cp4.w};
+                float c[4], h[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int n = n0 + 4 * (u0 + u);
+                    float p[4] = {acc[4 * (u0 + u)], acc[4 * (u0 + u) + 1], acc[4 * (u0 + u) + 2], acc[4 * (u0 + u) + 3]};
+                    if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + (int64_t)m * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+                    if (bias) { float4 x = *reinterpret_cast<const float4*>(bias + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+                    cell(p, cp[u], c[u], h[u]);
+                    if (gates) store4<T>(gates + (int64_t)m * ld_g + n, p);
+                }
+                *reinterpret_cast<float4*>(c_out + (int64_t)m * ld_co + j0) = make_float4(c[0], c[1], c[2], c[3]);
+                if (h_next) store4<T>(h_next + (int64_t)m * ld_hn + j0, h);
+                if (h_out) {
+                    if (mask) {
+                        const float4 mk = *reinterpret_cast<const float4*>(mask + (int64_t)m * ld_mask + j0);
+                        h[0] *= mk.x; h[1] *= mk.y; h[2] *= mk.z; h[3] *= mk.w;
+                    }
+                    store4<T>(h_out + (int64_t)m * ld_ho + j0, h);
+                }
             }
-            if (gates) {
-                T* g = gates + (int64_t)m * ld_g + n;
-                g[0] = from_f32<T>(gi); g[1] = from_f32<T>(gf); g[2] = from_f32<T>(gg); g[3] = from_f32<T>(go);
+        } else {
+#pragma unroll
+            for (int q = 0; q < NV / 4; ++q) {
+                const int n = n0 + 4 * q;
+                const int j = n >> 2;
+                if (j >= H) return;
+                float p[4] = {acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]};
+                if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + (int64_t)m * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+                if (bias) { float4 x = *reinterpret_cast<const float4*>(bias + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+                float c, h;
+                cell(p, c_prev[(int64_t)m * ld_cp + j], c, h);
+                c_out[(int64_t)m * ld_co + j] = c;
+                if (h_next) h_next[(int64_t)m * ld_hn + j] = from_f32<T>(h);
+                if (h_out) {
+                    const float mk = mask ? mask[(int64_t)m * ld_mask + j] : 1.0f;
+                    h_out[(int64_t)m * ld_ho + j] = from_f32<T>(h * mk);
+                }
+                if (gates) store4<T>(gates + (int64_t)m * ld_g + n, p);
             }
         }
     }

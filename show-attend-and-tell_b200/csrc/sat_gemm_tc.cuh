@@ -11,10 +11,17 @@
 
 namespace tc {
 constexpr int BM = 128, BK = 64, UMMA_K = 16;
-constexpr int THREADS = 192;   // warp0 = TMA producer, warp1 = TMEM alloc + MMA issuer, warps 2-5 = epilogue
+#ifndef SAT_GEMM_NPROD
+#define SAT_GEMM_NPROD 2
+#endif
+// One thread can start a TMA copy only every ~60 ns and a wait -> expect_tx -> copy round costs ~250-300 ns (measured,
+// tools/tma_bw.cu), which bounds a skinny GEMM's k-loop; so NPROD producer lanes take the k-blocks round-robin.
+constexpr int NPROD = SAT_GEMM_NPROD;
+// warp0 = TMA producer 0, warp1 = TMEM alloc + MMA issuer, warps 2-5 = epilogue, warps 6.. = further TMA producers
+constexpr int THREADS = 192 + 32 * (NPROD - 1);
 
 template <int BN> struct Cfg {
-    static constexpr int STAGES = (BN <= 64) ? 6 : (BN == 128 ? 5 : 4);
+    static constexpr int STAGES = (BN <= 128) ? 6 : 4;      // multiple of NPROD: a stage always has the same producer
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
@@ -91,10 +98,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) overlapped the previous
+    // kernel's tail; its results are needed from here on.  Let the next kernel start its own prologue right away.
+    pdl_wait();
+    pdl_launch_dependents();
 
-    if (warp == 0) {
+    static_assert(C::STAGES % NPROD == 0, "a stage must always be filled by the same producer");
+    if (warp == 0 || warp >= 6) {
         if (elect_one()) {
-            for (int kb = 0; kb < nk; ++kb) {
+            for (int kb = (warp == 0 ? 0 : warp - 5); kb < nk; kb += NPROD) {
                 const int s = kb % C::STAGES;
                 const uint32_t ph = (kb / C::STAGES) & 1;
                 mbar_wait(&empty_bar[s], ph ^ 1);
@@ -204,21 +216,37 @@ int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB,
         configured = true;
     }
     dim3 grid(sat_cdiv(N, BN), sat_cdiv(M, BM));
-    kern<<<grid, THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(mA, mB, M, N, K, epi);
-    SAT_CHECK_CUDA(cudaGetLastError());
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    pdl_config(&cfg, attr, grid, dim3(THREADS), Cfg<BN>::SMEM_BYTES, stream);
+    SAT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, M, N, K, epi));
     return SAT_OK;
 }
 
-inline int pick_bn(int M, int N, bool b_mn) {
-    const int mt = sat_cdiv(M, BM);
+// N-tile width.  Measured on B200 (tools/gemm_bench.cu): a launch costs ~4.3 us however small it is and every k-block adds
+// ~0.155 us per 20 KB stage in every wave of CTAs -- so the model is  waves x (fixed + k-blocks x stage bytes), which
+// keeps the per-step skinny GEMMs (M = batch) in ONE wave of <= #SMs CTAs; ties go to the wider tile (less A re-reading).
+inline int pick_bn(int M, int N, int K, bool b_mn) {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 148;
+    }
+    const int mt = sat_cdiv(M, BM), nk = sat_cdiv(K, BK);
     const int cands[4] = {256, 128, 64, 32};
+    int best = b_mn ? 64 : 32;
+    double best_cost = 1e30;
     for (int i = 0; i < 4; ++i) {
         const int bn = cands[i];
-        if (b_mn && bn < 64) break;
+        if (b_mn && bn < 64) continue;
         if (bn > 32 && bn / 2 >= N && !(b_mn && bn == 64)) continue;   // tile far wider than N
-        if (mt * sat_cdiv(N, bn) >= 120) return bn;
+        const long long tiles = (long long)mt * sat_cdiv(N, bn);
+        const double waves = (double)((tiles + sms - 1) / sms);
+        const double stage_kb = 16.0 + bn / 8.0;
+        const double cost = waves * (28.0 * 20.0 + nk * stage_kb);
+        if (cost < best_cost * 0.999) { best_cost = cost; best = bn; }
     }
-    return b_mn ? 64 : 32;
+    return best;
 }
 
 template <bool A_MN, bool B_MN, typename Epi>
@@ -247,7 +275,7 @@ int launch(cudaStream_t stream, const bf16* A, int64_t lda, bool a_kmajor, const
            int M, int N, int K, const Epi& epi, int bn_override = 0) {
     if (M <= 0 || N <= 0) return SAT_OK;
     SAT_REQUIRE(K > 0, "tcgen05 GEMM needs K > 0");
-    const int bn = bn_override ? bn_override : pick_bn(M, N, !b_kmajor);
+    const int bn = bn_override ? bn_override : pick_bn(M, N, K, !b_kmajor);
     if (a_kmajor && b_kmajor) return launch_mn<false, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
     if (a_kmajor && !b_kmajor) return launch_mn<false, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
     if (!a_kmajor && b_kmajor) return launch_mn<true, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);

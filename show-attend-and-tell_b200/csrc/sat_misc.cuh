@@ -362,33 +362,46 @@ __global__ void ce_rows_kernel(const float* __restrict__ logits, int64_t ld, int
     }
 }
 
-// loss[0] = ce mean, loss[1] = alpha_c * mean_{b,l} (1 - sum_t alpha)^2, loss[2] = total   (single block)
-__global__ void loss_finalize_kernel(const float* __restrict__ rowloss, int rows, int n_active, const float* __restrict__ alphas,
-                                     int B, int Tn, int L, float alpha_c, float* __restrict__ loss) {
+// loss[0] = ce mean, loss[1] = alpha_c * mean_{b,l} (1 - sum_t alpha)^2, loss[2] = total  (train.py:150-162).
+// Two deterministic stages: LOSS_PARTS blocks each reduce a strided share of the CE rows and of the (b, l) columns into
+// part[2 * block .. ], one block adds the partials up.
+constexpr int LOSS_PARTS = 256;
+__device__ __forceinline__ void block_sum2(float& x, float& y, float (*red)[32]) {
+    x = warp_sum(x); y = warp_sum(y);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = x; red[1][threadIdx.x >> 5] = y; }
+    __syncthreads();
+    const int nw = blockDim.x >> 5;
+    x = (int)threadIdx.x < nw ? red[0][threadIdx.x] : 0.0f;
+    y = (int)threadIdx.x < nw ? red[1][threadIdx.x] : 0.0f;
+    if (threadIdx.x < 32) { x = warp_sum(x); y = warp_sum(y); }
+}
+__global__ void loss_partial_kernel(const float* __restrict__ rowloss, int rows, const float* __restrict__ alphas, int B, int Tn, int L,
+                                    float* __restrict__ part) {
     __shared__ float red[2][32];
     float ce = 0.0f, reg = 0.0f;
-    for (int i = threadIdx.x; i < rows; i += blockDim.x) ce += rowloss[i];
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsz = gridDim.x * blockDim.x;
+    for (int i = gtid; i < rows; i += gsz) ce += rowloss[i];
     if (alphas) {
-        for (int i = threadIdx.x; i < B * L; i += blockDim.x) {
+        for (int i = gtid; i < B * L; i += gsz) {
             const int b = i / L, l = i - b * L;
             float s = 0.0f;
             for (int t = 0; t < Tn; ++t) s += alphas[((size_t)b * Tn + t) * L + l];
             reg += (1.0f - s) * (1.0f - s);
         }
     }
-    ce = warp_sum(ce); reg = warp_sum(reg);
-    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = ce; red[1][threadIdx.x >> 5] = reg; }
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        const int nw = blockDim.x >> 5;
-        ce = threadIdx.x < nw ? red[0][threadIdx.x] : 0.0f;
-        reg = threadIdx.x < nw ? red[1][threadIdx.x] : 0.0f;
-        ce = warp_sum(ce); reg = warp_sum(reg);
-        if (threadIdx.x == 0) {
-            loss[0] = n_active > 0 ? ce / (float)n_active : 0.0f;
-            loss[1] = alphas ? alpha_c * reg / (float)(B * L) : 0.0f;
-            loss[2] = loss[0] + loss[1];
-        }
+    block_sum2(ce, reg, red);
+    if (threadIdx.x == 0) { part[2 * blockIdx.x] = ce; part[2 * blockIdx.x + 1] = reg; }
+}
+__global__ void loss_finalize_kernel(const float* __restrict__ part, int nparts, int n_active, int has_alphas, int B, int L,
+                                     float alpha_c, float* __restrict__ loss) {
+    __shared__ float red[2][32];
+    float ce = 0.0f, reg = 0.0f;
+    for (int i = threadIdx.x; i < nparts; i += blockDim.x) { ce += part[2 * i]; reg += part[2 * i + 1]; }
+    block_sum2(ce, reg, red);
+    if (threadIdx.x == 0) {
+        loss[0] = n_active > 0 ? ce / (float)n_active : 0.0f;
+        loss[1] = has_alphas ? alpha_c * reg / (float)(B * L) : 0.0f;
+        loss[2] = loss[0] + loss[1];
     }
 }
 

@@ -95,6 +95,18 @@ class FusedTrainStep:
         a.stream = torch.cuda.current_stream(dev).cuda_stream
         return a
 
+    def sync_grads(self):
+        """The one exchange step of data-parallel training: sum the flat gradient buffer over the ranks (NCCL over
+        NVLink on GPUs).  The 1/world of the mean is folded into the Adam kernel (grad_scale)."""
+        if self.world > 1:
+            dist.all_reduce(self.flat_grad, group=self.pg)
+
+    def layout_signature(self):
+        """(key, offset, numel) of every trainable tensor in the flat buffers; must be identical on all ranks."""
+        base = self.flat_param.data_ptr()
+        named = dict(self.dec.named_parameters())
+        return [(k, (named[k].data_ptr() - base) // 4, named[k].numel()) for k in self.train_keys]
+
     def step(self, img_features, captions, dropout_mask=None, optimizer_step=True):
         """One training step; returns the device tensor [ce, alpha_reg, total] (no host sync)."""
         dec = self.dec
@@ -110,8 +122,7 @@ class FusedTrainStep:
             v = self.grad_views.get(_lib.PARAM_KEYS[field])
             setattr(g, field, None if v is None else v.data_ptr())
         _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(g)), "sat_decoder_backward")
-        if self.world > 1:
-            dist.all_reduce(self.flat_grad, group=self.pg)                  # NCCL sum over NVLink
+        self.sync_grads()
         if optimizer_step:
             self.step_count += 1
             _lib.check(L.sat_adam_step(self.flat_param.data_ptr(), self.flat_grad.data_ptr(), self.exp_avg.data_ptr(),

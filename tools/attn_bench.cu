@@ -10,6 +10,7 @@
 int g_attn_generic = 0;
 int g_attn_part = 0;
 long long g_attn_pin_bytes = 0;
+int g_pdl = 1;
 void sat_set_error(const char* fmt, ...) { va_list ap; va_start(ap, fmt); vfprintf(stderr, fmt, ap); va_end(ap); fprintf(stderr, "\n"); }
 SatProfScope::SatProfScope(int c, cudaStream_t s) : cat(c), st(s), slot(-1) {}
 SatProfScope::~SatProfScope() {}
@@ -52,6 +53,8 @@ __global__ void checksum_bf16(const bf16* x, size_t n, double* out) {
 int main(int argc, char** argv) {
     if (getenv("SAT_PART")) g_attn_part = atoi(getenv("SAT_PART"));
     if (getenv("SAT_PIN_MB")) g_attn_pin_bytes = (long long)atoi(getenv("SAT_PIN_MB")) << 20;
+    if (getenv("SAT_PDL")) g_pdl = atoi(getenv("SAT_PDL"));
+    const int static_in = getenv("SAT_STATIC") ? atoi(getenv("SAT_STATIC")) : 1;
     const int sameset = getenv("SAT_SAMESET") ? atoi(getenv("SAT_SAMESET")) : 0;      // 1: every launch reads the same inputs
     const int B = argc > 1 ? atoi(argv[1]) : 256, iters = argc > 2 ? atoi(argv[2]) : 20;
     const int L = 196, D = 2048, H = 512;
@@ -77,7 +80,7 @@ int main(int argc, char** argv) {
         attn::FwdParams p; memset(&p, 0, sizeof(p));
         p.a = a[s]; p.wa = wa[s]; p.uf = uf; p.ld_uf = H + D; p.v = v; p.bv = bv; p.alpha = alpha; p.ld_alpha = L;
         p.ctx = ctx; p.ld_ctx = D; p.z = z; p.ld_z = D; p.NI = B; p.NB = 1; p.L = L; p.D = D; p.H = H; p.gate = 1;
-        p.ctx32 = ctx32; p.ld_c32 = D; p.s_part = (float*)scratch;
+        p.ctx32 = ctx32; p.ld_c32 = D; p.s_part = (float*)scratch; p.static_inputs = static_in;
         if (attn_s::launch_fwd<bf16, false>(p, 0) != 0) exit(2);
     };
     auto bwd = [&](int s) {
@@ -85,7 +88,7 @@ int main(int argc, char** argv) {
         p.a = a[s]; p.wa = wa[s]; p.uf = uf; p.ld_uf = H + D; p.v = v; p.alpha = alpha; p.ld_alpha = L; p.ctx = ctx; p.ld_ctx = D;
         p.dz = dz; p.ld_dz = D; p.galpha = galpha; p.ld_ga = L; p.duf = duf; p.ld_duf = H + D; p.dv_acc = dv; p.dbv_acc = dbv;
         p.first = 1; p.B = B; p.L = L; p.D = D; p.H = H; p.gate = 1; p.dpre_out = dpre; p.ctx32 = ctx32; p.ld_c32 = D;
-        p.s_part = (float*)scratch; p.dz_is_dctx = 1;
+        p.s_part = (float*)scratch; p.dz_is_dctx = 1; p.static_inputs = static_in;
         if (attn_s::launch_bwd<bf16, false>(p, 0) != 0) exit(2);
     };
     cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
