@@ -396,12 +396,17 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     SAT_CHECK_CUDA(cudaMemsetAsync(w.dc_carry, 0, (size_t)B * H * 4, st));
     for (int t = Tn - 1; t >= 0; --t) {
         // (the cell backward stays a kernel of its own: fused into the 16-CTA dh GEMM below it ran 3x slower)
-        dim3 lg(sat_cdiv(H, 128), B);
-        misc::lstm_bwd_kernel<T><<<lg, 128, 0, st>>>(
-            w.Gates + (size_t)t * B * 4 * H, 4 * H, w.Cst + (size_t)t * B * H, H, w.Cst + (size_t)(t + 1) * B * H, H,
-            w.dHd + (size_t)t * B * H, H, a.dropout_mask ? a.dropout_mask + (size_t)t * H : nullptr, (int64_t)Tn * H,
-            w.dh_carry, w.dc_carry, w.dG + (size_t)t * B * 4 * H, 4 * H, B, H);
-        SAT_CHECK_CUDA(cudaGetLastError());
+        {
+            cudaLaunchConfig_t cfg;
+            cudaLaunchAttribute attr[1];
+            pdl_config(&cfg, attr, dim3(sat_cdiv(H, 128), B), dim3(128), 0, st);
+            SAT_CHECK_CUDA(cudaLaunchKernelEx(
+                &cfg, misc::lstm_bwd_kernel<T>, (const T*)(w.Gates + (size_t)t * B * 4 * H), (int64_t)(4 * H),
+                (const float*)(w.Cst + (size_t)t * B * H), (int64_t)H, (const float*)(w.Cst + (size_t)(t + 1) * B * H), (int64_t)H,
+                (const float*)(w.dHd + (size_t)t * B * H), (int64_t)H,
+                (const float*)(a.dropout_mask ? a.dropout_mask + (size_t)t * H : nullptr), (int64_t)Tn * H,
+                (const float*)w.dh_carry, w.dc_carry, w.dG + (size_t)t * B * 4 * H, (int64_t)(4 * H), B, H));
+        }
         // d[z | h_prev] = dG [W_ih[:,H:] | W_hh]   (streaming attention: with the context gate's backward in the epilogue)
         if (a.attention && w.attn_stream) {
             EpiDzGate<T, PRECISE> e;

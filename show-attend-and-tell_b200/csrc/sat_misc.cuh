@@ -203,6 +203,8 @@ __global__ void lstm_bwd_kernel(const T* __restrict__ gates, int64_t ld_g, const
                                 const float* __restrict__ mask, int64_t ld_mask, const float* __restrict__ dh_carry,
                                 float* __restrict__ dc_carry, T* __restrict__ dG, int64_t ld_dg, int B, int H) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    pdl_wait();                       // dh_carry comes from the GEMM launched just before
+    pdl_launch_dependents();
     if (j >= H) return;
     const T* g = gates + (int64_t)b * ld_g + 4 * j;
     const float gi = to_f32<T>(g[0]), gf = to_f32<T>(g[1]), gg = to_f32<T>(g[2]), go = to_f32<T>(g[3]);
