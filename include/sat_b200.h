@@ -31,8 +31,12 @@ int sat_set_attn_partition(int mode);
 /* debug knob: 1 (default) = PDL-aware kernels are launched with programmatic stream serialization (their prologue overlaps
  * the previous kernel's tail), 0 = ordinary launches */
 int sat_set_pdl(int on);
-/* tuning knob: bytes of a / Wa per attention launch loaded with the L2 evict_last hint (default 0: everything evict_first) */
-int sat_set_attn_l2_pin_bytes(int64_t bytes);
+/* tuning knob: L2 eviction hints of the streaming attention kernels' loads.  wa_fwd / wa_bwd: policy of the Wa rows in the
+ * forward / backward kernel (0 = evict_first like the feature rows, 1 = evict_last, 2 = evict_normal); pin_bytes: additionally
+ * load this many bytes of a + Wa per launch (a prefix of every item) with evict_last.  Default (1, 0, 0): the 51 MB of Wa stay
+ * in the 126 MB L2 from one forward step to the next (measured -13% on the forward kernel at c2; the backward kernel is
+ * fastest with everything evict_first). */
+int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes);
 
 /* Bench instrumentation: CUDA-event pairs around every attention-step (fwd = category 0, bwd = 1) and GEMM (2) launch,
  * recorded on the launching stream.  sat_profile_read fills ms[3] / counts[3] and resets. */

@@ -72,7 +72,7 @@ class BeamArgs(C.Structure):
 
 _LIB = None
 
-EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_set_attn_generic", "sat_set_attn_partition", "sat_set_pdl", "sat_set_attn_l2_pin_bytes", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_bwd", "sat_attn_scratch_bytes",
+EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_set_attn_generic", "sat_set_attn_partition", "sat_set_pdl", "sat_set_attn_l2_policy", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_bwd", "sat_attn_scratch_bytes",
            "sat_decoder_workspace_bytes", "sat_decoder_forward", "sat_decoder_backward", "sat_beam_workspace_bytes",
            "sat_beam_search", "sat_adam_step", "sat_profile", "sat_profile_read"]
 
@@ -91,7 +91,7 @@ def lib():
                                _vp, _i64, _vp, _i64, C.c_int, _vp]
         L.sat_attn_step_fwd.argtypes = [C.c_int] * 6 + [_vp, _vp, _vp, _i64, _vp, _vp, C.c_int, _vp, _i64, _vp, _i64,
                                                         _vp, _i64, _vp, _i64, _vp, _i64, _vp]
-        L.sat_set_attn_l2_pin_bytes.argtypes = [_i64]
+        L.sat_set_attn_l2_policy.argtypes = [C.c_int, C.c_int, _i64]
         L.sat_attn_scratch_bytes.argtypes = [C.c_int] * 5 + [C.POINTER(_i64)]
         L.sat_attn_step_bwd.argtypes = ([C.c_int] * 5 + [_vp, _vp, _vp, _i64, _vp, _vp, _i64, _vp, _i64, _vp, _i64, _vp,
                                                          _i64, _vp, _i64, C.c_int, _vp, _i64, _vp, _vp, _vp, _vp, C.c_int, _vp, _vp, _i64, _vp, _i64, _vp])

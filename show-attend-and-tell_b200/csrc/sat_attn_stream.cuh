@@ -22,6 +22,7 @@
 #include "sat_attn.cuh"
 
 extern int g_attn_generic;     // debug knob (sat_set_attn_generic): 1 = always use the generic cluster kernels
+extern int g_attn_wa_hint_fwd, g_attn_wa_hint_bwd;   // L2 policy of the Wa rows, see Part
 extern long long g_attn_pin_bytes;   // bytes of a / Wa per launch loaded with the L2 evict_last hint
 extern int g_attn_part;        // debug knob (sat_set_attn_partition): 0 = auto, 1 = whole items, 2 = equal slot counts
 
@@ -63,7 +64,8 @@ __device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterp
 // (align = 1: equal slot counts, items may be cut;  align = slots per item: whole items only)
 // the first `pin` slots of every item are loaded with the L2 evict_last hint (kept for the next step's kernels, which
 // read the same a / Wa), the rest with evict_first -- the same fraction of every CTA's range whatever the partition
-struct Part { long long tot; int align; int pin; };
+// wa_hint: L2 policy of the Wa rows (0 = like the rest of the slot, 1 = evict_last, 2 = evict_normal)
+struct Part { long long tot; int align; int pin; int wa_hint; };
 __host__ __device__ __forceinline__ long long pstart(const Part& pt, int G, int i) { return (pt.tot / pt.align) * i / G * pt.align; }
 __device__ __forceinline__ int cta_of(const Part& pt, int G, long long slot) {
     int i = (int)(slot * G / pt.tot);
@@ -111,7 +113,7 @@ inline Smem make_smem(int slot_bytes, size_t red_bytes, size_t es_bytes, size_t 
 // one producer and one consumer, neither of which can run a whole phase ahead of the barrier it waits on (the parity wait
 // would otherwise pass on stale data).
 template <typename T, int D, int H, typename SideFn>
-__device__ __forceinline__ void produce(int pidx, bool static_inputs, const void* wa, const void* a, int L, int ngroups, long long q0, long long q1, int pin, int spi,
+__device__ __forceinline__ void produce(int pidx, bool static_inputs, const void* wa, const void* a, int L, int ngroups, long long q0, long long q1, int pin, int wa_hint, int spi,
                                         uint8_t* ring, uint64_t* full, uint64_t* empty, int nslots, uint64_t* sfull,
                                         uint64_t* sempty, SideFn side) {
     using G = Geo<T, D, H>;
@@ -162,7 +164,8 @@ __device__ __forceinline__ void produce(int pidx, bool static_inputs, const void
         uint8_t* dst = ring + (size_t)rr * G::SLOT;
         mbar_expect_tx(&full[rr], (uint32_t)(nloc * G::ROWB));
         const uint64_t pol = k < pin ? L2_EVICT_LAST : L2_EVICT_FIRST;
-        bulk_g2s_hint(dst, reinterpret_cast<const T*>(wa) + ((size_t)img * L + l0) * H, (uint32_t)(nloc * H * sizeof(T)), &full[rr], pol);
+        bulk_g2s_hint(dst, reinterpret_cast<const T*>(wa) + ((size_t)img * L + l0) * H, (uint32_t)(nloc * H * sizeof(T)), &full[rr],
+                      wa_hint == 1 ? L2_EVICT_LAST : (wa_hint == 2 ? L2_EVICT_NORMAL : pol));
         bulk_g2s_hint(dst + LS * H * sizeof(T), reinterpret_cast<const T*>(a) + ((size_t)img * L + l0) * D, (uint32_t)(nloc * D * sizeof(T)), &full[rr], pol);
         rc += CWARPS;
         if (rc >= endc) { rc = basec; phc ^= 1; }
@@ -494,7 +497,7 @@ fwd_stream_kernel(FwdParams p, Smem sl, Part pt, int ngroups) {
                     bulk_g2s(side + (size_t)sb * SIDE_F + (size_t)nb * (H + D), p.uf + row * p.ld_uf, (uint32_t)((H + D) * 4), bar);
                 }
             };
-            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, ngroups, q0, q1, pt.pin, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
+            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, ngroups, q0, q1, pt.pin, pt.wa_hint, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
         }
     }
 }
@@ -818,7 +821,7 @@ bwd_stream_kernel(BwdParams p, Smem sl, Part pt) {
                 bulk_g2s(dst + D, p.ctx32 + b * p.ld_c32, (uint32_t)(D * 4), bar);
                 bulk_g2s(dst + 2 * D, p.uf + b * p.ld_uf, (uint32_t)(H * 4), bar);
             };
-            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, 1, q0, q1, pt.pin, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
+            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, 1, q0, q1, pt.pin, pt.wa_hint, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
         }
     }
 }
@@ -882,12 +885,13 @@ inline int64_t scratch_bytes(int NI, int NB, int D, int H) {
 // counts cost less than the combine launch from ~1/4 of the SMs upwards, and from two items per SM the step is HBM-bound
 // anyway.  Tiny batches (single-image beam search) get equal slot counts, never a range shorter than 1/8 of an item
 // (bounds the pieces per item).
-inline Part pick_part(long long nitems, int spi, int slot_bytes, int ngroups, int* grid) {
+inline Part pick_part(long long nitems, int spi, int slot_bytes, int ngroups, bool bwd, int* grid) {
     const int sms = num_sms();
     Part pt;
     pt.tot = nitems * spi;
     // beam groups of one image re-read the image inside the launch: count each image's bytes once
     const double total_bytes = (double)pt.tot * slot_bytes / ngroups;
+    pt.wa_hint = bwd ? g_attn_wa_hint_bwd : g_attn_wa_hint_fwd;
     pt.pin = (double)g_attn_pin_bytes >= total_bytes ? spi : (int)(spi * ((double)g_attn_pin_bytes / total_bytes));
     const bool whole = g_attn_part == 1 || (g_attn_part == 0 && nitems * 4 >= (long long)sms);
     if (whole) {
@@ -926,7 +930,7 @@ int launch_fwd_inst(const FwdParams& p, cudaStream_t stream) {
     SAT_REQUIRE(sl.nslots >= CWARPS && sl.total <= SMEM_MAX, "attention fwd (streaming): shared memory budget exceeded (L=%d)", p.L);
     const int ngroups = (p.NB + NBG - 1) / NBG, spi = (p.L + G::LS - 1) / G::LS;
     int grid = 1;
-    const Part pt = pick_part((long long)p.NI * ngroups, spi, G::SLOT, ngroups, &grid);
+    const Part pt = pick_part((long long)p.NI * ngroups, spi, G::SLOT, ngroups, false, &grid);
     SatProfScope prof(SAT_PROF_ATTN_FWD, stream);
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
@@ -985,7 +989,7 @@ int launch_bwd_inst(const BwdParams& p_in, cudaStream_t stream) {
     SAT_REQUIRE(sl.nslots >= CWARPS && sl.total <= SMEM_MAX, "attention bwd (streaming): shared memory budget exceeded (L=%d)", p.L);
     const int spi = (p.L + G::LS - 1) / G::LS;
     int grid = 1;
-    const Part pt = pick_part(p.B, spi, G::SLOT, 1, &grid);
+    const Part pt = pick_part(p.B, spi, G::SLOT, 1, true, &grid);
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
     pdl_config(&cfg, attr, dim3(grid), dim3(THREADS), sl.total, stream);

@@ -7,6 +7,7 @@ int g_force_simt = 0;
 int g_attn_generic = 0;
 int g_attn_part = 0;
 long long g_attn_pin_bytes = 0;
+int g_attn_wa_hint_fwd = 1, g_attn_wa_hint_bwd = 0;
 int g_pdl = 1;
 static thread_local char g_err[1024] = "";
 
@@ -63,7 +64,12 @@ const char* sat_last_error(void) { return g_err; }
 int sat_version(void) { return 100; }
 int sat_set_force_simt(int on) { g_force_simt = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_generic(int on) { g_attn_generic = on ? 1 : 0; return SAT_OK; }
-int sat_set_attn_l2_pin_bytes(int64_t bytes) { g_attn_pin_bytes = bytes > 0 ? bytes : 0; return SAT_OK; }
+int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes) {
+    g_attn_wa_hint_fwd = (wa_fwd >= 0 && wa_fwd <= 2) ? wa_fwd : 0;
+    g_attn_wa_hint_bwd = (wa_bwd >= 0 && wa_bwd <= 2) ? wa_bwd : 0;
+    g_attn_pin_bytes = pin_bytes > 0 ? pin_bytes : 0;
+    return SAT_OK;
+}
 int sat_set_pdl(int on) { g_pdl = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_partition(int mode) { g_attn_part = (mode == 1 || mode == 2) ? mode : 0; return SAT_OK; }
 

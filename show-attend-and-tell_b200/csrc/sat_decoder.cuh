@@ -62,7 +62,8 @@ struct DecWs {
     int64_t* tok_in; // (T,B) token fed to each step (free-running mode)
     float* rowloss;  // (B*T)
     float* loss_part; // (2 * LOSS_PARTS) partial sums of the loss reduction
-    float* logits_tmp;   // (B,T,V) when preds == NULL
+    float* logits_tmp;   // (B,T,Vp) when preds == NULL: row pitch padded to 8 so the GEMM epilogue stores 16-byte vectors
+    int64_t ldl;         // row pitch of the logits the drivers work on: V (preds) or Vp (logits_tmp)
     // backward
     T* dlog;         // (T,B,Vp)
     float* dHd;      // (T,B,H)
@@ -121,7 +122,8 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
     TK(Gates, B * Tn * 4 * H, T); TK(Ctx, B * Tn * D, T); TK(Hdrop, B * Tn * H, T); TK(hc0, B * 2 * H, float);
     TK(P1, a.ado ? B * Tn * H : 0, T); TK(P2, a.ado ? B * Tn * H : 0, T); TK(Comb, a.ado ? B * Tn * H : 0, T);
     TK(tok_in, B * Tn, int64_t); TK(rowloss, B * Tn, float); TK(loss_part, 2 * misc::LOSS_PARTS, float);
-    TK(logits_tmp, a.preds ? 0 : B * Tn * V, float);
+    TK(logits_tmp, a.preds ? 0 : B * Tn * w.Vp, float);
+    w.ldl = a.preds ? (int64_t)V : w.Vp;
     if (a.need_grad) {
         TK(dlog, B * Tn * w.Vp, T); TK(dHd, B * Tn * H, float); TK(dG, B * Tn * 4 * H, T); TK(dZH, B * (D + H), float);
         TK(dUF, B * Tn * (H + D), T); TK(dh_carry, B * H, float); TK(dc_carry, B * H, float);
@@ -135,6 +137,7 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
         TK(gscratch, gs, float);
         w.csum_floats = 64 * (V > 4 * H ? V : 4 * H);
         if (w.csum_floats < 64 * (H + D)) w.csum_floats = 64 * (H + D);
+        if (w.csum_floats < (int64_t)4 * 148 * H) w.csum_floats = (int64_t)4 * 148 * H;      // sum_over_t_colsum: one row per block
         TK(csum, w.csum_floats, float);
         TK(dcomb, a.ado ? B * Tn * H : 0, float); TK(dP1, a.ado ? B * Tn * H : 0, T); TK(dP2, a.ado ? B * Tn * H : 0, T);
         TK(dctx_all, a.ado ? B * Tn * D : 0, float);
@@ -194,15 +197,16 @@ template <typename T>
 int output_layer(const sat_decoder_args& a, DecWs<T>& w, cudaStream_t st, int t0, int nt) {
     const int B = a.B, D = a.D, H = a.H, V = a.V, Tn = a.T;
     const int M = nt * B;
-    float* logits = a.preds ? a.preds : w.logits_tmp;            // (B,T,V)
+    float* logits = a.preds ? a.preds : w.logits_tmp;            // (B,T,ldl)
+    const int64_t ldl = w.ldl;
     const T* hd = w.Hdrop + (size_t)t0 * B * H;
     auto set_out = [&](EpiLinear<T, IsF32<T>::value>& e) {
-        if (nt == 1) { e.Cf = logits + (size_t)t0 * V; e.ldcf = (int64_t)Tn * V; }
-        else { e.Cf = logits; e.ldcf = V; e.remapB = B; e.remapT = Tn; }
-        e.vec_ok = e.vec_ok && (V % 8 == 0);
+        if (nt == 1) { e.Cf = logits + (size_t)t0 * ldl; e.ldcf = (int64_t)Tn * ldl; }
+        else { e.Cf = logits; e.ldcf = ldl; e.remapB = B; e.remapT = Tn; }
+        e.vec_ok = e.vec_ok && (ldl % 8 == 0);
     };
     if (!a.ado) {
-        auto e = lin<T>(M, V, a.deep_b, SAT_ACT_NONE, logits, V, nullptr, 0);
+        auto e = lin<T>(M, V, a.deep_b, SAT_ACT_NONE, logits, ldl, nullptr, 0);
         set_out(e);
         return gemm<T>(st, hd, H, true, w.w_out, H, true, M, V, H, e);
     }
@@ -215,7 +219,7 @@ int output_layer(const sat_decoder_args& a, DecWs<T>& w, cudaStream_t st, int t0
     SAT_TRY(gemm<T>(st, ctx, D, true, w.w_fz, D, true, M, H, D, e2));
     misc::add3_kernel<T><<<misc::grid_for((int64_t)M * H), 256, 0, st>>>(cb, p1, p2, emb, (int64_t)M * H);
     SAT_CHECK_CUDA(cudaGetLastError());
-    auto e3 = lin<T>(M, V, a.f_out_b, SAT_ACT_RELU, logits, V, nullptr, 0);
+    auto e3 = lin<T>(M, V, a.f_out_b, SAT_ACT_RELU, logits, ldl, nullptr, 0);
     set_out(e3);
     return gemm<T>(st, cb, H, true, w.w_out, H, true, M, V, H, e3);
 }
@@ -309,8 +313,8 @@ int decoder_forward_t(const sat_decoder_args& a) {
         if (!a.tf) {
             SAT_TRY(output_layer<T>(a, w, st, t, 1));
             if (t + 1 < Tn) {
-                float* logits = (a.preds ? a.preds : w.logits_tmp) + (size_t)t * V;
-                misc::argmax_rows_kernel<<<B, 256, 0, st>>>(logits, (int64_t)Tn * V, V, w.tok_in + (size_t)(t + 1) * B, 1);
+                float* logits = (a.preds ? a.preds : w.logits_tmp) + (size_t)t * w.ldl;
+                misc::argmax_rows_kernel<<<B, 256, 0, st>>>(logits, (int64_t)Tn * w.ldl, V, w.tok_in + (size_t)(t + 1) * B, 1);
                 SAT_CHECK_CUDA(cudaGetLastError());
             }
         }
@@ -319,7 +323,7 @@ int decoder_forward_t(const sat_decoder_args& a) {
     if (a.fused_loss) {
         SAT_REQUIRE(a.loss != nullptr, "fused_loss needs a loss output");
         const float* logits = a.preds ? a.preds : w.logits_tmp;
-        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, V, V, Tn, a.captions, a.cap_stride, w.rowloss, (T*)nullptr, 0, nullptr, 1.0f);
+        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, w.rowloss, (T*)nullptr, 0, nullptr, 1.0f);
         misc::loss_partial_kernel<<<misc::LOSS_PARTS, 256, 0, st>>>(w.rowloss, B * Tn, a.alphas, B, Tn, L, w.loss_part);
         misc::loss_finalize_kernel<<<1, 256, 0, st>>>(w.loss_part, misc::LOSS_PARTS, B * (Tn - 1), a.alphas != nullptr, B, L, a.alpha_c, a.loss);
         SAT_CHECK_CUDA(cudaGetLastError());
@@ -348,7 +352,7 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     const float* galpha = g.dalphas;
     if (a.fused_loss) {
         const float scale = 1.0f / (float)(B * (Tn - 1));
-        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, V, V, Tn, a.captions, a.cap_stride, nullptr, w.dlog, Vp, g.dloss, scale);
+        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, nullptr, w.dlog, Vp, g.dloss, scale);
         if (a.attention) {
             misc::alpha_reg_grad_kernel<<<sat_cdiv(B * L, 128), 128, 0, st>>>(a.alphas, w.galpha, B, Tn, L, a.alpha_c, g.dloss);
             galpha = w.galpha;
@@ -356,7 +360,7 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         SAT_CHECK_CUDA(cudaGetLastError());
     } else {
         SAT_REQUIRE(g.dpreds != nullptr, "dpreds is NULL");
-        misc::dpreds_to_dlog_kernel<T><<<BT, 256, 0, st>>>(w.dlog, Vp, g.dpreds, a.ado ? logits : nullptr, B, Tn, V);
+        misc::dpreds_to_dlog_kernel<T><<<BT, 256, 0, st>>>(w.dlog, Vp, g.dpreds, a.ado ? logits : nullptr, w.ldl, B, Tn, V);
         SAT_CHECK_CUDA(cudaGetLastError());
     }
 
@@ -497,13 +501,22 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         if (g.att_U_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
         if (g.f_beta_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_b, w.gscratch + H, (size_t)D * 4, cudaMemcpyDeviceToDevice, st));
         // encoder projection: dW (H x D) = (sum_t dpre)^T a ; db_W = colsum ; dv, db_v
-        if (w.attn_stream) SAT_TRY(misc::sum_over_t<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L * H, Tn));
-        else SAT_TRY((misc::cast<float, T>(st, w.dwa_t, w.dwa_acc, (int64_t)B * L * H)));
+        bool att_W_b_done = false;
+        if (w.attn_stream) {
+            if (g.att_W_b) {     // one pass: sum over t + the bias gradient's column sums
+                SAT_TRY(misc::sum_over_t_colsum<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L, H, Tn, g.att_W_b, w.csum, w.csum_floats));
+                att_W_b_done = true;
+            } else {
+                SAT_TRY(misc::sum_over_t<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L * H, Tn));
+            }
+        } else {
+            SAT_TRY((misc::cast<float, T>(st, w.dwa_t, w.dwa_acc, (int64_t)B * L * H)));
+        }
         if (g.att_W_w) {
             auto e2 = lin<T>(H, D, nullptr, SAT_ACT_NONE, g.att_W_w, D, nullptr, 0);
             SAT_TRY(gemm<T>(st, w.dwa_t, H, false, w.a_c, D, false, H, D, B * L, e2));
         }
-        if (g.att_W_b) {
+        if (g.att_W_b && !att_W_b_done) {
             if (w.attn_stream) SAT_TRY(misc::colsum<T>(st, w.dwa_t, H, B * L, H, g.att_W_b, w.csum, w.csum_floats));
             else SAT_TRY(misc::colsum<float>(st, w.dwa_acc, H, B * L, H, g.att_W_b, w.csum, w.csum_floats));
         }

@@ -128,6 +128,68 @@ int sum_over_t(cudaStream_t s, T* out, const T* src, int64_t n, int Tn) {
     return SAT_OK;
 }
 
+// The same pass with the column sums of the result as a side output (the bias gradient of the encoder projection):
+// rows of H columns; a block is `rpb` whole rows of 16-byte vectors wide, so with a grid stride that is a multiple of the
+// row length a thread meets the same columns every iteration and keeps their sums in registers.
+// part[block][H] holds per-block partial column sums (fp32, taken before rounding to T); colsum_final_kernel adds them.
+template <typename T>
+__global__ void sum_over_t_colsum_kernel(T* __restrict__ out, const T* __restrict__ src, int64_t nvec, int64_t n, int Tn, int H,
+                                         float* __restrict__ part) {
+    constexpr int VEC = Vec16<T>::N;
+    extern __shared__ float red[];                 // [blockDim][VEC]
+    const int cpr = H / VEC;                       // vectors per row
+    float cs[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) cs[k] = 0.0f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (int64_t)gridDim.x * blockDim.x) {
+        float acc[VEC];
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) acc[k] = 0.0f;
+#pragma unroll 5
+        for (int t = 0; t < Tn; ++t) {
+            float f[VEC];
+            Vec16<T>::unpack(ldg_stream16(src + (size_t)t * n + i * VEC), f);
+#pragma unroll
+            for (int k = 0; k < VEC; ++k) acc[k] += f[k];
+        }
+        *reinterpret_cast<uint4*>(out + i * VEC) = Vec16<T>::pack(acc);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) cs[k] += acc[k];
+    }
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) red[threadIdx.x * VEC + k] = cs[k];
+    __syncthreads();
+    if ((int)threadIdx.x < cpr) {
+        const int rpb = blockDim.x / cpr;
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) {
+            float t = 0.0f;
+            for (int r = 0; r < rpb; ++r) t += red[(r * cpr + threadIdx.x) * VEC + k];
+            part[(size_t)blockIdx.x * H + threadIdx.x * VEC + k] = t;
+        }
+    }
+}
+__global__ void colsum_final_kernel(const float* __restrict__ part, int S, int N, float* __restrict__ out, int ilH);
+// out (rows x H, T) = sum_t src[t];  colsum_out[H] = column sums of that (fp32)
+template <typename T>
+int sum_over_t_colsum(cudaStream_t s, T* out, const T* src, int64_t rows, int H, int Tn, float* colsum_out, float* scratch,
+                      int64_t scratch_floats) {
+    constexpr int VEC = Vec16<T>::N;
+    SAT_REQUIRE(H % VEC == 0 && H / VEC <= 1024, "sum_over_t_colsum: H must be a multiple of %d", VEC);
+    const int cpr = H / VEC;
+    const int rpb = cpr >= 256 ? 1 : 256 / cpr;
+    const int threads = cpr * rpb;
+    const int64_t n = rows * H, nvec = n / VEC;
+    int64_t blocks = sat_cdiv64(nvec, threads);
+    if (blocks > 4 * 148) blocks = 4 * 148;
+    if (blocks * H > scratch_floats) blocks = scratch_floats / H;
+    SAT_REQUIRE(blocks >= 1, "sum_over_t_colsum: scratch too small");
+    sum_over_t_colsum_kernel<T><<<(int)blocks, threads, (size_t)threads * VEC * 4, s>>>(out, src, nvec, n, Tn, H, scratch);
+    colsum_final_kernel<<<sat_cdiv(H, 32), 256, 0, s>>>(scratch, (int)blocks, H, colsum_out, 0);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
 // abar[b,d] = mean_l a[b,l,d]   (decoder.py:139 / :104)
 template <typename T>
 __global__ void mean_l_kernel(const T* __restrict__ a, float* __restrict__ out_f, T* __restrict__ out_t, int L, int D) {
@@ -233,14 +295,24 @@ __global__ void colsum_partial_kernel(const T* __restrict__ X, int64_t ld, int M
     for (int m = m0; m < m1; ++m) acc += to_f32<T>(X[(int64_t)m * ld + n]);
     part[(size_t)s * N + n] = acc;
 }
+// block = 8 row groups x 32 columns: 8 partial sums per column in flight, combined through shared memory (fixed order)
 __global__ void colsum_final_kernel(const float* __restrict__ part, int S, int N, float* __restrict__ out, int ilH) {
-    const int n = blockIdx.x * blockDim.x + threadIdx.x;
-    if (n >= N) return;
+    __shared__ float red[8][33];
+    const int c = threadIdx.x & 31, rg = threadIdx.x >> 5;
+    const int n = blockIdx.x * 32 + c;
     float acc = 0.0f;
-    for (int s = 0; s < S; ++s) acc += part[(size_t)s * N + n];
-    // ilH > 0: column n of the interleaved gate axis belongs to source row (n%4)*ilH + n/4
-    const int d = ilH > 0 ? ((n % 4) * ilH + n / 4) : n;
-    out[d] = acc;
+    if (n < N)
+        for (int s = rg; s < S; s += 8) acc += part[(size_t)s * N + n];
+    red[rg][c] = acc;
+    __syncthreads();
+    if (rg == 0 && n < N) {
+        float t = 0.0f;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) t += red[r][c];
+        // ilH > 0: column n of the interleaved gate axis belongs to source row (n%4)*ilH + n/4
+        const int d = ilH > 0 ? ((n % 4) * ilH + n / 4) : n;
+        out[d] = t;
+    }
 }
 template <typename T>
 int colsum(cudaStream_t s, const T* X, int64_t ld, int M, int N, float* out, float* scratch, int64_t scratch_floats, int ilH = 0) {
@@ -250,7 +322,7 @@ int colsum(cudaStream_t s, const T* X, int64_t ld, int M, int N, float* out, flo
     const int rps = sat_cdiv(M, S);
     dim3 grid(sat_cdiv(N, 128), S);
     colsum_partial_kernel<T><<<grid, 128, 0, s>>>(X, ld, M, N, scratch, rps);
-    colsum_final_kernel<<<sat_cdiv(N, 128), 128, 0, s>>>(scratch, S, N, out, ilH);
+    colsum_final_kernel<<<sat_cdiv(N, 32), 256, 0, s>>>(scratch, S, N, out, ilH);
     SAT_CHECK_CUDA(cudaGetLastError());
     return SAT_OK;
 }
@@ -428,10 +500,10 @@ __global__ void relu_bwd_kernel(T* __restrict__ out, const float* __restrict__ x
 // dlog[t*B+b, v] (T, pitch ld_d) = dpreds[b,t,v] (* relu'(preds[b,t,v]) when ref != null: final ReLU of ado, Q8)
 template <typename T>
 __global__ void dpreds_to_dlog_kernel(T* __restrict__ out, int64_t ld_d, const float* __restrict__ x, const float* __restrict__ ref,
-                                      int B, int Tn, int V) {
+                                      int64_t ld_ref, int B, int Tn, int V) {
     const int r = blockIdx.x, b = r / Tn, t = r - b * Tn;
     const float* xr = x + (int64_t)r * V;
-    const float* rr = ref ? ref + (int64_t)r * V : nullptr;
+    const float* rr = ref ? ref + (int64_t)r * ld_ref : nullptr;
     T* o = out + ((int64_t)t * B + b) * ld_d;
     for (int v = threadIdx.x; v < V; v += blockDim.x) o[v] = from_f32<T>((rr && !(rr[v] > 0.0f)) ? 0.0f : xr[v]);
 }

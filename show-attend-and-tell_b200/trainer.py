@@ -80,16 +80,16 @@ class FusedTrainStep:
             setattr(a, field, None if p is None else p.data_ptr())
         key = (B, Lloc, D, T, a.a_dtype)
         if self._ws_key != key:
-            self.preds = torch.empty(B, T, a.V, device=dev, dtype=torch.float32)
             self.alphas = torch.empty(B, T, Lloc, device=dev, dtype=torch.float32)
             self.loss = torch.zeros(3, device=dev, dtype=torch.float32)
-            a.preds, a.alphas, a.loss = self.preds.data_ptr(), self.alphas.data_ptr(), self.loss.data_ptr()
+            # no (B,T,V) preds tensor: the fused loss reads the logits from the workspace (padded row pitch)
+            a.preds, a.alphas, a.loss = None, self.alphas.data_ptr(), self.loss.data_ptr()
             nbytes = C.c_int64(0)
             _lib.check(L.sat_decoder_workspace_bytes(C.byref(a), C.byref(nbytes)), "sat_decoder_workspace_bytes")
             self._ws = torch.empty(nbytes.value + 256, device=dev, dtype=torch.uint8)
             self._ws_bytes = nbytes.value
             self._ws_key = key
-        a.preds, a.alphas, a.loss = self.preds.data_ptr(), self.alphas.data_ptr(), self.loss.data_ptr()
+        a.preds, a.alphas, a.loss = None, self.alphas.data_ptr(), self.loss.data_ptr()
         a.workspace = self._ws.data_ptr() + ((-self._ws.data_ptr()) % 256)
         a.workspace_bytes = self._ws_bytes
         a.stream = torch.cuda.current_stream(dev).cuda_stream

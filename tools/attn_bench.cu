@@ -10,6 +10,7 @@
 int g_attn_generic = 0;
 int g_attn_part = 0;
 long long g_attn_pin_bytes = 0;
+int g_attn_wa_hint_fwd = 1, g_attn_wa_hint_bwd = 0;
 int g_pdl = 1;
 void sat_set_error(const char* fmt, ...) { va_list ap; va_start(ap, fmt); vfprintf(stderr, fmt, ap); va_end(ap); fprintf(stderr, "\n"); }
 SatProfScope::SatProfScope(int c, cudaStream_t s) : cat(c), st(s), slot(-1) {}
@@ -54,6 +55,8 @@ int main(int argc, char** argv) {
     if (getenv("SAT_PART")) g_attn_part = atoi(getenv("SAT_PART"));
     if (getenv("SAT_PIN_MB")) g_attn_pin_bytes = (long long)atoi(getenv("SAT_PIN_MB")) << 20;
     if (getenv("SAT_PDL")) g_pdl = atoi(getenv("SAT_PDL"));
+    if (getenv("SAT_WA_FWD")) g_attn_wa_hint_fwd = atoi(getenv("SAT_WA_FWD"));
+    if (getenv("SAT_WA_BWD")) g_attn_wa_hint_bwd = atoi(getenv("SAT_WA_BWD"));
     const int static_in = getenv("SAT_STATIC") ? atoi(getenv("SAT_STATIC")) : 1;
     const int sameset = getenv("SAT_SAMESET") ? atoi(getenv("SAT_SAMESET")) : 0;      // 1: every launch reads the same inputs
     const int B = argc > 1 ? atoi(argv[1]) : 256, iters = argc > 2 ? atoi(argv[2]) : 20;
@@ -125,6 +128,23 @@ int main(int argc, char** argv) {
         printf("%s B=%d  %.2f us  algorithmic %.0f GB/s  moved %.0f GB/s\n", which ? "bwd" : "fwd", B, us, bytes / us / 1e3, real / us / 1e3);
     }
     CK(cudaDeviceSynchronize());
+    if (getenv("SAT_TRAIN")) {   // the access pattern of a train step: T forward launches then T backward launches on one batch, next batch ...
+        const int T = 20;
+        cudaEvent_t ef0, ef1, eb1; CK(cudaEventCreate(&ef0)); CK(cudaEventCreate(&ef1)); CK(cudaEventCreate(&eb1));
+        double tf = 0, tb = 0;
+        for (int it = 0; it < 6; ++it) {
+            const int s = it & 1;
+            CK(cudaEventRecord(ef0));
+            for (int t = 0; t < T; ++t) fwd(s);
+            CK(cudaEventRecord(ef1));
+            for (int t = 0; t < T; ++t) bwd(s);
+            CK(cudaEventRecord(eb1)); CK(cudaEventSynchronize(eb1));
+            float a, b; CK(cudaEventElapsedTime(&a, ef0, ef1)); CK(cudaEventElapsedTime(&b, ef1, eb1));
+            if (it >= 2) { tf += a; tb += b; }
+        }
+        printf("train pattern B=%d wa_hint fwd=%d bwd=%d: fwd %.2f us/launch  bwd %.2f us/launch\n", B, g_attn_wa_hint_fwd, g_attn_wa_hint_bwd,
+               tf * 1e3 / (4 * T), tb * 1e3 / (4 * T));
+    }
     {   // checksums of the last fwd / bwd outputs: compare across SAT_PART settings
         double* cs; CK(cudaMalloc(&cs, 5 * 8)); CK(cudaMemset(cs, 0, 5 * 8));
         fwd(0); bwd(0);

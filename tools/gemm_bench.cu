@@ -23,7 +23,7 @@ __global__ void checksum_f32(const float* x, size_t n, double* out) {
     atomicAdd(out, acc);
 }
 
-struct Shape { const char* name; int M, N, K; bool b_kmajor; };
+struct Shape { const char* name; int M, N, K; bool b_kmajor; bool out_bf16; };
 
 int main(int argc, char** argv) {
     const int iters = argc > 1 ? atoi(argv[1]) : 50;
@@ -34,7 +34,8 @@ int main(int argc, char** argv) {
         {"dZH  = dG W_gzh     (B MN)   ", 256, 2560, 2048, false},
         {"dh   = dUF w_uf     (B MN)   ", 256, 512, 2560, false},
         {"c1 UF (B=32)                 ", 32, 1024, 512, true},
-        {"Wa   = a W^T (K1)            ", 50176, 512, 2048, true},
+        {"Wa   = a W^T (K1), bf16 out  ", 50176, 512, 2048, true, true},
+        {"logits = Hdrop W_out^T, ld=V ", 5120, 2531, 512, true},
         {"probe: one tile, one k-block ", 128, 32, 64, true},
         {"probe: 128 tiles, 1 k-block  ", 256, 2048, 64, true},
         {"probe: 128 tiles, 8 k-blocks ", 256, 2048, 512, true},
@@ -46,11 +47,14 @@ int main(int argc, char** argv) {
     double* cs; CK(cudaMalloc(&cs, 8));
     for (const Shape& s : shapes) {
         bf16 *A, *B; float* C;
-        CK(cudaMalloc(&A, (size_t)s.M * s.K * 2)); CK(cudaMalloc(&B, (size_t)s.N * s.K * 2)); CK(cudaMalloc(&C, (size_t)s.M * s.N * 4));
-        fill_bf16<<<512, 256>>>(A, (size_t)s.M * s.K, 3); fill_bf16<<<512, 256>>>(B, (size_t)s.N * s.K, 5);
+        const int Np = (s.N + 7) & ~7;
+        CK(cudaMalloc(&A, (size_t)s.M * s.K * 2)); CK(cudaMalloc(&B, (size_t)Np * s.K * 2)); CK(cudaMalloc(&C, (size_t)s.M * s.N * 4));
+        CK(cudaMemset(C, 0, (size_t)s.M * s.N * 4));
+        fill_bf16<<<512, 256>>>(A, (size_t)s.M * s.K, 3); fill_bf16<<<512, 256>>>(B, (size_t)Np * s.K, 5);
         EpiLinear<bf16, false> e;
         memset(&e, 0, sizeof(e));
-        e.Cf = C; e.ldcf = s.N; e.M = s.M; e.N = s.N; e.vec_ok = 1;
+        if (s.out_bf16) { e.Ct = reinterpret_cast<bf16*>(C); e.ldct = s.N; } else { e.Cf = C; e.ldcf = s.N; }
+        e.M = s.M; e.N = s.N; e.vec_ok = (s.N % 8 == 0);
         const int64_t ldb = s.b_kmajor ? s.K : s.N;
         auto run = [&]() { if (tc::launch(0, A, s.K, true, B, ldb, s.b_kmajor, s.M, s.N, s.K, e) != 0) exit(2); };
         for (int i = 0; i < 3; ++i) run();
@@ -72,7 +76,7 @@ int main(int argc, char** argv) {
         float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
         CK(cudaGraphExecDestroy(ge)); CK(cudaGraphDestroy(g)); CK(cudaStreamDestroy(st));
         CK(cudaMemset(cs, 0, 8));
-        checksum_f32<<<64, 256>>>(C, (size_t)s.M * s.N, cs);
+        checksum_f32<<<64, 256>>>(C, (size_t)s.M * s.N / (s.out_bf16 ? 2 : 1), cs);
         double h; CK(cudaMemcpy(&h, cs, 8, cudaMemcpyDeviceToHost));
         const double us = ms * 1e3 / iters;
         printf("%s M=%5d N=%4d K=%4d  graph %7.2f us  eager %7.2f us  %7.1f TFLOP/s  checksum %.6e\n", s.name, s.M, s.N, s.K, us,
