@@ -11,7 +11,8 @@ namespace beam {
 // K5: per image, the `n` best of (live rows x V) cumulative scores, sorted (score desc, flat index asc),
 // followed by the reference's bookkeeping (decoder.py:206-250).
 struct StepParams {
-    const float* logits;     // (R, V)
+    const float* logits;     // (R, ldl): row pitch padded to a multiple of 8 floats so the GEMM epilogue stores vectors
+    int64_t ldl;
     float* top_preds;        // (R)  cumulative score per live slot (in/out)
     int64_t* prev_word;      // (R)  word fed to the next step (out)
     int* live;               // (NI) current beam size (in/out)
@@ -28,6 +29,7 @@ struct StepParams {
     int* last_step;          // (NI) last executed step
     int* last_n;             // (NI) rows alive at the start of the last executed step
     int NI, beam, V, step, max_steps, stop_a, stop_b;
+    int cache_floats;        // dynamic shared memory available for the score cache (floats)
 };
 
 constexpr int TOPK_THREADS = 512;
@@ -40,12 +42,14 @@ topk_step_kernel(StepParams p) {
     __shared__ float pick_val[MAXBEAM];
     __shared__ int pick_idx[MAXBEAM];
     __shared__ float s_tp[MAXBEAM];
+    extern __shared__ float s_cache[];      // cumulative scores of this image, filled by the first selection pass
     const int img = blockIdx.x;
     if (p.done[img]) return;
     const int n = p.live[img];
     const int rows = (p.step == 1) ? 1 : n;                    // decoder.py:206-209 (Q14)
     const int total = rows * p.V;
-    const float* lg = p.logits + (size_t)img * p.beam * p.V;
+    const bool cached = total <= p.cache_floats;   // later passes then read shared memory instead of global
+    const float* lg = p.logits + (size_t)img * p.beam * p.ldl;
     if (threadIdx.x < MAXBEAM) s_tp[threadIdx.x] = (threadIdx.x < n) ? p.top_preds[img * p.beam + threadIdx.x] : 0.0f;
     __syncthreads();
     float last_v = INFINITY;
@@ -54,8 +58,14 @@ topk_step_kernel(StepParams p) {
         float bv = -INFINITY;
         int bi = 0x7fffffff;
         for (int i = threadIdx.x; i < total; i += TOPK_THREADS) {
-            const int r = i / p.V;
-            const float sc = s_tp[r] + lg[i];                  // decoder.py:204
+            float sc;
+            if (cached && k > 0) {
+                sc = s_cache[i];
+            } else {
+                const int r = i / p.V;
+                sc = s_tp[r] + lg[(size_t)r * p.ldl + (i - r * p.V)];   // decoder.py:204
+                if (cached) s_cache[i] = sc;
+            }
             const bool after = (sc < last_v) || (sc == last_v && i > last_i);
             if (after && (sc > bv || (sc == bv && i < bi))) { bv = sc; bi = i; }
         }
@@ -219,7 +229,7 @@ struct BeamWs {
     float* UF;     // (R, H + D)
     T* Ctx;        // (R, D)
     T *P1, *P2, *Comb;
-    float* logits; // (R, V)
+    float* logits; // (R, Vp)
     float* alpha_hist;   // (S, R, L)
     uint8_t* attn_scratch;
     bool attn_stream;
@@ -262,7 +272,7 @@ int64_t beam_carve(const sat_beam_args& a, BeamWs<T>& w, uint8_t* base) {
     TK(wa, a.attention ? NI * L * H : 0, T); TK(abar, NI * D, T); TK(abar_f, NI * D, float); TK(hc0, NI * 2 * H, float);
     TK(X, R * (2 * H + D), T); TK(Hn, R * H, T); TK(Cc, R * H, float); TK(Cn, R * H, float); TK(UF, R * (H + D), float);
     TK(Ctx, R * D, T); TK(P1, a.ado ? R * H : 0, T); TK(P2, a.ado ? R * H : 0, T); TK(Comb, a.ado ? R * H : 0, T);
-    TK(logits, R * V, float); TK(alpha_hist, a.attention ? S * R * L : 0, float);
+    TK(logits, R * ((V + 7) & ~(int64_t)7), float); TK(alpha_hist, a.attention ? S * R * L : 0, float);
     w.attn_stream = a.attention && attn_s::fwd_shape_ok(a.beam, a.L, a.D, a.H);
     TK(attn_scratch, w.attn_stream ? attn_s::scratch_bytes(a.NI, a.beam, a.D, a.H) : 0, uint8_t);
     TK(top_preds, R, float); TK(prev_word, R, int64_t);
@@ -336,6 +346,17 @@ int beam_search_t(const sat_beam_args& a) {
                                                              w.prev_word, NI, NB, (int64_t)a.start_token);
     SAT_CHECK_CUDA(cudaGetLastError());
     const int S = a.max_steps + 1;        // iterations 1..max_steps+1 (Q17)
+    const int64_t Vp = (V + 7) & ~(int64_t)7;
+    // shared-memory score cache of the top-k kernel: beam x V floats when that fits beside the static buffers
+    size_t topk_smem = (size_t)NB * V * 4;
+    if (topk_smem > 200 * 1024) topk_smem = 0;
+    {
+        static size_t configured = 0;
+        if (topk_smem > configured) {
+            SAT_CHECK_CUDA(cudaFuncSetAttribute(beam::topk_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            configured = 200 * 1024;
+        }
+    }
     for (int step = 1; step <= S; ++step) {
         SAT_TRY(misc::gather_rows<T>(st, w.X, xw, a.embedding, H, w.prev_word, 1, R, V));                  // decoder.py:183
         if (a.attention) {
@@ -359,8 +380,7 @@ int beam_search_t(const sat_beam_args& a) {
         e.M = R; e.H = H;
         SAT_TRY(gemm<T>(st, w.X, xw, true, w.w_gall, xw, true, R, 4 * H, (int)xw, e));                     // decoder.py:196-197
         if (!a.ado) {
-            auto eo = lin<T>(R, V, out_b, SAT_ACT_NONE, w.logits, V, nullptr, 0);
-            eo.vec_ok = eo.vec_ok && (V % 8 == 0);
+            auto eo = lin<T>(R, V, out_b, SAT_ACT_NONE, w.logits, Vp, nullptr, 0);
             SAT_TRY(gemm<T>(st, w.Hn, H, true, w.w_out, H, true, R, V, H, eo));                            // decoder.py:203
         } else {
             auto e1 = lin<T>(R, H, a.f_h_b, SAT_ACT_RELU, nullptr, 0, w.P1, H);
@@ -371,18 +391,18 @@ int beam_search_t(const sat_beam_args& a) {
             // comb = P1 + P2 + emb (emb = X[:, :H], strided rows)
             beam_add3_kernel<T><<<R, 128, 0, st>>>(w.Comb, w.P1, w.P2, w.X, xw, H);
             SAT_CHECK_CUDA(cudaGetLastError());
-            auto e3 = lin<T>(R, V, out_b, SAT_ACT_RELU, w.logits, V, nullptr, 0);
-            e3.vec_ok = e3.vec_ok && (V % 8 == 0);
+            auto e3 = lin<T>(R, V, out_b, SAT_ACT_RELU, w.logits, Vp, nullptr, 0);
             SAT_TRY(gemm<T>(st, w.Comb, H, true, w.w_out, H, true, R, V, H, e3));                          // decoder.py:199-201
         }
         beam::StepParams sp;
-        sp.logits = w.logits; sp.top_preds = w.top_preds; sp.prev_word = w.prev_word; sp.live = w.live; sp.done = w.done;
+        sp.logits = w.logits; sp.ldl = Vp; sp.top_preds = w.top_preds; sp.prev_word = w.prev_word; sp.live = w.live; sp.done = w.done;
         sp.n_active = w.n_active; sp.parent = w.parent; sp.cand_word = w.cand_word; sp.cand_parent = w.cand_parent;
         sp.slot_cand = w.slot_cand; sp.comp_score = w.comp_score; sp.comp_step = w.comp_step; sp.comp_cand = w.comp_cand;
         sp.ncomp = w.ncomp; sp.last_step = w.last_step; sp.last_n = w.last_n;
         sp.NI = NI; sp.beam = NB; sp.V = V; sp.step = step; sp.max_steps = a.max_steps;
         sp.stop_a = 1; sp.stop_b = a.bert ? 0 : 102;
-        beam::topk_step_kernel<<<NI, beam::TOPK_THREADS, 0, st>>>(sp);
+        sp.cache_floats = (int)(topk_smem / 4);
+        beam::topk_step_kernel<<<NI, beam::TOPK_THREADS, topk_smem, st>>>(sp);
         beam::gather_state_kernel<T><<<R, 128, 0, st>>>(w.X, xw, H + D, w.Hn, w.Cc, w.Cn, w.parent, w.live, w.done, NB, H);
         SAT_CHECK_CUDA(cudaGetLastError());
         if ((step % 4) == 0 && step < S) {     // early exit once every image has finished (no effect on results)

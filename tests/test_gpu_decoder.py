@@ -56,7 +56,8 @@ CASES = [
     dict(V=777, D=512, B=5, L=49, T=4, tf=False, ado=False, attention=True),
     dict(V=500, D=512, B=4, L=196, T=4, tf=True, ado=False, attention=False),
     dict(V=640, D=512, B=33, L=196, T=5, tf=True, ado=False, attention=True, gate=False),
-    # B >= 64 runs the streaming attention kernels (fwd + bwd with the per-step dpre buffer)
+    # small batches above run the streaming attention kernels with the equal-slot partition + combine kernels;
+    # from ~SMs/4 items the partition is whole items per CTA
     dict(V=640, D=512, B=66, L=196, T=4, tf=True, ado=False, attention=True),
     dict(V=520, D=2048, B=64, L=196, T=3, tf=True, ado=True, attention=True),
     dict(V=520, D=512, B=65, L=49, T=3, tf=True, ado=False, attention=True, gate=False),
