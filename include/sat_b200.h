@@ -31,6 +31,8 @@ int sat_set_attn_partition(int mode);
 /* debug knob: 1 (default) = PDL-aware kernels are launched with programmatic stream serialization (their prologue overlaps
  * the previous kernel's tail), 0 = ordinary launches */
 int sat_set_pdl(int on);
+/* tuning knob: largest split-K cluster size a skinny GEMM may use (1 = never split, default 4, at most 8) */
+int sat_set_gemm_splitk(int max_split);
 /* tuning knob: L2 eviction hints of the streaming attention kernels' loads.  wa_fwd / wa_bwd: policy of the Wa rows in the
  * forward / backward kernel (0 = evict_first like the feature rows, 1 = evict_last, 2 = evict_normal); pin_bytes: additionally
  * load this many bytes of a + Wa per launch (a prefix of every item) with evict_last.  Default (1, 0, 0): the 51 MB of Wa stay

@@ -9,6 +9,7 @@ int g_attn_part = 0;
 long long g_attn_pin_bytes = 0;
 int g_attn_wa_hint_fwd = 1, g_attn_wa_hint_bwd = 0;
 int g_pdl = 1;
+int g_gemm_max_split = 4;      // clusters of 8 launch slower than they save (tools/gemm_bench.cu)
 static thread_local char g_err[1024] = "";
 
 void sat_set_error(const char* fmt, ...) {
@@ -70,6 +71,7 @@ int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes) {
     g_attn_pin_bytes = pin_bytes > 0 ? pin_bytes : 0;
     return SAT_OK;
 }
+int sat_set_gemm_splitk(int max_split) { g_gemm_max_split = max_split >= 1 ? max_split : 1; return SAT_OK; }
 int sat_set_pdl(int on) { g_pdl = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_partition(int mode) { g_attn_part = (mode == 1 || mode == 2) ? mode : 0; return SAT_OK; }
 

@@ -222,6 +222,7 @@ struct BeamWs {
     float *b_uf, *b_g, *b_init;
     T *a_c, *wa, *abar;
     float* abar_f;
+    float* mean_part; // (4,NI,D) partial sums of the mean over L
     float* hc0;
     T* X;          // (R, H + D + H): [emb | z | h]
     T* Hn;         // (R, H)
@@ -269,7 +270,7 @@ int64_t beam_carve(const sat_beam_args& a, BeamWs<T>& w, uint8_t* base) {
     const bool a_alias = (a.a_dtype == a.dtype) && a.a_stride_d == 1 && a.a_stride_l == D && a.a_stride_b == L * D && al16(a.img_features);
     TK(a_c, a_alias ? 0 : NI * L * D, T);
     if (a_alias) w.a_c = reinterpret_cast<T*>(const_cast<void*>(a.img_features));
-    TK(wa, a.attention ? NI * L * H : 0, T); TK(abar, NI * D, T); TK(abar_f, NI * D, float); TK(hc0, NI * 2 * H, float);
+    TK(wa, a.attention ? NI * L * H : 0, T); TK(abar, NI * D, T); TK(abar_f, NI * D, float); TK(mean_part, 4 * NI * D, float); TK(hc0, NI * 2 * H, float);
     TK(X, R * (2 * H + D), T); TK(Hn, R * H, T); TK(Cc, R * H, float); TK(Cn, R * H, float); TK(UF, R * (H + D), float);
     TK(Ctx, R * D, T); TK(P1, a.ado ? R * H : 0, T); TK(P2, a.ado ? R * H : 0, T); TK(Comb, a.ado ? R * H : 0, T);
     TK(logits, R * ((V + 7) & ~(int64_t)7), float); TK(alpha_hist, a.attention ? S * R * L : 0, float);
@@ -332,7 +333,7 @@ int beam_search_t(const sat_beam_args& a) {
         else
             SAT_TRY((misc::cast3d<bf16, T>(st, w.a_c, reinterpret_cast<const bf16*>(a.img_features), NI, L, D, a.a_stride_b, a.a_stride_l, a.a_stride_d)));
     }
-    SAT_TRY(misc::mean_l<T>(st, w.a_c, w.abar_f, w.abar, NI, L, D));
+    SAT_TRY(misc::mean_l<T>(st, w.a_c, w.abar_f, w.abar, NI, L, D, w.mean_part, (int64_t)4 * NI * D));
     {
         auto e = lin<T>(NI, 2 * H, w.b_init, SAT_ACT_TANH, w.hc0, 2 * H, nullptr, 0);
         SAT_TRY(gemm<T>(st, w.abar, D, true, w.w_init, D, true, NI, 2 * H, D, e));

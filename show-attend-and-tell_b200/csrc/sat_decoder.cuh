@@ -49,6 +49,7 @@ struct DecWs {
     float *b_uf, *b_g, *b_init;
     T *a_c, *wa, *abar;
     float* abar_f;
+    float* mean_part; // (4,B,D) partial sums of the mean over L
     T* E;            // (T,B,H)     embeddings fed to each step
     float* Xg;       // (T,B,4H)    embedding share of the gate pre-activations (+ biases), interleaved
     float* UF;       // (T,B,H+D)   [U h | f_beta h] pre-activations
@@ -116,7 +117,7 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
     w.attn_scratch_bytes = w.attn_stream ? attn_s::scratch_bytes(a.B, 1, a.D, a.H) : 0;
     TK(attn_scratch, w.attn_scratch_bytes, uint8_t);
     TK(Ctx32, (w.attn_stream && a.need_grad) ? B * Tn * D : 0, float);
-    TK(abar, B * D, T); TK(abar_f, B * D, float);
+    TK(abar, B * D, T); TK(abar_f, B * D, float); TK(mean_part, 4 * B * D, float);
     TK(E, B * Tn * H, T); TK(Xg, B * Tn * 4 * H, float); TK(UF, B * Tn * (H + D), float);
     TK(ZH, B * (Tn + 1) * (D + H), T); TK(Cst, B * (Tn + 1) * H, float);
     TK(Gates, B * Tn * 4 * H, T); TK(Ctx, B * Tn * D, T); TK(Hdrop, B * Tn * H, T); TK(hc0, B * 2 * H, float);
@@ -244,7 +245,7 @@ int decoder_forward_t(const sat_decoder_args& a) {
             SAT_TRY((misc::cast3d<bf16, T>(st, w.a_c, reinterpret_cast<const bf16*>(a.img_features), B, L, D, a.a_stride_b, a.a_stride_l, a.a_stride_d)));
     }
     // initial state (decoder.py:137-147): [h0 | c0] = tanh(abar [init_h; init_c]^T + b)
-    SAT_TRY(misc::mean_l<T>(st, w.a_c, w.abar_f, w.abar, B, L, D));
+    SAT_TRY(misc::mean_l<T>(st, w.a_c, w.abar_f, w.abar, B, L, D, w.mean_part, (int64_t)4 * B * D));
     {
         auto e = lin<T>(B, 2 * H, w.b_init, SAT_ACT_TANH, w.hc0, 2 * H, nullptr, 0);
         SAT_TRY(gemm<T>(st, w.abar, D, true, w.w_init, D, true, B, 2 * H, D, e));
@@ -323,7 +324,10 @@ int decoder_forward_t(const sat_decoder_args& a) {
     if (a.fused_loss) {
         SAT_REQUIRE(a.loss != nullptr, "fused_loss needs a loss output");
         const float* logits = a.preds ? a.preds : w.logits_tmp;
-        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, w.rowloss, (T*)nullptr, 0, nullptr, 1.0f);
+        // with need_grad the same pass also leaves d loss / d logits for a unit upstream gradient (what the fused train step
+        // feeds back); sat_decoder_backward recomputes it only when it is handed a dloss scalar
+        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, w.rowloss,
+                                                        a.need_grad ? w.dlog : (T*)nullptr, w.Vp, nullptr, 1.0f / (float)(B * (Tn - 1)));
         misc::loss_partial_kernel<<<misc::LOSS_PARTS, 256, 0, st>>>(w.rowloss, B * Tn, a.alphas, B, Tn, L, w.loss_part);
         misc::loss_finalize_kernel<<<1, 256, 0, st>>>(w.loss_part, misc::LOSS_PARTS, B * (Tn - 1), a.alphas != nullptr, B, L, a.alpha_c, a.loss);
         SAT_CHECK_CUDA(cudaGetLastError());
@@ -352,7 +356,8 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     const float* galpha = g.dalphas;
     if (a.fused_loss) {
         const float scale = 1.0f / (float)(B * (Tn - 1));
-        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, nullptr, w.dlog, Vp, g.dloss, scale);
+        if (g.dloss)     // otherwise the forward's unit-gradient dlogits are still in the workspace
+            misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, nullptr, w.dlog, Vp, g.dloss, scale);
         if (a.attention) {
             misc::alpha_reg_grad_kernel<<<sat_cdiv(B * L, 128), 128, 0, st>>>(a.alphas, w.galpha, B, Tn, L, a.alpha_c, g.dloss);
             galpha = w.galpha;

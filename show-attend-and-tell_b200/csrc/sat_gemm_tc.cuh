@@ -17,6 +17,9 @@ constexpr int BM = 128, BK = 64, UMMA_K = 16;
 // One thread can start a TMA copy only every ~60 ns and a wait -> expect_tx -> copy round costs ~250-300 ns (measured,
 // tools/tma_bw.cu), which bounds a skinny GEMM's k-loop; so NPROD producer lanes take the k-blocks round-robin.
 constexpr int NPROD = SAT_GEMM_NPROD;
+}  // namespace tc
+extern int g_gemm_max_split;    // tuning knob (sat_set_gemm_splitk): largest split-K cluster size, 1 = never split
+namespace tc {
 // warp0 = TMA producer 0, warp1 = TMEM alloc + MMA issuer, warps 2-5 = epilogue, warps 6.. = further TMA producers
 constexpr int THREADS = 192 + 32 * (NPROD - 1);
 
@@ -25,7 +28,9 @@ template <int BN> struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int XBUF_OFF = STAGES * STAGE_BYTES + 256;            // split-K exchange buffer: BM x BN fp32
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+    static constexpr int SMEM_BYTES_SPLIT = SMEM_BYTES + BM * BN * 4;
 };
 
 __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
@@ -64,7 +69,12 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
     for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
-template <int BN, bool A_MN, bool B_MN, typename Epi>
+// SPLIT > 1: split-K over a thread-block cluster of SPLIT CTAs along z (a skinny GEMM with few tiles but a long K would
+// otherwise keep most SMs idle, each busy CTA pulling its operands at the ~130 GB/s one SM gets out of L2).  CTA z
+// accumulates k-blocks [nk*z/SPLIT, nk*(z+1)/SPLIT) in TMEM; the partial tiles are exchanged through distributed shared
+// memory reduce-scatter style -- CTA j receives columns [j*BN/SPLIT, (j+1)*BN/SPLIT) of every partial, adds them in a fixed
+// order (deterministic) and runs the epilogue for those columns.
+template <int BN, bool A_MN, bool B_MN, typename Epi, int SPLIT>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
             int M, int N, int K, Epi epi) {
@@ -82,7 +92,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
-    const int nk = (K + BK - 1) / BK;
+    const int nk_all = (K + BK - 1) / BK;
+    const int zsp = SPLIT > 1 ? (int)blockIdx.z : 0;
+    const int kb0 = SPLIT > 1 ? nk_all * zsp / SPLIT : 0;
+    const int nk = (SPLIT > 1 ? nk_all * (zsp + 1) / SPLIT : nk_all) - kb0;     // k-blocks of this CTA
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&mapA);
@@ -100,6 +113,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if constexpr (SPLIT > 1) cluster_arrive_release();     // #1 (waited on before the exchange): every CTA of the cluster runs
     // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) overlapped the previous
     // kernel's tail; its results are needed from here on.  Let the next kernel start its own prologue right away.
     pdl_wait();
@@ -115,7 +129,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
                 mbar_expect_tx(&full_bar[s], C::STAGE_BYTES);
                 uint8_t* a_dst = sA + s * C::A_BYTES;
                 uint8_t* b_dst = sB + s * C::B_BYTES;
-                const int k0 = kb * BK;
+                const int k0 = (kb0 + kb) * BK;
                 if (!A_MN) {
                     tma_load_2d(a_dst, &mapA, k0, m0, &full_bar[s]);
                 } else {
@@ -159,11 +173,53 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
         const int m = m0 + q * 32 + lane;
+        if constexpr (SPLIT == 1) {
 #pragma unroll 1
-        for (int c = 0; c < BN / 32; ++c) {
-            float v[32];
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v);
-            if (n0 + c * 32 < N) epi.template apply<32>(m, n0 + c * 32, v);
+            for (int c = 0; c < BN / 32; ++c) {
+                float v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v);
+                if (n0 + c * 32 < N) epi.template apply<32>(m, n0 + c * 32, v);
+            }
+        } else {
+            constexpr int CW = BN / SPLIT;           // columns this CTA finishes
+            static_assert(CW % 4 == 0 && BN <= 64, "split-K tiles are at most 64 wide and split into multiples of 4 columns");
+            float v[BN];
+#pragma unroll
+            for (int c = 0; c < BN / 32; ++c) tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v + 32 * c);
+            float* xbuf = reinterpret_cast<float*>(smem + C::XBUF_OFF);       // [SPLIT][BM][CW]
+            const int row = q * 32 + lane;
+            __syncwarp();
+            cluster_wait_acquire();                  // #1
+#pragma unroll
+            for (int j = 0; j < SPLIT; ++j) {
+                const uint32_t dst = dsmem_addr(xbuf + ((size_t)zsp * BM + row) * CW, (uint32_t)j);
+#pragma unroll
+                for (int c4 = 0; c4 < CW / 4; ++c4)
+                    dsmem_st_f32x4(dst + 16 * c4, v[j * CW + 4 * c4], v[j * CW + 4 * c4 + 1], v[j * CW + 4 * c4 + 2], v[j * CW + 4 * c4 + 3]);
+            }
+            cluster_arrive_release();                // #2: my slices are in every peer's buffer ...
+            cluster_wait_acquire();                  //     ... and every peer's slices are in mine
+            float acc[CW];
+#pragma unroll
+            for (int i = 0; i < CW; ++i) acc[i] = 0.0f;
+#pragma unroll
+            for (int sp = 0; sp < SPLIT; ++sp) {
+                const float4* src = reinterpret_cast<const float4*>(xbuf + ((size_t)sp * BM + row) * CW);
+#pragma unroll
+                for (int c4 = 0; c4 < CW / 4; ++c4) {
+                    const float4 t = src[c4];
+                    acc[4 * c4] += t.x; acc[4 * c4 + 1] += t.y; acc[4 * c4 + 2] += t.z; acc[4 * c4 + 3] += t.w;
+                }
+            }
+            if (n0 + zsp * CW < N) epi.template apply<CW>(m, n0 + zsp * CW, acc);
+        }
+    }
+    if constexpr (SPLIT > 1) {
+        if (warp < 2 || warp >= 6) {                 // the non-epilogue warps take part in both cluster barriers too
+            __syncwarp();
+            cluster_wait_acquire();
+            cluster_arrive_release();
+            cluster_wait_acquire();
         }
     }
     tc_fence_before();
@@ -209,26 +265,34 @@ inline int make_map(CUtensorMap* map, const void* ptr, uint64_t inner, uint64_t 
     return SAT_OK;
 }
 
-template <int BN, bool A_MN, bool B_MN, typename Epi>
+template <int BN, bool A_MN, bool B_MN, typename Epi, int SPLIT>
 int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB, int M, int N, int K, const Epi& epi) {
-    auto kern = gemm_kernel<BN, A_MN, B_MN, Epi>;
+    auto kern = gemm_kernel<BN, A_MN, B_MN, Epi, SPLIT>;
+    constexpr int smem = SPLIT > 1 ? Cfg<BN>::SMEM_BYTES_SPLIT : Cfg<BN>::SMEM_BYTES;
     static bool configured = false;
     if (!configured) {
-        SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+        SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         configured = true;
     }
-    dim3 grid(sat_cdiv(N, BN), sat_cdiv(M, BM));
+    dim3 grid(sat_cdiv(N, BN), sat_cdiv(M, BM), SPLIT);
     cudaLaunchConfig_t cfg;
-    cudaLaunchAttribute attr[1];
-    pdl_config(&cfg, attr, grid, dim3(THREADS), Cfg<BN>::SMEM_BYTES, stream);
+    cudaLaunchAttribute attr[2];
+    pdl_config(&cfg, attr, grid, dim3(THREADS), smem, stream);
+    if (SPLIT > 1) {
+        attr[1].id = cudaLaunchAttributeClusterDimension;
+        attr[1].val.clusterDim.x = 1; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = SPLIT;
+        cfg.numAttrs = 2;
+    }
     SAT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, M, N, K, epi));
     return SAT_OK;
 }
 
-// N-tile width.  Measured on B200 (tools/gemm_bench.cu): a launch costs ~4.3 us however small it is and every k-block adds
-// ~0.155 us per 20 KB stage in every wave of CTAs -- so the model is  waves x (fixed + k-blocks x stage bytes), which
-// keeps the per-step skinny GEMMs (M = batch) in ONE wave of <= #SMs CTAs; ties go to the wider tile (less A re-reading).
-inline int pick_bn(int M, int N, int K, bool b_mn) {
+// Tile width and split-K factor.  Measured on B200 (tools/gemm_bench.cu): a launch costs ~4.3 us however small it is and
+// every k-block adds ~0.155 us per 20 KB stage in every wave of CTAs (one SM pulls ~130 GB/s out of L2) -- so the model
+// is  waves x (fixed + exchange + k-blocks per CTA x stage bytes).  It keeps the per-step skinny GEMMs (M = batch) in ONE
+// wave of <= #SMs CTAs and splits K over a cluster when the tiles alone would leave most SMs idle; ties go to the wider
+// tile (less A re-reading).
+inline void pick_tile(int M, int N, int K, bool b_mn, int* bn_out, int* split_out) {
     static int sms = 0;
     if (!sms) {
         int dev = 0;
@@ -236,24 +300,27 @@ inline int pick_bn(int M, int N, int K, bool b_mn) {
     }
     const int mt = sat_cdiv(M, BM), nk = sat_cdiv(K, BK);
     const int cands[4] = {256, 128, 64, 32};
-    int best = b_mn ? 64 : 32;
+    int best = b_mn ? 64 : 32, best_split = 1;
     double best_cost = 1e30;
     for (int i = 0; i < 4; ++i) {
         const int bn = cands[i];
         if (b_mn && bn < 64) continue;
         if (bn > 32 && bn / 2 >= N && !(b_mn && bn == 64)) continue;   // tile far wider than N
         const long long tiles = (long long)mt * sat_cdiv(N, bn);
-        const double waves = (double)((tiles + sms - 1) / sms);
         const double stage_kb = 16.0 + bn / 8.0;
-        const double cost = waves * (28.0 * 20.0 + nk * stage_kb);
-        if (cost < best_cost * 0.999) { best_cost = cost; best = bn; }
+        for (int split = 1; split <= 8 && split <= g_gemm_max_split; split *= 2) {
+            if (split > 1 && (bn != 64 || tiles * split > sms || nk / split < 4)) continue;
+            const double waves = (double)((tiles * split + sms - 1) / sms);
+            const double cost = waves * (28.0 * 20.0 + (split > 1 ? 130.0 : 0.0) + sat_cdiv(nk, split) * stage_kb);
+            if (cost < best_cost * 0.999) { best_cost = cost; best = bn; best_split = split; }
+        }
     }
-    return best;
+    *bn_out = best; *split_out = best_split;
 }
 
 template <bool A_MN, bool B_MN, typename Epi>
 int launch_mn(cudaStream_t stream, const bf16* A, int64_t lda, const bf16* B, int64_t ldb, int M, int N, int K,
-              const Epi& epi, int bn) {
+              const Epi& epi, int bn, int split) {
     CUtensorMap mA, mB;
     if (!A_MN) SAT_TRY(make_map(&mA, A, K, M, lda, 64, BM));
     else       SAT_TRY(make_map(&mA, A, M, K, lda, 64, BK));
@@ -261,11 +328,15 @@ int launch_mn(cudaStream_t stream, const bf16* A, int64_t lda, const bf16* B, in
     if (!B_MN) SAT_TRY(make_map(&mB, B, K, N, ldb, 64, box_n));
     else       SAT_TRY(make_map(&mB, B, N, K, ldb, 64, BK));
     switch (bn) {
-        case 256: return launch_bn<256, A_MN, B_MN, Epi>(stream, mA, mB, M, N, K, epi);
-        case 128: return launch_bn<128, A_MN, B_MN, Epi>(stream, mA, mB, M, N, K, epi);
-        case 64:  return launch_bn<64, A_MN, B_MN, Epi>(stream, mA, mB, M, N, K, epi);
+        case 256: return launch_bn<256, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
+        case 128: return launch_bn<128, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
+        case 64:
+            if (split == 8) return launch_bn<64, A_MN, B_MN, Epi, 8>(stream, mA, mB, M, N, K, epi);
+            if (split == 4) return launch_bn<64, A_MN, B_MN, Epi, 4>(stream, mA, mB, M, N, K, epi);
+            if (split == 2) return launch_bn<64, A_MN, B_MN, Epi, 2>(stream, mA, mB, M, N, K, epi);
+            return launch_bn<64, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
         case 32:
-            if constexpr (!B_MN) return launch_bn<32, A_MN, B_MN, Epi>(stream, mA, mB, M, N, K, epi);
+            if constexpr (!B_MN) return launch_bn<32, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
         default: break;
     }
     sat_set_error("bad BN %d", bn);
@@ -277,10 +348,12 @@ int launch(cudaStream_t stream, const bf16* A, int64_t lda, bool a_kmajor, const
            int M, int N, int K, const Epi& epi, int bn_override = 0) {
     if (M <= 0 || N <= 0) return SAT_OK;
     SAT_REQUIRE(K > 0, "tcgen05 GEMM needs K > 0");
-    const int bn = bn_override ? bn_override : pick_bn(M, N, K, !b_kmajor);
-    if (a_kmajor && b_kmajor) return launch_mn<false, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
-    if (a_kmajor && !b_kmajor) return launch_mn<false, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
-    if (!a_kmajor && b_kmajor) return launch_mn<true, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
-    return launch_mn<true, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn);
+    int bn = 0, split = 1;
+    pick_tile(M, N, K, !b_kmajor, &bn, &split);
+    if (bn_override) { bn = bn_override; split = 1; }
+    if (a_kmajor && b_kmajor) return launch_mn<false, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
+    if (a_kmajor && !b_kmajor) return launch_mn<false, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
+    if (!a_kmajor && b_kmajor) return launch_mn<true, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
+    return launch_mn<true, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
 }
 }  // namespace tc

@@ -190,23 +190,52 @@ int sum_over_t_colsum(cudaStream_t s, T* out, const T* src, int64_t rows, int H,
     return SAT_OK;
 }
 
-// abar[b,d] = mean_l a[b,l,d]   (decoder.py:139 / :104)
+// abar[b,d] = mean_l a[b,l,d]   (decoder.py:139 / :104).  One pass over `a` (205 MB at c2): 16-byte loads, the L loop split
+// over blockIdx.z so that enough loads are in flight, partial sums combined with a second tiny pass when split.
 template <typename T>
-__global__ void mean_l_kernel(const T* __restrict__ a, float* __restrict__ out_f, T* __restrict__ out_t, int L, int D) {
-    const int b = blockIdx.y;
-    const int d = blockIdx.x * blockDim.x + threadIdx.x;
-    if (d >= D) return;
-    const T* p = a + (size_t)b * L * D + d;
-    float s = 0.0f;
-    for (int l = 0; l < L; ++l) s += to_f32<T>(p[(size_t)l * D]);
-    s /= (float)L;
-    if (out_f) out_f[(size_t)b * D + d] = s;
-    if (out_t) out_t[(size_t)b * D + d] = from_f32<T>(s);
+__global__ void mean_l_kernel(const T* __restrict__ a, float* __restrict__ part, int L, int D, int lsplit) {
+    constexpr int VEC = Vec16<T>::N;
+    const int b = blockIdx.y, z = blockIdx.z;
+    const int dv = blockIdx.x * blockDim.x + threadIdx.x;          // 16-byte column group
+    if (dv * VEC >= D) return;
+    const int l0 = (int)((int64_t)L * z / lsplit), l1 = (int)((int64_t)L * (z + 1) / lsplit);
+    const T* p = a + (size_t)b * L * D + (size_t)dv * VEC;
+    float acc[VEC];
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) acc[k] = 0.0f;
+#pragma unroll 4
+    for (int l = l0; l < l1; ++l) {
+        float f[VEC];
+        Vec16<T>::unpack(ldg_stream16(p + (size_t)l * D), f);
+#pragma unroll
+        for (int k = 0; k < VEC; ++k) acc[k] += f[k];
+    }
+    float* o = part + ((size_t)z * gridDim.y + b) * D + (size_t)dv * VEC;
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) o[k] = acc[k];
 }
 template <typename T>
-int mean_l(cudaStream_t s, const T* a, float* out_f, T* out_t, int B, int L, int D) {
-    dim3 grid(sat_cdiv(D, 128), B);
-    mean_l_kernel<T><<<grid, 128, 0, s>>>(a, out_f, out_t, L, D);
+__global__ void mean_l_final_kernel(const float* __restrict__ part, float* __restrict__ out_f, T* __restrict__ out_t, int64_t n, int lsplit, float inv_l) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float s = 0.0f;
+    for (int z = 0; z < lsplit; ++z) s += part[(size_t)z * n + i];
+    s *= inv_l;
+    if (out_f) out_f[i] = s;
+    if (out_t) out_t[i] = from_f32<T>(s);
+}
+// scratch: lsplit * B * D floats
+template <typename T>
+int mean_l(cudaStream_t s, const T* a, float* out_f, T* out_t, int B, int L, int D, float* scratch, int64_t scratch_floats) {
+    constexpr int VEC = Vec16<T>::N;
+    SAT_REQUIRE(D % VEC == 0, "mean_l: D must be a multiple of %d", VEC);
+    int lsplit = 4;
+    while (lsplit > 1 && ((int64_t)lsplit * B * D > scratch_floats || lsplit > L)) lsplit /= 2;
+    SAT_REQUIRE((int64_t)lsplit * B * D <= scratch_floats, "mean_l: scratch too small");
+    dim3 grid(sat_cdiv(D / VEC, 128), B, lsplit);
+    mean_l_kernel<T><<<grid, 128, 0, s>>>(a, scratch, L, D, lsplit);
+    const int64_t n = (int64_t)B * D;
+    mean_l_final_kernel<T><<<(int)sat_cdiv64(n, 256), 256, 0, s>>>(scratch, out_f, out_t, n, lsplit, 1.0f / (float)L);
     SAT_CHECK_CUDA(cudaGetLastError());
     return SAT_OK;
 }

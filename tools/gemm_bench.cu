@@ -8,6 +8,7 @@
 #include "../show-attend-and-tell_b200/csrc/sat_epilogue.cuh"
 
 int g_pdl = 1;
+int g_gemm_max_split = 4;
 void sat_set_error(const char* fmt, ...) { va_list ap; va_start(ap, fmt); vfprintf(stderr, fmt, ap); va_end(ap); fprintf(stderr, "\n"); }
 #define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { fprintf(stderr, "%s:%d %s\n", __FILE__, __LINE__, cudaGetErrorString(e)); exit(1); } } while (0)
 
@@ -28,6 +29,7 @@ struct Shape { const char* name; int M, N, K; bool b_kmajor; bool out_bf16; };
 int main(int argc, char** argv) {
     const int iters = argc > 1 ? atoi(argv[1]) : 50;
     if (getenv("SAT_PDL")) g_pdl = atoi(getenv("SAT_PDL"));
+    if (getenv("SAT_MAXSPLIT")) g_gemm_max_split = atoi(getenv("SAT_MAXSPLIT"));
     const Shape shapes[] = {
         {"UF   = h [U;f_beta]^T        ", 256, 2560, 512, true},
         {"gates= [z|h] W_gzh^T         ", 256, 2048, 2560, true},
