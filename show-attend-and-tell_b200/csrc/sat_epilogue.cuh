@@ -26,6 +26,7 @@ struct EpiLinear {
     __device__ __forceinline__ void apply(int m, int n0, const float* acc) const {
         if (m >= M) return;
         const int64_t mo = remapT > 0 ? (int64_t)(m % remapB) * remapT + m / remapB : (int64_t)m;
+        uint2 pend = make_uint2(0u, 0u);
 #pragma unroll
         for (int q = 0; q < NV / 4; ++q) {
             const int n = n0 + 4 * q;
@@ -61,7 +62,11 @@ struct EpiLinear {
                     } else {
                         __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
                         uint2 u = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
-                        *reinterpret_cast<uint2*>(reinterpret_cast<bf16*>(Ct) + mo * ldct + n) = u;
+                        bf16* dst = reinterpret_cast<bf16*>(Ct) + mo * ldct + n;
+                        // 16-byte stores: an even group of four waits for its odd neighbour (n0 is a multiple of 8)
+                        if (NV >= 8 && (q & 1) == 0 && n + 8 <= N) { pend = u; continue; }
+                        if (NV >= 8 && (q & 1) == 1) *reinterpret_cast<uint4*>(dst - 4) = make_uint4(pend.x, pend.y, u.x, u.y);
+                        else *reinterpret_cast<uint2*>(dst) = u;
                     }
                 }
             } else {

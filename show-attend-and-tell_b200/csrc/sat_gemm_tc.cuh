@@ -20,8 +20,17 @@ constexpr int NPROD = SAT_GEMM_NPROD;
 }  // namespace tc
 extern int g_gemm_max_split;    // tuning knob (sat_set_gemm_splitk): largest split-K cluster size, 1 = never split
 namespace tc {
-// warp0 = TMA producer 0, warp1 = TMEM alloc + MMA issuer, warps 2-5 = epilogue, warps 6.. = further TMA producers
-constexpr int THREADS = 192 + 32 * (NPROD - 1);
+#ifndef SAT_GEMM_EPI_GROUPS
+#define SAT_GEMM_EPI_GROUPS 4
+#endif
+// A warp keeps only a few global stores in flight (~2 GB/s per warp measured: with four epilogue warps the stores were
+// 50-80% of the large GEMMs, profiles/r1_gemm_harness_epilogue_store_cost.txt), so the accumulator is drained by EPI_GROUPS
+// groups of four warps (a warp may only touch the TMEM lane quarter warp % 4); the groups split the tile's columns.
+constexpr int EPI_GROUPS = SAT_GEMM_EPI_GROUPS;
+constexpr int EPI_WARPS = 4 * EPI_GROUPS;
+constexpr int PROD_WARP0 = 2 + EPI_WARPS;      // first extra producer warp
+// warp0 = TMA producer 0, warp1 = TMEM alloc + MMA issuer, warps 2 .. 2+EPI_WARPS-1 = epilogue, then further TMA producers
+constexpr int THREADS = 32 * (2 + EPI_WARPS + (NPROD - 1));
 
 template <int BN> struct Cfg {
     static constexpr int STAGES = (BN <= 128) ? 6 : 4;      // multiple of NPROD: a stage always has the same producer
@@ -52,6 +61,27 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
+    uint32_t r[8];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
     uint32_t r[32];
@@ -120,9 +150,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     pdl_launch_dependents();
 
     static_assert(C::STAGES % NPROD == 0, "a stage must always be filled by the same producer");
-    if (warp == 0 || warp >= 6) {
+    if (warp == 0 || warp >= PROD_WARP0) {
         if (elect_one()) {
-            for (int kb = (warp == 0 ? 0 : warp - 5); kb < nk; kb += NPROD) {
+            for (int kb = (warp == 0 ? 0 : warp - PROD_WARP0 + 1); kb < nk; kb += NPROD) {
                 const int s = kb % C::STAGES;
                 const uint32_t ph = (kb / C::STAGES) & 1;
                 mbar_wait(&empty_bar[s], ph ^ 1);
@@ -173,14 +203,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
         const int m = m0 + q * 32 + lane;
+        const int grp = (warp - 2) >> 2;             // epilogue group of this warp
         if constexpr (SPLIT == 1) {
+            constexpr int NC = BN / 32;
+            if constexpr (NC >= EPI_GROUPS) {        // whole 32-column chunks, dealt round-robin to the groups
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                float v[32];
-                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v);
-                if (n0 + c * 32 < N) epi.template apply<32>(m, n0 + c * 32, v);
+                for (int c = grp; c < NC; c += EPI_GROUPS) {
+                    float v[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v);
+                    if (n0 + c * 32 < N) epi.template apply<32>(m, n0 + c * 32, v);
+                }
+            } else {                                 // narrow tile: each group takes BN / EPI_GROUPS columns
+                constexpr int W = BN / EPI_GROUPS;
+                static_assert(W == 8 || W == 16, "narrow tiles are split into 8- or 16-column pieces");
+                float v[W];
+                const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(grp * W);
+                if constexpr (W == 16) tmem_ld16(ta, v); else tmem_ld8(ta, v);
+                if (n0 + grp * W < N) epi.template apply<W>(m, n0 + grp * W, v);
             }
-        } else {
+        } else if (grp == 0) {
             constexpr int CW = BN / SPLIT;           // columns this CTA finishes
             static_assert(CW % 4 == 0 && BN <= 64, "split-K tiles are at most 64 wide and split into multiples of 4 columns");
             float v[BN];
@@ -215,7 +256,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         }
     }
     if constexpr (SPLIT > 1) {
-        if (warp < 2 || warp >= 6) {                 // the non-epilogue warps take part in both cluster barriers too
+        if (warp < 2 || warp >= 6) {                 // all other warps take part in both cluster barriers too
             __syncwarp();
             cluster_wait_acquire();
             cluster_arrive_release();
