@@ -37,9 +37,7 @@ template <int BN> struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int XBUF_OFF = STAGES * STAGE_BYTES + 256;            // split-K exchange buffer: BM x BN fp32
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
-    static constexpr int SMEM_BYTES_SPLIT = SMEM_BYTES + BM * BN * 4;
 };
 
 __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
@@ -143,7 +141,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    if constexpr (SPLIT > 1) cluster_arrive_release();     // #1 (waited on before the exchange): every CTA of the cluster runs
+    if constexpr (SPLIT > 1) {                             // cluster barrier #1: the epilogue warps arrive once the accumulator is done
+        if (warp < 2 || warp >= PROD_WARP0) cluster_arrive_release();
+    }
     // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) overlapped the previous
     // kernel's tail; its results are needed from here on.  Let the next kernel start its own prologue right away.
     pdl_wait();
@@ -151,27 +151,25 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
 
     static_assert(C::STAGES % NPROD == 0, "a stage must always be filled by the same producer");
     if (warp == 0 || warp >= PROD_WARP0) {
-        if (elect_one()) {
-            for (int kb = (warp == 0 ? 0 : warp - PROD_WARP0 + 1); kb < nk; kb += NPROD) {
-                const int s = kb % C::STAGES;
-                const uint32_t ph = (kb / C::STAGES) & 1;
-                mbar_wait(&empty_bar[s], ph ^ 1);
-                mbar_expect_tx(&full_bar[s], C::STAGE_BYTES);
-                uint8_t* a_dst = sA + s * C::A_BYTES;
-                uint8_t* b_dst = sB + s * C::B_BYTES;
-                const int k0 = (kb0 + kb) * BK;
-                if (!A_MN) {
-                    tma_load_2d(a_dst, &mapA, k0, m0, &full_bar[s]);
-                } else {
-#pragma unroll
-                    for (int c = 0; c < BM / 64; ++c) tma_load_2d(a_dst + c * (BK * 128), &mapA, m0 + c * 64, k0, &full_bar[s]);
-                }
-                if (!B_MN) {
-                    tma_load_2d(b_dst, &mapB, k0, n0, &full_bar[s]);
-                } else {
-#pragma unroll
-                    for (int c = 0; c < BN / 64; ++c) tma_load_2d(b_dst + c * (BK * 128), &mapB, n0 + c * 64, k0, &full_bar[s]);
-                }
+        // An MN-major operand arrives as 64-column boxes (128-byte swizzle span), up to six copies per stage; one thread
+        // can only start a copy every ~60 ns, so lane b of the producer warp issues box b of the stage.
+        constexpr int A_BOXES = A_MN ? BM / 64 : 1, B_BOXES = B_MN ? BN / 64 : 1;
+        for (int kb = (warp == 0 ? 0 : warp - PROD_WARP0 + 1); kb < nk; kb += NPROD) {
+            const int s = kb % C::STAGES;
+            const uint32_t ph = (kb / C::STAGES) & 1;
+            mbar_wait(&empty_bar[s], ph ^ 1);
+            if (lane == 0) mbar_expect_tx(&full_bar[s], C::STAGE_BYTES);
+            __syncwarp();
+            uint8_t* a_dst = sA + s * C::A_BYTES;
+            uint8_t* b_dst = sB + s * C::B_BYTES;
+            const int k0 = (kb0 + kb) * BK;
+            if (lane < A_BOXES) {
+                if (!A_MN) tma_load_2d(a_dst, &mapA, k0, m0, &full_bar[s]);
+                else tma_load_2d(a_dst + lane * (BK * 128), &mapA, m0 + lane * 64, k0, &full_bar[s]);
+            } else if (lane < A_BOXES + B_BOXES) {
+                const int c = lane - A_BOXES;
+                if (!B_MN) tma_load_2d(b_dst, &mapB, k0, n0, &full_bar[s]);
+                else tma_load_2d(b_dst + c * (BK * 128), &mapB, n0 + c * 64, k0, &full_bar[s]);
             }
         }
     } else if (warp == 1) {
@@ -221,42 +219,58 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
                 if constexpr (W == 16) tmem_ld16(ta, v); else tmem_ld8(ta, v);
                 if (n0 + grp * W < N) epi.template apply<W>(m, n0 + grp * W, v);
             }
-        } else if (grp == 0) {
+        } else {
+            // Exchange buffer [SPLIT][BM][XP] fp32 ALIASES the operand stages: a CTA signals barrier #1 only after its own
+            // accumulator is complete (all its MMAs have read their stages), so once #1 completes every peer's stages are dead.
             constexpr int CW = BN / SPLIT;           // columns this CTA finishes
-            static_assert(CW % 4 == 0 && BN <= 64, "split-K tiles are at most 64 wide and split into multiples of 4 columns");
-            float v[BN];
-#pragma unroll
-            for (int c = 0; c < BN / 32; ++c) tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(c * 32), v + 32 * c);
-            float* xbuf = reinterpret_cast<float*>(smem + C::XBUF_OFF);       // [SPLIT][BM][CW]
+            constexpr int XP = CW + 4;               // padded row pitch: float4 accesses of 8 consecutive rows hit distinct banks
+            constexpr int PW0 = (BN / EPI_GROUPS > 8) ? BN / EPI_GROUPS : 8;
+            constexpr int PW = (PW0 > CW ? CW : PW0) > 32 ? 32 : (PW0 > CW ? CW : PW0);      // scatter piece: 8, 16 or 32 columns
+            constexpr int RW0 = (CW / EPI_GROUPS > 4) ? CW / EPI_GROUPS : 4;
+            constexpr int RW = RW0 > 32 ? 32 : RW0;                                            // reduce piece: 4 .. 32 columns
+            static_assert(PW == 8 || PW == 16 || PW == 32, "scatter pieces are 8, 16 or 32 columns");
+            static_assert(CW % PW == 0 && CW % RW == 0 && RW % 4 == 0, "column slices must divide evenly");
+            static_assert(SPLIT * BM * XP * 4 <= C::STAGES * C::STAGE_BYTES, "exchange buffer must fit in the stage ring");
+            float* xbuf = reinterpret_cast<float*>(smem);
             const int row = q * 32 + lane;
             __syncwarp();
-            cluster_wait_acquire();                  // #1
+            cluster_arrive_release();                // #1: my accumulator is complete, my stages may be overwritten
+            cluster_wait_acquire();
+#pragma unroll 1
+            for (int p = grp; p < BN / PW; p += EPI_GROUPS) {
+                float v[PW];
+                const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(p * PW);
+                if constexpr (PW == 32) tmem_ld32(ta, v); else if constexpr (PW == 16) tmem_ld16(ta, v); else tmem_ld8(ta, v);
+                const int col = p * PW;
+                const uint32_t dst = dsmem_addr(xbuf + ((size_t)zsp * BM + row) * XP + (col % CW), (uint32_t)(col / CW));
 #pragma unroll
-            for (int j = 0; j < SPLIT; ++j) {
-                const uint32_t dst = dsmem_addr(xbuf + ((size_t)zsp * BM + row) * CW, (uint32_t)j);
-#pragma unroll
-                for (int c4 = 0; c4 < CW / 4; ++c4)
-                    dsmem_st_f32x4(dst + 16 * c4, v[j * CW + 4 * c4], v[j * CW + 4 * c4 + 1], v[j * CW + 4 * c4 + 2], v[j * CW + 4 * c4 + 3]);
+                for (int c4 = 0; c4 < PW / 4; ++c4)
+                    dsmem_st_f32x4(dst + 16 * c4, v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
             }
+            __syncwarp();
             cluster_arrive_release();                // #2: my slices are in every peer's buffer ...
             cluster_wait_acquire();                  //     ... and every peer's slices are in mine
-            float acc[CW];
+#pragma unroll 1
+            for (int r = grp; r < CW / RW; r += EPI_GROUPS) {
+                float acc[RW];
 #pragma unroll
-            for (int i = 0; i < CW; ++i) acc[i] = 0.0f;
+                for (int i = 0; i < RW; ++i) acc[i] = 0.0f;
 #pragma unroll
-            for (int sp = 0; sp < SPLIT; ++sp) {
-                const float4* src = reinterpret_cast<const float4*>(xbuf + ((size_t)sp * BM + row) * CW);
+                for (int sp = 0; sp < SPLIT; ++sp) {                 // fixed order: deterministic
+                    const float4* src = reinterpret_cast<const float4*>(xbuf + ((size_t)sp * BM + row) * XP + r * RW);
 #pragma unroll
-                for (int c4 = 0; c4 < CW / 4; ++c4) {
-                    const float4 t = src[c4];
-                    acc[4 * c4] += t.x; acc[4 * c4 + 1] += t.y; acc[4 * c4 + 2] += t.z; acc[4 * c4 + 3] += t.w;
+                    for (int c4 = 0; c4 < RW / 4; ++c4) {
+                        const float4 t = src[c4];
+                        acc[4 * c4] += t.x; acc[4 * c4 + 1] += t.y; acc[4 * c4 + 2] += t.z; acc[4 * c4 + 3] += t.w;
+                    }
                 }
+                const int n = n0 + zsp * CW + r * RW;
+                if (n < N) epi.template apply<RW>(m, n, acc);
             }
-            if (n0 + zsp * CW < N) epi.template apply<CW>(m, n0 + zsp * CW, acc);
         }
     }
     if constexpr (SPLIT > 1) {
-        if (warp < 2 || warp >= 6) {                 // all other warps take part in both cluster barriers too
+        if (warp < 2 || warp >= PROD_WARP0) {        // the other warps (arrived at #1 after setup) take part in both barriers too
             __syncwarp();
             cluster_wait_acquire();
             cluster_arrive_release();
@@ -309,7 +323,7 @@ inline int make_map(CUtensorMap* map, const void* ptr, uint64_t inner, uint64_t 
 template <int BN, bool A_MN, bool B_MN, typename Epi, int SPLIT>
 int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB, int M, int N, int K, const Epi& epi) {
     auto kern = gemm_kernel<BN, A_MN, B_MN, Epi, SPLIT>;
-    constexpr int smem = SPLIT > 1 ? Cfg<BN>::SMEM_BYTES_SPLIT : Cfg<BN>::SMEM_BYTES;
+    constexpr int smem = Cfg<BN>::SMEM_BYTES;
     static bool configured = false;
     if (!configured) {
         SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -328,11 +342,11 @@ int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB,
     return SAT_OK;
 }
 
-// Tile width and split-K factor.  Measured on B200 (tools/gemm_bench.cu): a launch costs ~4.3 us however small it is and
-// every k-block adds ~0.155 us per 20 KB stage in every wave of CTAs (one SM pulls ~130 GB/s out of L2) -- so the model
-// is  waves x (fixed + exchange + k-blocks per CTA x stage bytes).  It keeps the per-step skinny GEMMs (M = batch) in ONE
-// wave of <= #SMs CTAs and splits K over a cluster when the tiles alone would leave most SMs idle; ties go to the wider
-// tile (less A re-reading).
+// Tile width and split-K factor from a cost model fitted to tools/gemm_bench.cu on B200 (profiles/r1_gemm_harness_*.txt), in
+// units of ~6.5 ns:  waves x (launch 560 + exchange [150 + BN x split] + drain 2.4 x BN / split + k-blocks per CTA x kb(BN)),
+// kb = 20 / 24 / 26 / 48 for BN = 32 / 64 / 128 / 256 (0.155 us is the floor of a k-block up to BN = 128).  It keeps the per-step
+// skinny GEMMs (M = batch) in ONE wave of <= #SMs CTAs, splits K over a cluster when the tiles alone would leave most SMs idle
+// (dh: 16 tiles x 40 k-blocks; dW_att: 64 tiles x 784 k-blocks) and takes the widest tile that does not add a wave otherwise.
 inline void pick_tile(int M, int N, int K, bool b_mn, int* bn_out, int* split_out) {
     static int sms = 0;
     if (!sms) {
@@ -348,11 +362,12 @@ inline void pick_tile(int M, int N, int K, bool b_mn, int* bn_out, int* split_ou
         if (b_mn && bn < 64) continue;
         if (bn > 32 && bn / 2 >= N && !(b_mn && bn == 64)) continue;   // tile far wider than N
         const long long tiles = (long long)mt * sat_cdiv(N, bn);
-        const double stage_kb = 16.0 + bn / 8.0;
-        for (int split = 1; split <= 8 && split <= g_gemm_max_split; split *= 2) {
-            if (split > 1 && (bn != 64 || tiles * split > sms || nk / split < 4)) continue;
+        const double stage_kb = bn == 256 ? 48.0 : bn == 128 ? 26.0 : bn == 64 ? 24.0 : 20.0;
+        for (int split = 1; split <= 4 && split <= g_gemm_max_split; split *= 2) {
+            if (split > 1 && (bn < 64 || tiles * split > sms || nk / split < 4)) continue;
             const double waves = (double)((tiles * split + sms - 1) / sms);
-            const double cost = waves * (28.0 * 20.0 + (split > 1 ? 130.0 : 0.0) + sat_cdiv(nk, split) * stage_kb);
+            const double cost = waves * (560.0 + (split > 1 ? 150.0 + (double)bn * split : 0.0) + 2.4 * bn / split +
+                                         sat_cdiv(nk, split) * stage_kb);
             if (cost < best_cost * 0.999) { best_cost = cost; best = bn; best_split = split; }
         }
     }
@@ -368,30 +383,32 @@ int launch_mn(cudaStream_t stream, const bf16* A, int64_t lda, const bf16* B, in
     const int box_n = bn;
     if (!B_MN) SAT_TRY(make_map(&mB, B, K, N, ldb, 64, box_n));
     else       SAT_TRY(make_map(&mB, B, N, K, ldb, 64, BK));
+#define SAT_TC_SPLITS(BN_)                                                                                     \
+        case BN_:                                                                                              \
+            if (split == 4) return launch_bn<BN_, A_MN, B_MN, Epi, 4>(stream, mA, mB, M, N, K, epi);           \
+            if (split == 2) return launch_bn<BN_, A_MN, B_MN, Epi, 2>(stream, mA, mB, M, N, K, epi);           \
+            return launch_bn<BN_, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
     switch (bn) {
-        case 256: return launch_bn<256, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
-        case 128: return launch_bn<128, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
-        case 64:
-            if (split == 8) return launch_bn<64, A_MN, B_MN, Epi, 8>(stream, mA, mB, M, N, K, epi);
-            if (split == 4) return launch_bn<64, A_MN, B_MN, Epi, 4>(stream, mA, mB, M, N, K, epi);
-            if (split == 2) return launch_bn<64, A_MN, B_MN, Epi, 2>(stream, mA, mB, M, N, K, epi);
-            return launch_bn<64, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
+        SAT_TC_SPLITS(256)
+        SAT_TC_SPLITS(128)
+        SAT_TC_SPLITS(64)
         case 32:
             if constexpr (!B_MN) return launch_bn<32, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
         default: break;
     }
+#undef SAT_TC_SPLITS
     sat_set_error("bad BN %d", bn);
     return SAT_ERR_ARG;
 }
 
 template <typename Epi>
 int launch(cudaStream_t stream, const bf16* A, int64_t lda, bool a_kmajor, const bf16* B, int64_t ldb, bool b_kmajor,
-           int M, int N, int K, const Epi& epi, int bn_override = 0) {
+           int M, int N, int K, const Epi& epi, int bn_override = 0, int split_override = 0) {
     if (M <= 0 || N <= 0) return SAT_OK;
     SAT_REQUIRE(K > 0, "tcgen05 GEMM needs K > 0");
     int bn = 0, split = 1;
     pick_tile(M, N, K, !b_kmajor, &bn, &split);
-    if (bn_override) { bn = bn_override; split = 1; }
+    if (bn_override) { bn = bn_override; split = split_override > 0 ? split_override : 1; }
     if (a_kmajor && b_kmajor) return launch_mn<false, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
     if (a_kmajor && !b_kmajor) return launch_mn<false, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
     if (!a_kmajor && b_kmajor) return launch_mn<true, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);

@@ -24,7 +24,7 @@ __global__ void checksum_f32(const float* x, size_t n, double* out) {
     atomicAdd(out, acc);
 }
 
-struct Shape { const char* name; int M, N, K; bool b_kmajor; bool out_bf16; int ldc; };
+struct Shape { const char* name; int M, N, K; bool b_kmajor; bool out_bf16; int ldc; bool a_mn; };
 
 int main(int argc, char** argv) {
     const int iters = argc > 1 ? atoi(argv[1]) : 50;
@@ -37,6 +37,8 @@ int main(int argc, char** argv) {
         {"dh   = dUF w_uf     (B MN)   ", 256, 512, 2560, false},
         {"c1 UF (B=32)                 ", 32, 1024, 512, true},
         {"Wa   = a W^T (K1), bf16 out  ", 50176, 512, 2048, true, true},
+        {"dW_att = dWa^T a (A,B MN)    ", 512, 2048, 50176, false, false, 0, true},
+        {"dW_gzh = dG^T ZH (A,B MN)    ", 2048, 2560, 5120, false, false, 0, true},
         {"logits = Hdrop W_out^T, ld=V ", 5120, 2531, 512, true},
         {"logits, ld=Vp (train path)   ", 5120, 2531, 512, true, false, 2536},
         {"probe: one tile, one k-block ", 128, 32, 64, true},
@@ -60,8 +62,10 @@ int main(int argc, char** argv) {
         if (s.out_bf16) { e.Ct = reinterpret_cast<bf16*>(C); e.ldct = ldc; } else { e.Cf = C; e.ldcf = ldc; }
         e.M = s.M; e.N = s.N; e.vec_ok = (ldc % 8 == 0);
         const int64_t ldb = s.b_kmajor ? s.K : s.N;
+        const int64_t lda = s.a_mn ? s.M : s.K;
         const int bn_over = getenv("SAT_BN") ? atoi(getenv("SAT_BN")) : 0;
-        auto run = [&]() { if (tc::launch(0, A, s.K, true, B, ldb, s.b_kmajor, s.M, s.N, s.K, e, bn_over) != 0) exit(2); };
+        const int sp_over = getenv("SAT_SPLIT") ? atoi(getenv("SAT_SPLIT")) : 0;
+        auto run = [&]() { if (tc::launch(0, A, lda, !s.a_mn, B, ldb, s.b_kmajor, s.M, s.N, s.K, e, bn_over, sp_over) != 0) exit(2); };
         for (int i = 0; i < 3; ++i) run();
         CK(cudaDeviceSynchronize());
         // (a) eager launches: includes the host cost of two tensor-map encodes + launch per call
@@ -73,7 +77,7 @@ int main(int argc, char** argv) {
         cudaStream_t st; CK(cudaStreamCreate(&st));
         cudaGraph_t g; cudaGraphExec_t ge;
         CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        for (int i = 0; i < iters; ++i) if (tc::launch(st, A, s.K, true, B, ldb, s.b_kmajor, s.M, s.N, s.K, e, bn_over) != 0) exit(2);
+        for (int i = 0; i < iters; ++i) if (tc::launch(st, A, lda, !s.a_mn, B, ldb, s.b_kmajor, s.M, s.N, s.K, e, bn_over, sp_over) != 0) exit(2);
         CK(cudaStreamEndCapture(st, &g));
         CK(cudaGraphInstantiate(&ge, g, 0));
         CK(cudaGraphLaunch(ge, st)); CK(cudaStreamSynchronize(st));
