@@ -39,48 +39,71 @@ def read_peaks():
 
 
 class ClockSampler:
-    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock + throttle reasons sampled DURING the timed regions.  NVML is polled from a thread every few ms (the timed
+    region is only tens of ms long, far below nvidia-smi's start-up time); `mark(True/False)` brackets the regions that count."""
+    REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4))
 
-    def __init__(self, index=0):
-        self.rows, self.proc, self.index = [], None, index
+    def __init__(self, dev):
+        self.rows, self.thread, self.handle, self.nv = [], None, None, None
+        self.stop_flag, self.active, self.err = False, False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            try:
+                uuid = str(torch.cuda.get_device_properties(dev).uuid)
+                if not uuid.startswith("GPU-"):
+                    uuid = "GPU-" + uuid
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+            except Exception:
+                vis = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+                idx = dev.index or 0
+                if vis and all(x.strip().isdigit() for x in vis.split(",")):
+                    idx = int(vis.split(",")[idx])
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+        except Exception as e:                                   # noqa: BLE001
+            self.err = f"nvml unavailable: {type(e).__name__}"
+            self.handle = None
+
+    def _poll(self):
+        nv, h = self.nv, self.handle
+        while not self.stop_flag:
+            try:
+                sm = float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+                try:
+                    rs = int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    rs = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                self.rows.append((self.active, sm, rs))
+            except Exception as e:                               # noqa: BLE001
+                self.err = f"nvml query failed: {type(e).__name__}"
+                return
+            time.sleep(0.002)
 
     def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+        if self.handle is not None:
+            self.thread = threading.Thread(target=self._poll, daemon=True)
             self.thread.start()
-        except Exception:
-            self.proc = None
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+    def mark(self, on):
+        self.active = on
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            if len(r) < 6:
-                continue
-            try:
-                sm.append(float(r[0])); mx.append(float(r[1]))
-            except ValueError:
-                continue
-            for n, v in zip(names, r[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.thread is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [self.err or "nvml unavailable"], "samples": 0}
+        self.stop_flag = True
+        self.thread.join(timeout=2)
+        rows = [r for r in self.rows if r[0]] or self.rows
+        sm = [r[1] for r in rows]
+        bits = 0
+        for r in rows:
+            bits |= r[2]
+        reasons = [n for n, b in self.REASONS if bits & b]
+        if self.err:
+            reasons.append(self.err)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": self.sm_max, "reasons": reasons,
+                "samples": len(sm), "sampled": "NVML polled every ~2 ms inside the timed regions (value + e2e)"}
 
 
 def make_host_batches(n, B, seed0=42):
@@ -186,18 +209,19 @@ def run_ours(args, rank, world, local_rank):
     # ---- device-resident throughput ("value") -----------------------------------------------------
     for i in range(args.warmup):
         trainer.step(*dev_batches[i % 2])
-    barrier()
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(dev)
     if rank == 0:
         sampler.start()
+    barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.mark(True)
     e0.record()
     for i in range(args.steps):
         loss = trainer.step(*dev_batches[i % 2])
     e1.record()
     barrier()
+    sampler.mark(False)
     ms_total = max_over_ranks(e0.elapsed_time(e1))
-    clocks = sampler.stop() if rank == 0 else None
     ms_step = ms_total / args.steps
     value = world * B / (ms_step / 1e3)
     loss_val = loss[2].item()
@@ -235,10 +259,13 @@ def run_ours(args, rank, world, local_rank):
 
     e2e_loop(max(2, args.warmup))
     barrier()
+    sampler.mark(True)
     e0.record()
     e2e_loop(args.steps)
     e1.record()
     barrier()
+    sampler.mark(False)
+    clocks = sampler.stop() if rank == 0 else None
     e2e_ms = max_over_ranks(e0.elapsed_time(e1)) / args.steps
     e2e_val = world * B / (e2e_ms / 1e3)
     h2d = host[0][0].numel() * host[0][0].element_size() + host[0][1].numel() * 8
