@@ -162,19 +162,28 @@ def run_reference(args, rank):
 
 
 def count_my_launches(fn):
-    """Kernel launches of ONE step, counted with the CUDA profiler (kineto); all kernels in a step are ours or NCCL's."""
+    """Kernel launches of ONE step, counted with the CUDA profiler (kineto); all kernels in a step are ours or NCCL's.
+    The same activity records give each attention kernel's EXPOSED time: from the later of (its own start, the end of the
+    kernel before it) to its end.  With programmatic dependent launch a kernel starts while its predecessor drains, so this
+    is what one launch adds to the step -- the CUDA-event brackets of the roofline section cannot overlap like that."""
     try:
         from torch.profiler import ProfilerActivity, profile
         with profile(activities=[ProfilerActivity.CUDA]) as prof:
             fn()
             torch.cuda.synchronize()
-        n = 0
-        for ev in prof.events():
-            if ev.device_type == torch.autograd.DeviceType.CUDA and "memcpy" not in ev.name.lower() and "memset" not in ev.name.lower():
-                n += 1
-        return n
+        evs = [ev for ev in prof.events() if ev.device_type == torch.autograd.DeviceType.CUDA
+               and "memcpy" not in ev.name.lower() and "memset" not in ev.name.lower()]
+        evs.sort(key=lambda e: e.time_range.start)
+        exposed, prev_end = {}, None
+        for ev in evs:
+            st, en = ev.time_range.start, ev.time_range.end
+            for key, tag in (("attn_step_fwd", "fwd_stream_kernel"), ("attn_step_bwd", "bwd_stream_kernel")):
+                if tag in ev.name and prev_end is not None:
+                    exposed.setdefault(key, []).append(en - max(st, prev_end))
+            prev_end = en if prev_end is None else max(prev_end, en)
+        return len(evs), {k: sum(v) / len(v) / 1e3 for k, v in exposed.items()}
     except Exception:
-        return None
+        return None, {}
 
 
 def run_ours(args, rank, world, local_rank):
@@ -185,6 +194,14 @@ def run_ours(args, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     L = _lib.lib()
+    if "SAT_DEC_SPLIT" in os.environ:                      # A/B switch for the half-batch pipelining (default on)
+        L.sat_set_decoder_split(int(os.environ["SAT_DEC_SPLIT"]))
+    if "SAT_TAIL" in os.environ:
+        L.sat_set_tail_overlap(int(os.environ["SAT_TAIL"]))
+    if "SAT_STATIC_W" in os.environ:
+        L.sat_set_gemm_static_weights(int(os.environ["SAT_STATIC_W"]))
+    if "SAT_SPLIT_SMS" in os.environ:                      # "attn_ctas,gemm_sms"
+        L.sat_set_decoder_split_sms(*[int(x) for x in os.environ["SAT_SPLIT_SMS"].split(",")])
     B, T = CFG["B"], CFG["T"]
     dec = Decoder(CFG["V"], CFG["D"], tf=True, ado=False, bert=False, attention=True, compute_dtype=torch.bfloat16)
     dec.load_state_dict(synth.make_params(CFG["V"], CFG["D"], CFG["H"], seed=42))
@@ -304,7 +321,20 @@ def run_ours(args, rank, world, local_rank):
                 "frac": kern[dom]["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
                 "share_of_step": kern[dom]["ms_per_step"] / ms_step, "kernels": kern}
 
-    launches = count_my_launches(lambda: trainer.step(*dev_batches[0]))
+    launches, exposed = count_my_launches(lambda: trainer.step(*dev_batches[0]))
+    for name, ems in exposed.items():
+        if name in kern:
+            kern[name]["exposed_avg_ms"] = ems
+            kern[name]["exposed_gbs"] = kern[name]["algorithmic_bytes"] / ems / 1e6
+    # host -> device bandwidth of the pinned feature batch alone (what bounds e2e when it exceeds the device step)
+    h2d_ev0, h2d_ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    h2d_ev0.record()
+    for _ in range(3):
+        bufs[0][0].copy_(host[0][0], non_blocking=True)
+    h2d_ev1.record()
+    torch.cuda.synchronize()
+    h2d_ms = h2d_ev0.elapsed_time(h2d_ev1) / 3
     if rank != 0:
         return
     cpu = None
@@ -322,7 +352,8 @@ def run_ours(args, rank, world, local_rank):
                        "l2": "inputs larger than L2 (a+Wa = 257 MB per step > 126 MB), two alternating batches",
                        "optimizer": "fused Adam inside the timed step", "dropout": "train mode (p=0.5)", "loss": loss_val},
             "clocks": clocks,
-            "e2e": {"value": e2e_val, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "e2e": {"value": e2e_val, "unit": UNIT, "ms_per_step": e2e_ms, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "h2d_alone_ms": h2d_ms, "h2d_alone_gbs": host[0][0].numel() * 2 / h2d_ms / 1e6},
             "gpu_launches": None if launches is None else launches * args.steps,
             "roofline": roofline, "cpu_baseline": cpu}
     print(json.dumps(line), flush=True)

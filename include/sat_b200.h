@@ -31,6 +31,20 @@ int sat_set_attn_partition(int mode);
 /* debug knob: 1 (default) = PDL-aware kernels are launched with programmatic stream serialization (their prologue overlaps
  * the previous kernel's tail), 0 = ordinary launches */
 int sat_set_pdl(int on);
+/* tuning knob: 1 (default) = the per-step GEMMs of the decoder loop load their weight operand with the L2 evict_last hint (it
+ * survives the attention kernel's 257 MB stream until the next step) and request its first tiles before the PDL wait */
+int sat_set_gemm_static_weights(int on);
+/* tuning knob: 1 (default) = sat_decoder_backward runs the work after the BPTT loop as two independent chains on two streams
+ * (sum over t + dW_att on the caller's stream, the small weight-gradient GEMMs / column sums on an internal side stream that
+ * is joined back before the call returns), 0 = one chain */
+int sat_set_tail_overlap(int on);
+/* tuning knob (default 0, see DESIGN.md for the measurements): 1 = sat_decoder_forward / sat_decoder_backward run the recurrent loop of a teacher-forced batch
+ * (B >= 128, streaming attention shapes) as two half-batches on two streams, so that one half's latency-bound skinny GEMMs
+ * overlap the other half's HBM-bound attention kernel; 0 = whole batch on the caller's stream */
+int sat_set_decoder_split(int on);
+/* tuning knob of the half-batch pipelining: the attention kernel of a half uses at most attn_ctas CTAs (0 = one per item up to
+ * the SM count) and the half's skinny GEMMs pick their tiles for gemm_sms SMs (0 = all) */
+int sat_set_decoder_split_sms(int attn_ctas, int gemm_sms);
 /* tuning knob: largest split-K cluster size a skinny GEMM may use (1 = never split, default 4, at most 8) */
 int sat_set_gemm_splitk(int max_split);
 /* tuning knob: L2 eviction hints of the streaming attention kernels' loads.  wa_fwd / wa_bwd: policy of the Wa rows in the

@@ -45,6 +45,7 @@ struct FwdParams {
     float* s_part;        // cross-CTA partial records (scratch)
     int static_inputs;    // a / wa were NOT written by the kernel launched just before this one: the producers may
                           // start streaming them before the programmatic-dependent-launch wait
+    int max_ctas;         // > 0: the grid uses at most this many CTAs (leaves SMs to kernels running beside it)
 };
 
 struct SmemLayout {
@@ -330,6 +331,7 @@ struct BwdParams {
     int first;              // first backward step: overwrite the accumulators
     int B, L, D, H, gate;
     int C, Lc, Ds, Hs, G2;
+    int max_ctas;         // > 0: the grid uses at most this many CTAs
 };
 
 struct BwdSmem {

@@ -885,15 +885,19 @@ inline int64_t scratch_bytes(int NI, int NB, int D, int H) {
 // counts cost less than the combine launch from ~1/4 of the SMs upwards, and from two items per SM the step is HBM-bound
 // anyway.  Tiny batches (single-image beam search) get equal slot counts, never a range shorter than 1/8 of an item
 // (bounds the pieces per item).
-inline Part pick_part(long long nitems, int spi, int slot_bytes, int ngroups, bool bwd, int* grid) {
-    const int sms = num_sms();
+inline Part pick_part(long long nitems, int spi, int slot_bytes, int ngroups, bool bwd, int* grid, int max_ctas = 0) {
+    int sms = num_sms();
+    const bool capped = max_ctas > 0 && max_ctas < sms;
+    if (capped) sms = max_ctas;
     Part pt;
     pt.tot = nitems * spi;
     // beam groups of one image re-read the image inside the launch: count each image's bytes once
     const double total_bytes = (double)pt.tot * slot_bytes / ngroups;
     pt.wa_hint = bwd ? g_attn_wa_hint_bwd : g_attn_wa_hint_fwd;
     pt.pin = (double)g_attn_pin_bytes >= total_bytes ? spi : (int)(spi * ((double)g_attn_pin_bytes / total_bytes));
-    const bool whole = g_attn_part == 1 || (g_attn_part == 0 && nitems * 4 >= (long long)sms);
+    bool whole = g_attn_part == 1 || (g_attn_part == 0 && nitems * 4 >= (long long)sms);
+    // a capped grid that the items do not fill evenly would leave some CTAs a whole item more than others
+    if (capped && g_attn_part == 0 && nitems > sms && nitems % sms != 0) whole = false;
     if (whole) {
         pt.align = spi;
         *grid = (int)(nitems < sms ? nitems : sms);
@@ -930,7 +934,7 @@ int launch_fwd_inst(const FwdParams& p, cudaStream_t stream) {
     SAT_REQUIRE(sl.nslots >= CWARPS && sl.total <= SMEM_MAX, "attention fwd (streaming): shared memory budget exceeded (L=%d)", p.L);
     const int ngroups = (p.NB + NBG - 1) / NBG, spi = (p.L + G::LS - 1) / G::LS;
     int grid = 1;
-    const Part pt = pick_part((long long)p.NI * ngroups, spi, G::SLOT, ngroups, false, &grid);
+    const Part pt = pick_part((long long)p.NI * ngroups, spi, G::SLOT, ngroups, false, &grid, p.max_ctas);
     SatProfScope prof(SAT_PROF_ATTN_FWD, stream);
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
@@ -989,7 +993,7 @@ int launch_bwd_inst(const BwdParams& p_in, cudaStream_t stream) {
     SAT_REQUIRE(sl.nslots >= CWARPS && sl.total <= SMEM_MAX, "attention bwd (streaming): shared memory budget exceeded (L=%d)", p.L);
     const int spi = (p.L + G::LS - 1) / G::LS;
     int grid = 1;
-    const Part pt = pick_part(p.B, spi, G::SLOT, 1, true, &grid);
+    const Part pt = pick_part(p.B, spi, G::SLOT, 1, true, &grid, p.max_ctas);
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
     pdl_config(&cfg, attr, dim3(grid), dim3(THREADS), sl.total, stream);

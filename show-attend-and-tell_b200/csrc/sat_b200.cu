@@ -4,11 +4,15 @@
 #include "sat_beam.cuh"
 
 int g_force_simt = 0;
+int g_gemm_static_b = 1;     // in-loop GEMMs: weights loaded with evict_last and requested before the PDL wait
 int g_attn_generic = 0;
 int g_attn_part = 0;
 long long g_attn_pin_bytes = 0;
 int g_attn_wa_hint_fwd = 1, g_attn_wa_hint_bwd = 0;
 int g_pdl = 1;
+int g_dec_split = 0;      // half-batch pipelining of the recurrent loop (sat_decoder.cuh)
+int g_split_attn_ctas = 0, g_split_gemm_sms = 0, g_split_chain = 1;
+int g_tail_overlap = 1;   // backward tail as two chains on two streams (sat_decoder.cuh)
 int g_gemm_max_split = 4;      // clusters of 8 launch slower than they save (tools/gemm_bench.cu)
 static thread_local char g_err[1024] = "";
 
@@ -73,6 +77,12 @@ int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes) {
 }
 int sat_set_gemm_splitk(int max_split) { g_gemm_max_split = max_split >= 1 ? max_split : 1; return SAT_OK; }
 int sat_set_pdl(int on) { g_pdl = on ? 1 : 0; return SAT_OK; }
+int sat_set_gemm_static_weights(int on) { g_gemm_static_b = on ? 1 : 0; return SAT_OK; }
+int sat_set_tail_overlap(int on) { g_tail_overlap = on ? 1 : 0; return SAT_OK; }
+int sat_set_decoder_split(int on) { g_dec_split = on ? 1 : 0; g_split_chain = on == 2 ? 0 : 1; return SAT_OK; }
+int sat_set_decoder_split_sms(int attn_ctas, int gemm_sms) {
+    g_split_attn_ctas = attn_ctas > 0 ? attn_ctas : 0; g_split_gemm_sms = gemm_sms > 0 ? gemm_sms : 0; return SAT_OK;
+}
 int sat_set_attn_partition(int mode) { g_attn_part = (mode == 1 || mode == 2) ? mode : 0; return SAT_OK; }
 
 /* profiling: sat_profile(1) starts recording CUDA-event pairs around attention-step and GEMM launches on their own

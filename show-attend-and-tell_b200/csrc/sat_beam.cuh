@@ -302,30 +302,32 @@ int beam_search_t(const sat_beam_args& a) {
     SAT_REQUIRE(a.workspace && a.workspace_bytes >= need, "beam workspace too small: %lld < %lld", (long long)a.workspace_bytes, (long long)need);
     const int NI = a.NI, L = a.L, D = a.D, H = a.H, V = a.V, NB = a.beam, R = NI * NB;
     const int64_t xw = 2 * (int64_t)H + D;
-    // ---- weights ----
+    // ---- weights (one launch) ----
+    misc::PackList<T> pl;
     if (a.attention) {
-        SAT_TRY(misc::pack_weight<T>(st, w.w_att, D, a.att_W_w, D, H, D, 0, 0));
-        SAT_TRY(misc::pack_weight<T>(st, w.w_uf, H, a.att_U_w, H, H, H, 0, 0));
-        SAT_TRY(misc::pack_weight<T>(st, w.w_uf + (size_t)H * H, H, a.f_beta_w, H, D, H, 0, 0));
-        SAT_TRY(misc::pack_bias(st, w.b_uf, a.att_U_b, nullptr, H, 0));
-        SAT_TRY(misc::pack_bias(st, w.b_uf + H, a.f_beta_b, nullptr, D, 0));
+        SAT_TRY(pl.weight(w.w_att, D, a.att_W_w, D, H, D, 0, 0));
+        SAT_TRY(pl.weight(w.w_uf, H, a.att_U_w, H, H, H, 0, 0));
+        SAT_TRY(pl.weight(w.w_uf + (size_t)H * H, H, a.f_beta_w, H, D, H, 0, 0));
+        SAT_TRY(pl.bias(w.b_uf, a.att_U_b, nullptr, H, 0));
+        SAT_TRY(pl.bias(w.b_uf + H, a.f_beta_b, nullptr, D, 0));
     }
-    SAT_TRY(misc::pack_weight<T>(st, w.w_gall, xw, a.lstm_w_ih, H + D, 4 * H, H + D, 0, H));      // cols [0,H+D): [emb | ctx]
-    SAT_TRY(misc::pack_weight<T>(st, w.w_gall + H + D, xw, a.lstm_w_hh, H, 4 * H, H, 0, H));      // cols [H+D, 2H+D): h
-    SAT_TRY(misc::pack_bias(st, w.b_g, a.lstm_b_ih, a.lstm_b_hh, 4 * H, H));
-    SAT_TRY(misc::pack_weight<T>(st, w.w_init, D, a.init_h_w, D, H, D, 0, 0));
-    SAT_TRY(misc::pack_weight<T>(st, w.w_init + (size_t)H * D, D, a.init_c_w, D, H, D, 0, 0));
-    SAT_TRY(misc::pack_bias(st, w.b_init, a.init_h_b, nullptr, H, 0));
-    SAT_TRY(misc::pack_bias(st, w.b_init + H, a.init_c_b, nullptr, H, 0));
+    SAT_TRY(pl.weight(w.w_gall, xw, a.lstm_w_ih, H + D, 4 * H, H + D, 0, H));      // cols [0,H+D): [emb | ctx]
+    SAT_TRY(pl.weight(w.w_gall + H + D, xw, a.lstm_w_hh, H, 4 * H, H, 0, H));      // cols [H+D, 2H+D): h
+    SAT_TRY(pl.bias(w.b_g, a.lstm_b_ih, a.lstm_b_hh, 4 * H, H));
+    SAT_TRY(pl.weight(w.w_init, D, a.init_h_w, D, H, D, 0, 0));
+    SAT_TRY(pl.weight(w.w_init + (size_t)H * D, D, a.init_c_w, D, H, D, 0, 0));
+    SAT_TRY(pl.bias(w.b_init, a.init_h_b, nullptr, H, 0));
+    SAT_TRY(pl.bias(w.b_init + H, a.init_c_b, nullptr, H, 0));
     const float* out_b = a.ado ? a.f_out_b : a.deep_b;
     if (a.ado) {
         SAT_REQUIRE(a.f_h_w && a.f_z_w && a.f_out_w, "ado=1 needs f_h/f_z/f_out parameters");
-        SAT_TRY(misc::pack_weight<T>(st, w.w_fh, H, a.f_h_w, H, H, H, 0, 0));
-        SAT_TRY(misc::pack_weight<T>(st, w.w_fz, D, a.f_z_w, D, H, D, 0, 0));
-        SAT_TRY(misc::pack_weight<T>(st, w.w_out, H, a.f_out_w, H, V, H, 0, 0));
+        SAT_TRY(pl.weight(w.w_fh, H, a.f_h_w, H, H, H, 0, 0));
+        SAT_TRY(pl.weight(w.w_fz, D, a.f_z_w, D, H, D, 0, 0));
+        SAT_TRY(pl.weight(w.w_out, H, a.f_out_w, H, V, H, 0, 0));
     } else {
-        SAT_TRY(misc::pack_weight<T>(st, w.w_out, H, a.deep_w, H, V, H, 0, 0));
+        SAT_TRY(pl.weight(w.w_out, H, a.deep_w, H, V, H, 0, 0));
     }
+    SAT_TRY(pl.flush(st));
     // ---- per-image precompute ----
     if (reinterpret_cast<const void*>(w.a_c) != a.img_features) {
         if (a.a_dtype == SAT_DTYPE_F32)

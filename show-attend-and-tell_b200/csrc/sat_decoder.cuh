@@ -10,23 +10,51 @@
 #include "sat_attn_stream.cuh"
 #include "sat_misc.cuh"
 
-extern int g_force_simt;
+extern int g_force_simt, g_gemm_static_b;
 
 template <typename T> struct IsF32 { static constexpr bool value = std::is_same<T, float>::value; };
 
 template <typename T, typename Epi>
 int gemm(cudaStream_t s, const T* A, int64_t lda, bool a_k, const T* B, int64_t ldb, bool b_k, int M, int N, int K,
-         const Epi& epi, int bn = 0) {
+         const Epi& epi, int bn = 0, int sm_budget = 0, int b_static = 0) {
     SatProfScope prof(SAT_PROF_GEMM, s);
     if constexpr (IsF32<T>::value) {
         return simt::launch<float, Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi);
     } else {
         if (g_force_simt) return simt::launch<bf16, Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi);
-        return tc::launch<Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi, bn);
+        return tc::launch<Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi, bn, 0, sm_budget, g_gemm_static_b ? b_static : 0);
     }
 }
 
 static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+
+// ---------------------------------------------------------------------------------------------------
+// Half-batch pipelining of the recurrent loop.  The decode steps of different captions never exchange data, so the
+// batch is cut into two halves that run the whole T-step loop on two streams: while one half's attention kernel
+// streams a / Wa out of HBM (memory-bound, one CTA per item), the other half's latency-bound skinny GEMMs (U h, gates,
+// dz, dh) run on the SMs the attention grid leaves free.  Everything outside the loop still sees the full (t, b) row
+// space; a half is only a row range [b0, b0 + nb) of every time-major slice.  The side stream and its two events are
+// created once per host thread and device; the caller's stream forks into it before the loop and joins after it.
+// ---------------------------------------------------------------------------------------------------
+extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap;
+struct SideStream { cudaStream_t s; cudaEvent_t fork, join, attn_done[2]; bool ok; };
+static inline int side_stream(SideStream** out) {
+    static thread_local SideStream cache[32] = {};
+    int dev = 0;
+    SAT_CHECK_CUDA(cudaGetDevice(&dev));
+    SAT_REQUIRE(dev >= 0 && dev < 32, "device index %d out of range", dev);
+    SideStream& ss = cache[dev];
+    if (!ss.ok) {
+        SAT_CHECK_CUDA(cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking));
+        SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming));
+        SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming));
+        SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.attn_done[0], cudaEventDisableTiming));
+        SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.attn_done[1], cudaEventDisableTiming));
+        ss.ok = true;
+    }
+    *out = &ss;
+    return SAT_OK;
+}
 
 template <typename T>
 EpiLinear<T, IsF32<T>::value> lin(int M, int N, const float* bias, int act, float* Cf, int64_t ldcf, T* Ct, int64_t ldct,
@@ -76,6 +104,7 @@ struct DecWs {
     T* dpre_all;     // (T,B,L,H)    streaming attention backward: each step's dpre written once
     float* Ctx32;    // (T,B,D)      fp32 un-gated context saved by the streaming forward kernel for its backward
     uint8_t* attn_scratch;   // streaming attention kernels: arrival counters + partial records
+    uint8_t* attn_scratch2;
     int64_t attn_scratch_bytes;
     bool attn_stream;
     T* dwa_t;        // (B,L,H)
@@ -85,6 +114,7 @@ struct DecWs {
     float* galpha;   // (B,T,L)
     float* gscratch;
     float* csum;
+    float* csum2;
     float* dcomb;    // ado (T,B,H) fp32
     T *dP1, *dP2;    // ado (T,B,H)
     float* dctx_all; // ado (T,B,D) fp32
@@ -116,6 +146,7 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
     w.attn_stream = a.attention && attn_s::fwd_shape_ok(1, a.L, a.D, a.H);
     w.attn_scratch_bytes = w.attn_stream ? attn_s::scratch_bytes(a.B, 1, a.D, a.H) : 0;
     TK(attn_scratch, w.attn_scratch_bytes, uint8_t);
+    TK(attn_scratch2, w.attn_scratch_bytes, uint8_t);      // second half of a split batch (half-batch pipelining)
     TK(Ctx32, (w.attn_stream && a.need_grad) ? B * Tn * D : 0, float);
     TK(abar, B * D, T); TK(abar_f, B * D, float); TK(mean_part, 4 * B * D, float);
     TK(E, B * Tn * H, T); TK(Xg, B * Tn * 4 * H, float); TK(UF, B * Tn * (H + D), float);
@@ -140,6 +171,7 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
         if (w.csum_floats < 64 * (H + D)) w.csum_floats = 64 * (H + D);
         if (w.csum_floats < (int64_t)4 * 148 * H) w.csum_floats = (int64_t)4 * 148 * H;      // sum_over_t_colsum: one row per block
         TK(csum, w.csum_floats, float);
+        TK(csum2, w.csum_floats, float);      // column-sum scratch of the side chain of the backward tail
         TK(dcomb, a.ado ? B * Tn * H : 0, float); TK(dP1, a.ado ? B * Tn * H : 0, T); TK(dP2, a.ado ? B * Tn * H : 0, T);
         TK(dctx_all, a.ado ? B * Tn * D : 0, float);
     }
@@ -166,31 +198,32 @@ static inline int check_args(const sat_decoder_args* a) {
 template <typename T>
 int prep_weights(const sat_decoder_args& a, DecWs<T>& w, cudaStream_t st) {
     const int D = a.D, H = a.H, V = a.V;
+    misc::PackList<T> pl;       // every packing job of the call goes out in one launch
     if (a.attention) {
-        SAT_TRY(misc::pack_weight<T>(st, w.w_att, D, a.att_W_w, D, H, D, 0, 0));
-        SAT_TRY(misc::pack_weight<T>(st, w.w_uf, H, a.att_U_w, H, H, H, 0, 0));                       // rows [0,H): U
-        SAT_TRY(misc::pack_weight<T>(st, w.w_uf + (size_t)H * H, H, a.f_beta_w, H, D, H, 0, 0));       // rows [H,H+D): f_beta
-        SAT_TRY(misc::pack_bias(st, w.b_uf, a.att_U_b, nullptr, H, 0));
-        SAT_TRY(misc::pack_bias(st, w.b_uf + H, a.f_beta_b, nullptr, D, 0));
+        SAT_TRY(pl.weight(w.w_att, D, a.att_W_w, D, H, D, 0, 0));
+        SAT_TRY(pl.weight(w.w_uf, H, a.att_U_w, H, H, H, 0, 0));                       // rows [0,H): U
+        SAT_TRY(pl.weight(w.w_uf + (size_t)H * H, H, a.f_beta_w, H, D, H, 0, 0));       // rows [H,H+D): f_beta
+        SAT_TRY(pl.bias(w.b_uf, a.att_U_b, nullptr, H, 0));
+        SAT_TRY(pl.bias(w.b_uf + H, a.f_beta_b, nullptr, D, 0));
     }
     // gate weights, rows interleaved (4j+g).  lstm.weight_ih columns: [0,H) embedding, [H,H+D) context.
-    SAT_TRY(misc::pack_weight<T>(st, w.w_gx, H, a.lstm_w_ih, H + D, 4 * H, H, 0, H));
-    SAT_TRY(misc::pack_weight<T>(st, w.w_gzh, D + H, a.lstm_w_ih, H + D, 4 * H, D, H, H));            // cols [0,D): context
-    SAT_TRY(misc::pack_weight<T>(st, w.w_gzh + D, D + H, a.lstm_w_hh, H, 4 * H, H, 0, H));            // cols [D,D+H): hidden
-    SAT_TRY(misc::pack_bias(st, w.b_g, a.lstm_b_ih, a.lstm_b_hh, 4 * H, H));
-    SAT_TRY(misc::pack_weight<T>(st, w.w_init, D, a.init_h_w, D, H, D, 0, 0));
-    SAT_TRY(misc::pack_weight<T>(st, w.w_init + (size_t)H * D, D, a.init_c_w, D, H, D, 0, 0));
-    SAT_TRY(misc::pack_bias(st, w.b_init, a.init_h_b, nullptr, H, 0));
-    SAT_TRY(misc::pack_bias(st, w.b_init + H, a.init_c_b, nullptr, H, 0));
+    SAT_TRY(pl.weight(w.w_gx, H, a.lstm_w_ih, H + D, 4 * H, H, 0, H));
+    SAT_TRY(pl.weight(w.w_gzh, D + H, a.lstm_w_ih, H + D, 4 * H, D, H, H));            // cols [0,D): context
+    SAT_TRY(pl.weight(w.w_gzh + D, D + H, a.lstm_w_hh, H, 4 * H, H, 0, H));            // cols [D,D+H): hidden
+    SAT_TRY(pl.bias(w.b_g, a.lstm_b_ih, a.lstm_b_hh, 4 * H, H));
+    SAT_TRY(pl.weight(w.w_init, D, a.init_h_w, D, H, D, 0, 0));
+    SAT_TRY(pl.weight(w.w_init + (size_t)H * D, D, a.init_c_w, D, H, D, 0, 0));
+    SAT_TRY(pl.bias(w.b_init, a.init_h_b, nullptr, H, 0));
+    SAT_TRY(pl.bias(w.b_init + H, a.init_c_b, nullptr, H, 0));
     if (a.ado) {
         SAT_REQUIRE(a.f_h_w && a.f_z_w && a.f_out_w, "ado=1 needs f_h/f_z/f_out parameters");
-        SAT_TRY(misc::pack_weight<T>(st, w.w_fh, H, a.f_h_w, H, H, H, 0, 0));
-        SAT_TRY(misc::pack_weight<T>(st, w.w_fz, D, a.f_z_w, D, H, D, 0, 0));
-        SAT_TRY(misc::pack_weight<T>(st, w.w_out, H, a.f_out_w, H, V, H, 0, 0));
+        SAT_TRY(pl.weight(w.w_fh, H, a.f_h_w, H, H, H, 0, 0));
+        SAT_TRY(pl.weight(w.w_fz, D, a.f_z_w, D, H, D, 0, 0));
+        SAT_TRY(pl.weight(w.w_out, H, a.f_out_w, H, V, H, 0, 0));
     } else {
-        SAT_TRY(misc::pack_weight<T>(st, w.w_out, H, a.deep_w, H, V, H, 0, 0));
+        SAT_TRY(pl.weight(w.w_out, H, a.deep_w, H, V, H, 0, 0));
     }
-    return SAT_OK;
+    return pl.flush(st);
 }
 
 // output layer for steps [t0, t0+nt): nt == T (teacher forcing: one GEMM over all (t,b) rows) or nt == 1.
@@ -223,6 +256,12 @@ int output_layer(const sat_decoder_args& a, DecWs<T>& w, cudaStream_t st, int t0
     auto e3 = lin<T>(M, V, a.f_out_b, SAT_ACT_RELU, logits, ldl, nullptr, 0);
     set_out(e3);
     return gemm<T>(st, cb, H, true, w.w_out, H, true, M, V, H, e3);
+}
+
+// 2 when the recurrent loop runs as two half-batches on two streams (see SideStream above), else 1
+template <typename T>
+inline int dec_split(const sat_decoder_args& a, const DecWs<T>& w) {
+    return (g_dec_split && a.tf && a.attention && w.attn_stream && a.B >= 128 && a.B % 16 == 0) ? 2 : 1;
 }
 
 template <typename T>
@@ -274,43 +313,67 @@ int decoder_forward_t(const sat_decoder_args& a) {
         misc::fill_tokens_kernel<<<sat_cdiv(B, 128), 128, 0, st>>>(w.tok_in, B, (int64_t)a.start_token);
         SAT_CHECK_CUDA(cudaGetLastError());
     }
+    // one decode step for the captions [b0, b0 + nb) on stream s
+    auto fwd_step = [&](int t, int b0, int nb, cudaStream_t s, uint8_t* scratch, cudaEvent_t wait_ev, cudaEvent_t rec_ev) -> int {
+        const int gsm = nb < B ? g_split_gemm_sms : 0, actas = nb < B ? g_split_attn_ctas : 0;
+        T* zh_t = w.ZH + ((size_t)t * B + b0) * zw;
+        if (a.attention) {
+            float* uf_t = w.UF + ((size_t)t * B + b0) * (H + D);
+            auto e = lin<T>(nb, H + D, w.b_uf, SAT_ACT_NONE, uf_t, H + D, nullptr, 0);
+            SAT_TRY(gemm<T>(s, zh_t + D, zw, true, w.w_uf, H, true, nb, H + D, H, e, 0, gsm, 1));       // [U h | f_beta h]
+            attn::FwdParams p;
+            memset(&p, 0, sizeof(p));
+            p.a = w.a_c + (size_t)b0 * L * D; p.wa = w.wa + (size_t)b0 * L * H;
+            p.uf = uf_t; p.ld_uf = H + D; p.v = a.att_v_w; p.bv = a.att_v_b;
+            p.alpha = a.alphas + ((size_t)b0 * Tn + t) * L; p.ld_alpha = (int64_t)Tn * L;
+            p.ctx = w.Ctx + ((size_t)t * B + b0) * D; p.ld_ctx = D;
+            p.z = zh_t; p.ld_z = zw;
+            p.NI = nb; p.NB = 1; p.L = L; p.D = D; p.H = H; p.gate = a.gate; p.max_ctas = actas;
+            if (w.attn_stream) {
+                if (a.need_grad) { p.ctx32 = w.Ctx32 + ((size_t)t * B + b0) * D; p.ld_c32 = D; }
+                p.static_inputs = 1;         // a_c / wa were written before the loop
+                p.s_part = reinterpret_cast<float*>(scratch);
+            }
+            if (wait_ev) SAT_CHECK_CUDA(cudaStreamWaitEvent(s, wait_ev, 0));      // the other half's attention kernel has finished
+            SAT_TRY((attn_step_fwd<T, PRECISE>(p, s)));
+            if (rec_ev) SAT_CHECK_CUDA(cudaEventRecord(rec_ev, s));
+        }
+        // K3: gates = Xg[t] + [z | h] [W_ih[:,H:] | W_hh]^T, LSTM cell in the epilogue (decoder.py:108-115)
+        EpiLstm<T, PRECISE> e;
+        e.xg = w.Xg + ((size_t)t * B + b0) * 4 * H; e.ld_xg = 4 * H; e.bias = nullptr;
+        e.c_prev = w.Cst + ((size_t)t * B + b0) * H; e.ld_cp = H;
+        e.c_out = w.Cst + ((size_t)(t + 1) * B + b0) * H; e.ld_co = H;
+        e.h_next = w.ZH + ((size_t)(t + 1) * B + b0) * zw + D; e.ld_hn = zw;
+        e.h_out = w.Hdrop + ((size_t)t * B + b0) * H; e.ld_ho = H;
+        e.mask = a.dropout_mask ? a.dropout_mask + ((size_t)b0 * Tn + t) * H : nullptr; e.ld_mask = (int64_t)Tn * H;
+        e.gates = a.need_grad ? w.Gates + ((size_t)t * B + b0) * 4 * H : nullptr; e.ld_g = 4 * H;
+        e.M = nb; e.H = H;
+        return gemm<T>(s, zh_t, zw, true, w.w_gzh, zw, true, nb, 4 * H, D + H, e, 0, gsm, 1);
+    };
+    const int nsplit = dec_split(a, w);
+    SideStream* ss = nullptr;
+    if (nsplit > 1) {
+        SAT_TRY(side_stream(&ss));
+        SAT_CHECK_CUDA(cudaEventRecord(ss->fork, st));
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(ss->s, ss->fork, 0));
+    }
     for (int t = 0; t < Tn; ++t) {
-        T* zh_t = w.ZH + (size_t)t * B * zw;
         if (!a.tf) {
             // token fed at step t: start token, then argmax of the previous logits (decoder.py:79-82,132-133)
             SAT_TRY(misc::gather_rows<T>(st, w.E + (size_t)t * B * H, H, a.embedding, H, w.tok_in + (size_t)t * B, 1, B, V));
             auto e = lin<T>(B, 4 * H, w.b_g, SAT_ACT_NONE, w.Xg + (size_t)t * B * 4 * H, 4 * H, nullptr, 0);
             SAT_TRY(gemm<T>(st, w.E + (size_t)t * B * H, H, true, w.w_gx, H, true, B, 4 * H, H, e));
         }
-        if (a.attention) {
-            float* uf_t = w.UF + (size_t)t * B * (H + D);
-            auto e = lin<T>(B, H + D, w.b_uf, SAT_ACT_NONE, uf_t, H + D, nullptr, 0);
-            SAT_TRY(gemm<T>(st, zh_t + D, zw, true, w.w_uf, H, true, B, H + D, H, e));       // [U h | f_beta h]
-            attn::FwdParams p;
-            memset(&p, 0, sizeof(p));
-            p.a = w.a_c; p.wa = w.wa; p.uf = uf_t; p.ld_uf = H + D; p.v = a.att_v_w; p.bv = a.att_v_b;
-            p.alpha = a.alphas + (size_t)t * L; p.ld_alpha = (int64_t)Tn * L;
-            p.ctx = w.Ctx + (size_t)t * B * D; p.ld_ctx = D;
-            p.z = zh_t; p.ld_z = zw;
-            p.NI = B; p.NB = 1; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
-            if (w.attn_stream) {
-                if (a.need_grad) { p.ctx32 = w.Ctx32 + (size_t)t * B * D; p.ld_c32 = D; }
-                p.static_inputs = 1;         // a_c / wa were written before the loop
-                p.s_part = reinterpret_cast<float*>(w.attn_scratch);
-            }
-            SAT_TRY((attn_step_fwd<T, PRECISE>(p, st)));
+        if (nsplit > 1) {
+            const int nb0 = B / 2;
+            // chained: the two halves' attention kernels take turns on the HBM (A_t, B_t, A_t+1, ...) instead of drifting
+            // into lockstep, so each half's GEMMs run while the other half streams
+            const bool ch = g_split_chain != 0;
+            SAT_TRY(fwd_step(t, 0, nb0, st, w.attn_scratch, (ch && t > 0) ? ss->attn_done[1] : nullptr, ch ? ss->attn_done[0] : nullptr));
+            SAT_TRY(fwd_step(t, nb0, B - nb0, ss->s, w.attn_scratch2, ch ? ss->attn_done[0] : nullptr, ch ? ss->attn_done[1] : nullptr));
+        } else {
+            SAT_TRY(fwd_step(t, 0, B, st, w.attn_scratch, nullptr, nullptr));
         }
-        // K3: gates = Xg[t] + [z | h] [W_ih[:,H:] | W_hh]^T, LSTM cell in the epilogue (decoder.py:108-115)
-        EpiLstm<T, PRECISE> e;
-        e.xg = w.Xg + (size_t)t * B * 4 * H; e.ld_xg = 4 * H; e.bias = nullptr;
-        e.c_prev = w.Cst + (size_t)t * B * H; e.ld_cp = H;
-        e.c_out = w.Cst + (size_t)(t + 1) * B * H; e.ld_co = H;
-        e.h_next = w.ZH + (size_t)(t + 1) * B * zw + D; e.ld_hn = zw;
-        e.h_out = w.Hdrop + (size_t)t * B * H; e.ld_ho = H;
-        e.mask = a.dropout_mask ? a.dropout_mask + (size_t)t * H : nullptr; e.ld_mask = (int64_t)Tn * H;
-        e.gates = a.need_grad ? w.Gates + (size_t)t * B * 4 * H : nullptr; e.ld_g = 4 * H;
-        e.M = B; e.H = H;
-        SAT_TRY(gemm<T>(st, zh_t, zw, true, w.w_gzh, zw, true, B, 4 * H, D + H, e));
         if (!a.tf) {
             SAT_TRY(output_layer<T>(a, w, st, t, 1));
             if (t + 1 < Tn) {
@@ -319,6 +382,10 @@ int decoder_forward_t(const sat_decoder_args& a) {
                 SAT_CHECK_CUDA(cudaGetLastError());
             }
         }
+    }
+    if (nsplit > 1) {
+        SAT_CHECK_CUDA(cudaEventRecord(ss->join, ss->s));
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(st, ss->join, 0));
     }
     if (a.tf) SAT_TRY(output_layer<T>(a, w, st, 0, Tn));   // K4: one (T*B) x H x V GEMM after the loop
     if (a.fused_loss) {
@@ -373,11 +440,7 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     float* g_out_w = a.ado ? g.f_out_w : g.deep_w;
     float* g_out_b = a.ado ? g.f_out_b : g.deep_b;
     const T* out_in = a.ado ? w.Comb : w.Hdrop;     // input rows of the V-projection
-    if (g_out_w) {
-        auto e = lin<T>(V, H, nullptr, SAT_ACT_NONE, g_out_w, H, nullptr, 0);
-        SAT_TRY(gemm<T>(st, w.dlog, Vp, false, out_in, H, false, V, H, BT, e));          // dW = dlog^T X
-    }
-    if (g_out_b) SAT_TRY(misc::colsum<T>(st, w.dlog, Vp, BT, V, g_out_b, w.csum, w.csum_floats));
+    // (dW_out = dlog^T X and db_out are not needed by the BPTT loop: they run in the side chain of the tail below)
     if (!a.ado) {
         auto e = lin<T>(BT, H, nullptr, SAT_ACT_NONE, w.dHd, H, nullptr, 0);
         SAT_TRY(gemm<T>(st, w.dlog, Vp, true, w.w_out, H, false, BT, H, V, e));          // dHdrop = dlog W_out
@@ -403,108 +466,107 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     // ---- BPTT loop ------------------------------------------------------------------------------------
     SAT_CHECK_CUDA(cudaMemsetAsync(w.dh_carry, 0, (size_t)B * H * 4, st));
     SAT_CHECK_CUDA(cudaMemsetAsync(w.dc_carry, 0, (size_t)B * H * 4, st));
-    for (int t = Tn - 1; t >= 0; --t) {
+    // one BPTT step for the captions [b0, b0 + nb) on stream s
+    auto bwd_step = [&](int t, int b0, int nb, cudaStream_t s, uint8_t* scratch, cudaEvent_t wait_ev, cudaEvent_t rec_ev) -> int {
+        const int gsm = nb < B ? g_split_gemm_sms : 0, actas = nb < B ? g_split_attn_ctas : 0;
+        const size_t r = (size_t)t * B + b0;       // first time-major row of this half at step t
+        float* dzh = w.dZH + (size_t)b0 * zw;
+        float* dh_carry = w.dh_carry + (size_t)b0 * H;
         // (the cell backward stays a kernel of its own: fused into the 16-CTA dh GEMM below it ran 3x slower)
         {
             cudaLaunchConfig_t cfg;
             cudaLaunchAttribute attr[1];
-            pdl_config(&cfg, attr, dim3(sat_cdiv(H, 128), B), dim3(128), 0, st);
+            pdl_config(&cfg, attr, dim3(sat_cdiv(H, 128), nb), dim3(128), 0, s);
             SAT_CHECK_CUDA(cudaLaunchKernelEx(
-                &cfg, misc::lstm_bwd_kernel<T>, (const T*)(w.Gates + (size_t)t * B * 4 * H), (int64_t)(4 * H),
-                (const float*)(w.Cst + (size_t)t * B * H), (int64_t)H, (const float*)(w.Cst + (size_t)(t + 1) * B * H), (int64_t)H,
-                (const float*)(w.dHd + (size_t)t * B * H), (int64_t)H,
-                (const float*)(a.dropout_mask ? a.dropout_mask + (size_t)t * H : nullptr), (int64_t)Tn * H,
-                (const float*)w.dh_carry, w.dc_carry, w.dG + (size_t)t * B * 4 * H, (int64_t)(4 * H), B, H));
+                &cfg, misc::lstm_bwd_kernel<T>, (const T*)(w.Gates + r * 4 * H), (int64_t)(4 * H),
+                (const float*)(w.Cst + r * H), (int64_t)H, (const float*)(w.Cst + ((size_t)(t + 1) * B + b0) * H), (int64_t)H,
+                (const float*)(w.dHd + r * H), (int64_t)H,
+                (const float*)(a.dropout_mask ? a.dropout_mask + ((size_t)b0 * Tn + t) * H : nullptr), (int64_t)Tn * H,
+                (const float*)dh_carry, w.dc_carry + (size_t)b0 * H, w.dG + r * 4 * H, (int64_t)(4 * H), nb, H));
         }
         // d[z | h_prev] = dG [W_ih[:,H:] | W_hh]   (streaming attention: with the context gate's backward in the epilogue)
         if (a.attention && w.attn_stream) {
             EpiDzGate<T, PRECISE> e;
-            e.out = w.dZH; e.ld_out = zw;
-            e.uf = w.UF + (size_t)t * B * (H + D); e.ld_uf = H + D;
-            e.ctx32 = w.Ctx32 + (size_t)t * B * D; e.ld_c32 = D;
-            e.extra = a.ado ? w.dctx_all + (size_t)t * B * D : nullptr; e.ld_ex = D;
-            e.duf = w.dUF + (size_t)t * B * (H + D); e.ld_duf = H + D;
-            e.M = B; e.D = D; e.H = H; e.gate = a.gate;
-            SAT_TRY(gemm<T>(st, w.dG + (size_t)t * B * 4 * H, 4 * H, true, w.w_gzh, zw, false, B, D + H, 4 * H, e));
+            e.out = dzh; e.ld_out = zw;
+            e.uf = w.UF + r * (H + D); e.ld_uf = H + D;
+            e.ctx32 = w.Ctx32 + r * D; e.ld_c32 = D;
+            e.extra = a.ado ? w.dctx_all + r * D : nullptr; e.ld_ex = D;
+            e.duf = w.dUF + r * (H + D); e.ld_duf = H + D;
+            e.M = nb; e.D = D; e.H = H; e.gate = a.gate;
+            SAT_TRY(gemm<T>(s, w.dG + r * 4 * H, 4 * H, true, w.w_gzh, zw, false, nb, D + H, 4 * H, e, 0, gsm, 1));
         } else {
-            auto e = lin<T>(B, D + H, nullptr, SAT_ACT_NONE, w.dZH, zw, nullptr, 0);
-            SAT_TRY(gemm<T>(st, w.dG + (size_t)t * B * 4 * H, 4 * H, true, w.w_gzh, zw, false, B, D + H, 4 * H, e));
+            auto e = lin<T>(nb, D + H, nullptr, SAT_ACT_NONE, dzh, zw, nullptr, 0);
+            SAT_TRY(gemm<T>(s, w.dG + r * 4 * H, 4 * H, true, w.w_gzh, zw, false, nb, D + H, 4 * H, e, 0, gsm, 1));
         }
         if (a.attention) {
             attn::BwdParams p;
             memset(&p, 0, sizeof(p));
-            p.a = w.a_c; p.wa = w.wa; p.uf = w.UF + (size_t)t * B * (H + D); p.ld_uf = H + D;
-            p.v = a.att_v_w; p.alpha = a.alphas + (size_t)t * L; p.ld_alpha = (int64_t)Tn * L;
-            p.ctx = w.Ctx + (size_t)t * B * D; p.ld_ctx = D;
-            p.dz = w.dZH; p.ld_dz = zw;
-            p.dctx_extra = a.ado ? w.dctx_all + (size_t)t * B * D : nullptr; p.ld_dce = D;
-            p.galpha = galpha ? galpha + (size_t)t * L : nullptr; p.ld_ga = (int64_t)Tn * L;
-            p.duf = w.dUF + (size_t)t * B * (H + D); p.ld_duf = H + D;
-            p.dwa_acc = w.dwa_acc; p.dv_acc = w.dv_acc; p.dbv_acc = w.dbv_acc; p.da_acc = nullptr;
+            p.a = w.a_c + (size_t)b0 * L * D; p.wa = w.wa + (size_t)b0 * L * H; p.uf = w.UF + r * (H + D); p.ld_uf = H + D;
+            p.v = a.att_v_w; p.alpha = a.alphas + ((size_t)b0 * Tn + t) * L; p.ld_alpha = (int64_t)Tn * L;
+            p.ctx = w.Ctx + r * D; p.ld_ctx = D;
+            p.dz = dzh; p.ld_dz = zw;
+            p.dctx_extra = a.ado ? w.dctx_all + r * D : nullptr; p.ld_dce = D;
+            p.galpha = galpha ? galpha + ((size_t)b0 * Tn + t) * L : nullptr; p.ld_ga = (int64_t)Tn * L;
+            p.duf = w.dUF + r * (H + D); p.ld_duf = H + D;
+            p.dwa_acc = w.dwa_acc ? w.dwa_acc + (size_t)b0 * L * H : nullptr;
+            p.dv_acc = w.dv_acc + (size_t)b0 * H; p.dbv_acc = w.dbv_acc + b0; p.da_acc = nullptr;
             if (w.attn_stream) {
-                p.dpre_out = w.dpre_all + (size_t)t * B * L * H;
-                p.ctx32 = w.Ctx32 + (size_t)t * B * D; p.ld_c32 = D;
-                p.s_part = reinterpret_cast<float*>(w.attn_scratch);
+                p.dpre_out = w.dpre_all + ((size_t)t * B + b0) * L * H;
+                p.ctx32 = w.Ctx32 + r * D; p.ld_c32 = D;
+                p.s_part = reinterpret_cast<float*>(scratch);
                 p.dz_is_dctx = 1;            // EpiDzGate above already turned dz into dctx and wrote d f_beta
                 p.static_inputs = 1;
             }
             p.first = (t == Tn - 1);
-            p.B = B; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
-            SAT_TRY((attn_step_bwd<T, PRECISE>(p, st)));
+            p.B = nb; p.L = L; p.D = D; p.H = H; p.gate = a.gate; p.max_ctas = actas;
+            if (wait_ev) SAT_CHECK_CUDA(cudaStreamWaitEvent(s, wait_ev, 0));
+            SAT_TRY((attn_step_bwd<T, PRECISE>(p, s)));
+            if (rec_ev) SAT_CHECK_CUDA(cudaEventRecord(rec_ev, s));
             // dh_prev = dZH[:, D:] + [dUh | dfb] [U ; f_beta]
-            auto e = lin<T>(B, H, nullptr, SAT_ACT_NONE, w.dh_carry, H, nullptr, 0, w.dZH + D, zw);
-            SAT_TRY(gemm<T>(st, w.dUF + (size_t)t * B * (H + D), H + D, true, w.w_uf, H, false, B, H, H + D, e));
+            auto e = lin<T>(nb, H, nullptr, SAT_ACT_NONE, dh_carry, H, nullptr, 0, dzh + D, zw);
+            SAT_TRY(gemm<T>(s, w.dUF + r * (H + D), H + D, true, w.w_uf, H, false, nb, H, H + D, e, 0, gsm, 1));
         } else {
             // no attention: z is the constant mean feature; only the hidden path carries on
-            SAT_CHECK_CUDA(cudaMemcpy2DAsync(w.dh_carry, (size_t)H * 4, w.dZH + D, (size_t)zw * 4, (size_t)H * 4, B,
-                                             cudaMemcpyDeviceToDevice, st));
+            SAT_CHECK_CUDA(cudaMemcpy2DAsync(dh_carry, (size_t)H * 4, dzh + D, (size_t)zw * 4, (size_t)H * 4, nb,
+                                             cudaMemcpyDeviceToDevice, s));
+        }
+        return SAT_OK;
+    };
+    const int nsplit = dec_split(a, w);
+    SideStream* ss = nullptr;
+    if (nsplit > 1) {
+        SAT_TRY(side_stream(&ss));
+        SAT_CHECK_CUDA(cudaEventRecord(ss->fork, st));
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(ss->s, ss->fork, 0));
+    }
+    for (int t = Tn - 1; t >= 0; --t) {
+        if (nsplit > 1) {
+            const int nb0 = B / 2;
+            const bool ch = g_split_chain != 0;
+            SAT_TRY(bwd_step(t, 0, nb0, st, w.attn_scratch, (ch && t < Tn - 1) ? ss->attn_done[1] : nullptr, ch ? ss->attn_done[0] : nullptr));
+            SAT_TRY(bwd_step(t, nb0, B - nb0, ss->s, w.attn_scratch2, ch ? ss->attn_done[0] : nullptr, ch ? ss->attn_done[1] : nullptr));
+        } else {
+            SAT_TRY(bwd_step(t, 0, B, st, w.attn_scratch, nullptr, nullptr));
         }
     }
-
-    // ---- initial state (decoder.py:137-147) ----------------------------------------------------------
-    misc::dinit_kernel<T><<<sat_cdiv(B * H, 256), 256, 0, st>>>(w.dpre0, w.dh_carry, w.dc_carry, w.hc0, B, H);
-    SAT_CHECK_CUDA(cudaGetLastError());
-    {
-        auto e = lin<T>(2 * H, D, nullptr, SAT_ACT_NONE, w.gscratch, D, nullptr, 0);
-        SAT_TRY(gemm<T>(st, w.dpre0, 2 * H, false, w.abar, D, false, 2 * H, D, B, e));
-        if (g.init_h_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_h_w, w.gscratch, (size_t)H * D * 4, cudaMemcpyDeviceToDevice, st));
-        if (g.init_c_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_c_w, w.gscratch + (size_t)H * D, (size_t)H * D * 4, cudaMemcpyDeviceToDevice, st));
-        SAT_TRY(misc::colsum<T>(st, w.dpre0, 2 * H, B, 2 * H, w.gscratch, w.csum, w.csum_floats));
-        if (g.init_h_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_h_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
-        if (g.init_c_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_c_b, w.gscratch + H, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
+    if (nsplit > 1) {
+        SAT_CHECK_CUDA(cudaEventRecord(ss->join, ss->s));
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(st, ss->join, 0));
     }
 
-    // ---- batched weight gradients (contraction over k = t*B + b) ---------------------------------------
-    {
-        // gate weights: dW_gzh (4H x (D+H)) = dG^T [Z | Hprev] ; dW_gx (4H x H) = dG^T E ; un-interleave rows
-        auto e = lin<T>(4 * H, D + H, nullptr, SAT_ACT_NONE, w.gscratch, zw, nullptr, 0);
-        SAT_TRY(gemm<T>(st, w.dG, 4 * H, false, w.ZH, zw, false, 4 * H, D + H, BT, e));
-        if (g.lstm_w_ih) SAT_TRY(misc::unpack_grad(st, g.lstm_w_ih, H + D, w.gscratch, zw, 4 * H, D, H, H));
-        if (g.lstm_w_hh) SAT_TRY(misc::unpack_grad(st, g.lstm_w_hh, H, w.gscratch + D, zw, 4 * H, H, 0, H));
-        auto e2 = lin<T>(4 * H, H, nullptr, SAT_ACT_NONE, w.gscratch, H, nullptr, 0);
-        SAT_TRY(gemm<T>(st, w.dG, 4 * H, false, w.E, H, false, 4 * H, H, BT, e2));
-        if (g.lstm_w_ih) SAT_TRY(misc::unpack_grad(st, g.lstm_w_ih, H + D, w.gscratch, H, 4 * H, H, 0, H));
-        if (g.lstm_b_ih) SAT_TRY(misc::colsum<T>(st, w.dG, 4 * H, BT, 4 * H, g.lstm_b_ih, w.csum, w.csum_floats, H));
-        if (g.lstm_b_hh) SAT_TRY(misc::colsum<T>(st, w.dG, 4 * H, BT, 4 * H, g.lstm_b_hh, w.csum, w.csum_floats, H));
+    // ---- after the loop: two independent chains on two streams ---------------------------------------------------
+    // main chain (HBM / tensor bound): sum over t of the attention pre-activation gradients -> dW_att GEMM -> dv, db_v.
+    // side chain (many small launches): initial-state, gate, embedding, [U; f_beta] and output-layer weight gradients.
+    // They share no buffer (gscratch / csum2 belong to the side chain, csum to the main chain) and join before returning.
+    SideStream* tl = nullptr;
+    SAT_TRY(side_stream(&tl));
+    cudaStream_t sb = g_tail_overlap ? tl->s : st;
+    float* csb = g_tail_overlap ? w.csum2 : w.csum;
+    if (g_tail_overlap) {
+        SAT_CHECK_CUDA(cudaEventRecord(tl->fork, st));
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(sb, tl->fork, 0));
     }
-    // embedding: dE = dG W_gx (+ dcomb for ado), scatter-add by token (skipped when frozen / NULL: Q23)
-    if (g.embedding) {
-        SAT_CHECK_CUDA(cudaMemsetAsync(g.embedding, 0, (size_t)V * H * 4, st));
-        auto e = lin<T>(BT, H, nullptr, SAT_ACT_NONE, nullptr, 0, w.dE, H, a.ado ? w.dcomb : nullptr, H);
-        SAT_TRY(gemm<T>(st, w.dG, 4 * H, true, w.w_gx, H, false, BT, H, 4 * H, e));
-        if (a.tf) misc::scatter_add_bt_kernel<T><<<BT, 128, 0, st>>>(g.embedding, H, w.dE, a.captions, a.cap_stride, B, V);
-        else misc::scatter_add_rows_kernel<T><<<BT, 128, 0, st>>>(g.embedding, H, w.dE, w.tok_in, V);
-        SAT_CHECK_CUDA(cudaGetLastError());
-    }
-    if (a.attention) {
-        // [U ; f_beta] grads: dW_uf ((H+D) x H) = dUF^T Hprev  (Hprev = ZH[:, D:], steps 0..T-1)
-        auto e = lin<T>(H + D, H, nullptr, SAT_ACT_NONE, w.gscratch, H, nullptr, 0);
-        SAT_TRY(gemm<T>(st, w.dUF, H + D, false, w.ZH + D, zw, false, H + D, H, BT, e));
-        if (g.att_U_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_w, w.gscratch, (size_t)H * H * 4, cudaMemcpyDeviceToDevice, st));
-        if (g.f_beta_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_w, w.gscratch + (size_t)H * H, (size_t)D * H * 4, cudaMemcpyDeviceToDevice, st));
-        SAT_TRY(misc::colsum<T>(st, w.dUF, H + D, BT, H + D, w.gscratch, w.csum, w.csum_floats));
-        if (g.att_U_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
-        if (g.f_beta_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_b, w.gscratch + H, (size_t)D * 4, cudaMemcpyDeviceToDevice, st));
+    if (a.attention) {      // main chain
         // encoder projection: dW (H x D) = (sum_t dpre)^T a ; db_W = colsum ; dv, db_v
         bool att_W_b_done = false;
         if (w.attn_stream) {
@@ -527,6 +589,64 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         }
         if (g.att_v_w) SAT_TRY(misc::colsum<float>(st, w.dv_acc, H, B, H, g.att_v_w, w.csum, w.csum_floats));
         if (g.att_v_b) SAT_TRY(misc::colsum<float>(st, w.dbv_acc, 1, B, 1, g.att_v_b, w.csum, w.csum_floats));
+    }
+
+    // ---- side chain: initial state (decoder.py:137-147) ------------------------------------------------------------
+    misc::dinit_kernel<T><<<sat_cdiv(B * H, 256), 256, 0, sb>>>(w.dpre0, w.dh_carry, w.dc_carry, w.hc0, B, H);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    {
+        auto e = lin<T>(2 * H, D, nullptr, SAT_ACT_NONE, w.gscratch, D, nullptr, 0);
+        SAT_TRY(gemm<T>(sb, w.dpre0, 2 * H, false, w.abar, D, false, 2 * H, D, B, e));
+        if (g.init_h_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_h_w, w.gscratch, (size_t)H * D * 4, cudaMemcpyDeviceToDevice, sb));
+        if (g.init_c_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_c_w, w.gscratch + (size_t)H * D, (size_t)H * D * 4, cudaMemcpyDeviceToDevice, sb));
+        SAT_TRY(misc::colsum<T>(sb, w.dpre0, 2 * H, B, 2 * H, w.gscratch, csb, w.csum_floats));
+        if (g.init_h_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_h_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, sb));
+        if (g.init_c_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_c_b, w.gscratch + H, (size_t)H * 4, cudaMemcpyDeviceToDevice, sb));
+    }
+    // ---- side chain: batched weight gradients (contraction over k = t*B + b) -----------------------------------------
+    {
+        // gate weights: dW_gzh (4H x (D+H)) = dG^T [Z | Hprev] ; dW_gx (4H x H) = dG^T E ; un-interleave rows
+        auto e = lin<T>(4 * H, D + H, nullptr, SAT_ACT_NONE, w.gscratch, zw, nullptr, 0);
+        SAT_TRY(gemm<T>(sb, w.dG, 4 * H, false, w.ZH, zw, false, 4 * H, D + H, BT, e));
+        if (g.lstm_w_ih) SAT_TRY(misc::unpack_grad(sb, g.lstm_w_ih, H + D, w.gscratch, zw, 4 * H, D, H, H));
+        if (g.lstm_w_hh) SAT_TRY(misc::unpack_grad(sb, g.lstm_w_hh, H, w.gscratch + D, zw, 4 * H, H, 0, H));
+        auto e2 = lin<T>(4 * H, H, nullptr, SAT_ACT_NONE, w.gscratch, H, nullptr, 0);
+        SAT_TRY(gemm<T>(sb, w.dG, 4 * H, false, w.E, H, false, 4 * H, H, BT, e2));
+        if (g.lstm_w_ih) SAT_TRY(misc::unpack_grad(sb, g.lstm_w_ih, H + D, w.gscratch, H, 4 * H, H, 0, H));
+        // d b_ih = d b_hh = column sums of dG: computed once, copied
+        float* gb = g.lstm_b_ih ? g.lstm_b_ih : g.lstm_b_hh;
+        if (gb) SAT_TRY(misc::colsum<T>(sb, w.dG, 4 * H, BT, 4 * H, gb, csb, w.csum_floats, H));
+        if (g.lstm_b_ih && g.lstm_b_hh)
+            SAT_CHECK_CUDA(cudaMemcpyAsync(g.lstm_b_hh, g.lstm_b_ih, (size_t)4 * H * 4, cudaMemcpyDeviceToDevice, sb));
+    }
+    // embedding: dE = dG W_gx (+ dcomb for ado), scatter-add by token (skipped when frozen / NULL: Q23)
+    if (g.embedding) {
+        SAT_CHECK_CUDA(cudaMemsetAsync(g.embedding, 0, (size_t)V * H * 4, sb));
+        auto e = lin<T>(BT, H, nullptr, SAT_ACT_NONE, nullptr, 0, w.dE, H, a.ado ? w.dcomb : nullptr, H);
+        SAT_TRY(gemm<T>(sb, w.dG, 4 * H, true, w.w_gx, H, false, BT, H, 4 * H, e));
+        if (a.tf) misc::scatter_add_bt_kernel<T><<<BT, 128, 0, sb>>>(g.embedding, H, w.dE, a.captions, a.cap_stride, B, V);
+        else misc::scatter_add_rows_kernel<T><<<BT, 128, 0, sb>>>(g.embedding, H, w.dE, w.tok_in, V);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    }
+    if (a.attention) {
+        // [U ; f_beta] grads: dW_uf ((H+D) x H) = dUF^T Hprev  (Hprev = ZH[:, D:], steps 0..T-1)
+        auto e = lin<T>(H + D, H, nullptr, SAT_ACT_NONE, w.gscratch, H, nullptr, 0);
+        SAT_TRY(gemm<T>(sb, w.dUF, H + D, false, w.ZH + D, zw, false, H + D, H, BT, e));
+        if (g.att_U_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_w, w.gscratch, (size_t)H * H * 4, cudaMemcpyDeviceToDevice, sb));
+        if (g.f_beta_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_w, w.gscratch + (size_t)H * H, (size_t)D * H * 4, cudaMemcpyDeviceToDevice, sb));
+        SAT_TRY(misc::colsum<T>(sb, w.dUF, H + D, BT, H + D, w.gscratch, csb, w.csum_floats));
+        if (g.att_U_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, sb));
+        if (g.f_beta_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_b, w.gscratch + H, (size_t)D * 4, cudaMemcpyDeviceToDevice, sb));
+    }
+    // output layer weights (deferred from before the loop)
+    if (g_out_w) {
+        auto e = lin<T>(V, H, nullptr, SAT_ACT_NONE, g_out_w, H, nullptr, 0);
+        SAT_TRY(gemm<T>(sb, w.dlog, Vp, false, out_in, H, false, V, H, BT, e));          // dW = dlog^T X
+    }
+    if (g_out_b) SAT_TRY(misc::colsum<T>(sb, w.dlog, Vp, BT, V, g_out_b, csb, w.csum_floats));
+    if (g_tail_overlap) {
+        SAT_CHECK_CUDA(cudaEventRecord(tl->join, sb));
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(st, tl->join, 0));
     }
     return SAT_OK;
 }

@@ -22,6 +22,12 @@ struct EpiLinear {
     int vec_ok;              // all pointers 16B aligned, all ld % 8 == 0
     int remapB, remapT;      // remapT > 0: GEMM row m = t*remapB + b is stored at output row b*remapT + t
 
+    // L2 warm-up of what apply(m, n .. n + nc) will read (issued by the epilogue warps while the MMAs run)
+    __device__ __forceinline__ void prefetch(int m, int n, int nc) const {
+        if (m >= M || !addend) return;
+        for (int c = 0; c < nc; c += 32) l2_prefetch(addend + (int64_t)m * ld_add + n + c);
+    }
+
     template <int NV>
     __device__ __forceinline__ void apply(int m, int n0, const float* acc) const {
         if (m >= M) return;
@@ -100,6 +106,14 @@ struct EpiDzGate {
     int64_t ld_duf;
     int M, D, H, gate;
 
+    __device__ __forceinline__ void prefetch(int m, int n, int nc) const {
+        if (m >= M || n >= D) return;
+        for (int c = 0; c < nc; c += 32) {
+            if (gate) { l2_prefetch(uf + (int64_t)m * ld_uf + H + n + c); l2_prefetch(ctx32 + (int64_t)m * ld_c32 + n + c); }
+            if (extra) l2_prefetch(extra + (int64_t)m * ld_ex + n + c);
+        }
+    }
+
     template <int NV>
     __device__ __forceinline__ void apply(int m, int n0, const float* acc) const {
         if (m >= M) return;
@@ -158,6 +172,15 @@ struct EpiLstm {
         p[3] = sat_sigmoid<true>(p[3]);
         c = p[1] * cp + p[0] * p[2];
         h = p[3] * sat_tanh<true>(c);
+    }
+
+    // the epilogue's inputs (this step's Xg rows, the previous cell state, the dropout mask) were last touched before the
+    // attention kernel streamed 257 MB through L2: request them while the MMAs run instead of after the accumulator is ready
+    __device__ __forceinline__ void prefetch(int m, int n, int nc) const {
+        if (m >= M) return;
+        if (xg) for (int c = 0; c < nc; c += 32) l2_prefetch(xg + (int64_t)m * ld_xg + n + c);
+        l2_prefetch(c_prev + (int64_t)m * ld_cp + (n >> 2));
+        if (mask) l2_prefetch(mask + (int64_t)m * ld_mask + (n >> 2));
     }
 
     template <int NV>

@@ -105,7 +105,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
 template <int BN, bool A_MN, bool B_MN, typename Epi, int SPLIT>
 __global__ void __launch_bounds__(THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
-            int M, int N, int K, Epi epi) {
+            int M, int N, int K, Epi epi, int b_static) {
     using C = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment (128B swizzle atoms) as an OFFSET from the __shared__ array, so that the compiler still knows the
@@ -144,33 +144,54 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     if constexpr (SPLIT > 1) {                             // cluster barrier #1: the epilogue warps arrive once the accumulator is done
         if (warp < 2 || warp >= PROD_WARP0) cluster_arrive_release();
     }
+    // An MN-major operand arrives as 64-column boxes (128-byte swizzle span), up to six copies per stage; one thread
+    // can only start a copy every ~60 ns, so lane b of the producer warp issues box b of the stage.
+    constexpr int A_BOXES = A_MN ? BM / 64 : 1, B_BOXES = B_MN ? BN / 64 : 1;
+    static_assert(C::STAGES % NPROD == 0, "a stage must always be filled by the same producer");
+    const bool producer = warp == 0 || warp >= PROD_WARP0;
+    const int kb_first = warp == 0 ? 0 : warp - PROD_WARP0 + 1;
+    auto load_b = [&](int kb, int s) {
+        if (lane >= A_BOXES && lane < A_BOXES + B_BOXES) {
+            const int c = lane - A_BOXES, k0 = (kb0 + kb) * BK;
+            uint8_t* b_dst = sB + s * C::B_BYTES;
+            if (b_static) {         // a weight matrix re-read every decode step: keep it in L2 across the attention kernel's stream
+                if (!B_MN) tma_load_2d_hint(b_dst, &mapB, k0, n0, &full_bar[s], L2_EVICT_LAST);
+                else tma_load_2d_hint(b_dst + c * (BK * 128), &mapB, n0 + c * 64, k0, &full_bar[s], L2_EVICT_LAST);
+            } else {
+                if (!B_MN) tma_load_2d(b_dst, &mapB, k0, n0, &full_bar[s]);
+                else tma_load_2d(b_dst + c * (BK * 128), &mapB, n0 + c * 64, k0, &full_bar[s]);
+            }
+        }
+    };
+    // b_static: operand B (a packed weight matrix) is older than the previous kernel in the stream, so the first ring pass
+    // of its tiles is requested BEFORE the programmatic-dependent-launch wait and lands while the predecessor drains.
+    if (b_static && producer) {
+        for (int kb = kb_first; kb < nk && kb < C::STAGES; kb += NPROD) {
+            if (lane == 0) mbar_expect_tx(&full_bar[kb], C::STAGE_BYTES);
+            __syncwarp();
+            load_b(kb, kb);
+        }
+    }
     // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) overlapped the previous
     // kernel's tail; its results are needed from here on.  Let the next kernel start its own prologue right away.
     pdl_wait();
     pdl_launch_dependents();
 
-    static_assert(C::STAGES % NPROD == 0, "a stage must always be filled by the same producer");
-    if (warp == 0 || warp >= PROD_WARP0) {
-        // An MN-major operand arrives as 64-column boxes (128-byte swizzle span), up to six copies per stage; one thread
-        // can only start a copy every ~60 ns, so lane b of the producer warp issues box b of the stage.
-        constexpr int A_BOXES = A_MN ? BM / 64 : 1, B_BOXES = B_MN ? BN / 64 : 1;
-        for (int kb = (warp == 0 ? 0 : warp - PROD_WARP0 + 1); kb < nk; kb += NPROD) {
+    if (producer) {
+        for (int kb = kb_first; kb < nk; kb += NPROD) {
             const int s = kb % C::STAGES;
             const uint32_t ph = (kb / C::STAGES) & 1;
+            const bool b_done = b_static && kb < C::STAGES;       // expect_tx posted and B requested before the wait
             mbar_wait(&empty_bar[s], ph ^ 1);
-            if (lane == 0) mbar_expect_tx(&full_bar[s], C::STAGE_BYTES);
+            if (lane == 0 && !b_done) mbar_expect_tx(&full_bar[s], C::STAGE_BYTES);
             __syncwarp();
             uint8_t* a_dst = sA + s * C::A_BYTES;
-            uint8_t* b_dst = sB + s * C::B_BYTES;
             const int k0 = (kb0 + kb) * BK;
             if (lane < A_BOXES) {
                 if (!A_MN) tma_load_2d(a_dst, &mapA, k0, m0, &full_bar[s]);
                 else tma_load_2d(a_dst + lane * (BK * 128), &mapA, m0 + lane * 64, k0, &full_bar[s]);
-            } else if (lane < A_BOXES + B_BOXES) {
-                const int c = lane - A_BOXES;
-                if (!B_MN) tma_load_2d(b_dst, &mapB, k0, n0, &full_bar[s]);
-                else tma_load_2d(b_dst + c * (BK * 128), &mapB, n0 + c * 64, k0, &full_bar[s]);
             }
+            if (!b_done) load_b(kb, s);
         }
     } else if (warp == 1) {
         if (elect_one()) {
@@ -198,10 +219,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         }
     } else {
         const int q = warp & 3;                      // TMEM lane quarter this warp may access
-        mbar_wait(tmem_full_bar, 0);
-        tc_fence_after();
         const int m = m0 + q * 32 + lane;
         const int grp = (warp - 2) >> 2;             // epilogue group of this warp
+        {   // while the MMAs run: warm L2 with the epilogue's global inputs for the columns this CTA finishes
+            constexpr int CWP = BN / SPLIT;
+            constexpr int PWD = CWP / EPI_GROUPS >= 4 ? CWP / EPI_GROUPS : 4;
+            const int pn = n0 + zsp * CWP + grp * PWD;
+            if (grp * PWD < CWP && pn < N) epi.prefetch(m, pn, PWD);
+        }
+        mbar_wait(tmem_full_bar, 0);
+        tc_fence_after();
         if constexpr (SPLIT == 1) {
             constexpr int NC = BN / 32;
             if constexpr (NC >= EPI_GROUPS) {        // whole 32-column chunks, dealt round-robin to the groups
@@ -321,7 +348,7 @@ inline int make_map(CUtensorMap* map, const void* ptr, uint64_t inner, uint64_t 
 }
 
 template <int BN, bool A_MN, bool B_MN, typename Epi, int SPLIT>
-int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB, int M, int N, int K, const Epi& epi) {
+int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB, int M, int N, int K, const Epi& epi, int b_static) {
     auto kern = gemm_kernel<BN, A_MN, B_MN, Epi, SPLIT>;
     constexpr int smem = Cfg<BN>::SMEM_BYTES;
     static bool configured = false;
@@ -338,7 +365,7 @@ int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB,
         attr[1].val.clusterDim.x = 1; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = SPLIT;
         cfg.numAttrs = 2;
     }
-    SAT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, M, N, K, epi));
+    SAT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, M, N, K, epi, b_static));
     return SAT_OK;
 }
 
@@ -347,12 +374,14 @@ int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB,
 // kb = 20 / 24 / 26 / 48 for BN = 32 / 64 / 128 / 256 (0.155 us is the floor of a k-block up to BN = 128).  It keeps the per-step
 // skinny GEMMs (M = batch) in ONE wave of <= #SMs CTAs, splits K over a cluster when the tiles alone would leave most SMs idle
 // (dh: 16 tiles x 40 k-blocks; dW_att: 64 tiles x 784 k-blocks) and takes the widest tile that does not add a wave otherwise.
-inline void pick_tile(int M, int N, int K, bool b_mn, int* bn_out, int* split_out) {
-    static int sms = 0;
-    if (!sms) {
+inline void pick_tile(int M, int N, int K, bool b_mn, int* bn_out, int* split_out, int sm_budget = 0) {
+    static int dev_sms = 0;
+    if (!dev_sms) {
         int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) sms = 148;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) dev_sms = 148;
     }
+    // sm_budget > 0: the SMs this GEMM can count on while another kernel holds the rest (half-batch pipelining)
+    const int sms = (sm_budget > 0 && sm_budget < dev_sms) ? sm_budget : dev_sms;
     const int mt = sat_cdiv(M, BM), nk = sat_cdiv(K, BK);
     const int cands[4] = {256, 128, 64, 32};
     int best = b_mn ? 64 : 32, best_split = 1;
@@ -376,7 +405,7 @@ inline void pick_tile(int M, int N, int K, bool b_mn, int* bn_out, int* split_ou
 
 template <bool A_MN, bool B_MN, typename Epi>
 int launch_mn(cudaStream_t stream, const bf16* A, int64_t lda, const bf16* B, int64_t ldb, int M, int N, int K,
-              const Epi& epi, int bn, int split) {
+              const Epi& epi, int bn, int split, int b_static) {
     CUtensorMap mA, mB;
     if (!A_MN) SAT_TRY(make_map(&mA, A, K, M, lda, 64, BM));
     else       SAT_TRY(make_map(&mA, A, M, K, lda, 64, BK));
@@ -385,15 +414,15 @@ int launch_mn(cudaStream_t stream, const bf16* A, int64_t lda, const bf16* B, in
     else       SAT_TRY(make_map(&mB, B, N, K, ldb, 64, BK));
 #define SAT_TC_SPLITS(BN_)                                                                                     \
         case BN_:                                                                                              \
-            if (split == 4) return launch_bn<BN_, A_MN, B_MN, Epi, 4>(stream, mA, mB, M, N, K, epi);           \
-            if (split == 2) return launch_bn<BN_, A_MN, B_MN, Epi, 2>(stream, mA, mB, M, N, K, epi);           \
-            return launch_bn<BN_, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
+            if (split == 4) return launch_bn<BN_, A_MN, B_MN, Epi, 4>(stream, mA, mB, M, N, K, epi, b_static);           \
+            if (split == 2) return launch_bn<BN_, A_MN, B_MN, Epi, 2>(stream, mA, mB, M, N, K, epi, b_static);           \
+            return launch_bn<BN_, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi, b_static);
     switch (bn) {
         SAT_TC_SPLITS(256)
         SAT_TC_SPLITS(128)
         SAT_TC_SPLITS(64)
         case 32:
-            if constexpr (!B_MN) return launch_bn<32, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi);
+            if constexpr (!B_MN) return launch_bn<32, A_MN, B_MN, Epi, 1>(stream, mA, mB, M, N, K, epi, b_static);
         default: break;
     }
 #undef SAT_TC_SPLITS
@@ -403,15 +432,15 @@ int launch_mn(cudaStream_t stream, const bf16* A, int64_t lda, const bf16* B, in
 
 template <typename Epi>
 int launch(cudaStream_t stream, const bf16* A, int64_t lda, bool a_kmajor, const bf16* B, int64_t ldb, bool b_kmajor,
-           int M, int N, int K, const Epi& epi, int bn_override = 0, int split_override = 0) {
+           int M, int N, int K, const Epi& epi, int bn_override = 0, int split_override = 0, int sm_budget = 0, int b_static = 0) {
     if (M <= 0 || N <= 0) return SAT_OK;
     SAT_REQUIRE(K > 0, "tcgen05 GEMM needs K > 0");
     int bn = 0, split = 1;
-    pick_tile(M, N, K, !b_kmajor, &bn, &split);
+    pick_tile(M, N, K, !b_kmajor, &bn, &split, sm_budget);
     if (bn_override) { bn = bn_override; split = split_override > 0 ? split_override : 1; }
-    if (a_kmajor && b_kmajor) return launch_mn<false, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
-    if (a_kmajor && !b_kmajor) return launch_mn<false, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
-    if (!a_kmajor && b_kmajor) return launch_mn<true, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
-    return launch_mn<true, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split);
+    if (a_kmajor && b_kmajor) return launch_mn<false, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split, b_static);
+    if (a_kmajor && !b_kmajor) return launch_mn<false, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split, b_static);
+    if (!a_kmajor && b_kmajor) return launch_mn<true, false, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split, b_static);
+    return launch_mn<true, true, Epi>(stream, A, lda, B, ldb, M, N, K, epi, bn, split, b_static);
 }
 }  // namespace tc

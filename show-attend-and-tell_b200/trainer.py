@@ -51,35 +51,43 @@ class FusedTrainStep:
         self.step_count = 0
         self._ws = None
         self._ws_key = None
+        self._a = None
+        self._a_ptrs = None
+        self._named = dict(decoder.named_parameters())
+        self._ptr_sig = None
+        self._ptr_list = None
+        self._grads = None
+        self._next_mask = None
         self.last_alphas = None
 
     def _args(self, img_features, captions, dropout_mask):
+        """The sat_decoder_args of this step.  The struct is built once per (shape, dtype, flags) and kept; a step only
+        refreshes the pointers that change (inputs, mask, stream) -- the host path between two steps is on the critical
+        path of a training loop that reads the loss back every step."""
         dec = self.dec
         L = _lib.lib()
         dev = img_features.device
         B, Lloc, D = img_features.shape
         T = captions.shape[1] - 1
-        a = _lib.DecoderArgs()
-        a.struct_bytes = C.sizeof(_lib.DecoderArgs)
-        a.dtype = _lib.dtype_code(dec.compute_dtype)
-        a.B, a.L, a.D, a.H, a.V, a.T = B, Lloc, D, dec.embedding_size, dec.vocabulary_size, T
-        a.tf, a.ado, a.attention, a.gate = (int(dec.use_tf), int(dec.use_advanced_deep_output), int(dec.use_attention),
-                                            int(dec.use_gate))
-        a.start_token = int(dec.start_token)
-        a.need_grad, a.fused_loss = 1, 1
-        a.alpha_c = float(self.alpha_c)
-        a.a_dtype = _lib.dtype_code(img_features.dtype)
-        a.img_features = img_features.data_ptr()
-        a.a_stride_b, a.a_stride_l, a.a_stride_d = img_features.stride()
-        a.captions = captions.data_ptr()
-        a.cap_stride = captions.stride(0)
-        a.dropout_mask = None if dropout_mask is None else dropout_mask.data_ptr()
-        named = dict(dec.named_parameters())
-        for field in _lib.PARAM_FIELDS:
-            p = named.get(_lib.PARAM_KEYS[field])
-            setattr(a, field, None if p is None else p.data_ptr())
-        key = (B, Lloc, D, T, a.a_dtype)
+        a_dtype = _lib.dtype_code(img_features.dtype)
+        # (strides and 16-byte alignment decide whether the library uses the features in place or compacts them into the
+        # workspace, which changes the workspace size)
+        key = (B, Lloc, D, T, a_dtype, bool(dec.use_tf), bool(dec.use_advanced_deep_output), bool(dec.use_attention),
+               bool(dec.use_gate), dec.compute_dtype, tuple(img_features.stride()), img_features.data_ptr() % 16 == 0)
         if self._ws_key != key:
+            a = _lib.DecoderArgs()
+            a.struct_bytes = C.sizeof(_lib.DecoderArgs)
+            a.dtype = _lib.dtype_code(dec.compute_dtype)
+            a.B, a.L, a.D, a.H, a.V, a.T = B, Lloc, D, dec.embedding_size, dec.vocabulary_size, T
+            a.tf, a.ado, a.attention, a.gate = (int(dec.use_tf), int(dec.use_advanced_deep_output), int(dec.use_attention),
+                                                int(dec.use_gate))
+            a.start_token = int(dec.start_token)
+            a.need_grad, a.fused_loss = 1, 1
+            a.a_dtype = a_dtype
+            a.img_features = img_features.data_ptr()
+            a.a_stride_b, a.a_stride_l, a.a_stride_d = img_features.stride()
+            a.captions = captions.data_ptr()
+            a.cap_stride = captions.stride(0)
             self.alphas = torch.empty(B, T, Lloc, device=dev, dtype=torch.float32)
             self.loss = torch.zeros(3, device=dev, dtype=torch.float32)
             # no (B,T,V) preds tensor: the fused loss reads the logits from the workspace (padded row pitch)
@@ -87,13 +95,36 @@ class FusedTrainStep:
             nbytes = C.c_int64(0)
             _lib.check(L.sat_decoder_workspace_bytes(C.byref(a), C.byref(nbytes)), "sat_decoder_workspace_bytes")
             self._ws = torch.empty(nbytes.value + 256, device=dev, dtype=torch.uint8)
-            self._ws_bytes = nbytes.value
+            a.workspace = self._ws.data_ptr() + ((-self._ws.data_ptr()) % 256)
+            a.workspace_bytes = nbytes.value
+            self._a = a
             self._ws_key = key
-        a.preds, a.alphas, a.loss = None, self.alphas.data_ptr(), self.loss.data_ptr()
-        a.workspace = self._ws.data_ptr() + ((-self._ws.data_ptr()) % 256)
-        a.workspace_bytes = self._ws_bytes
+        a = self._a
+        a.alpha_c = float(self.alpha_c)
+        a.img_features = img_features.data_ptr()
+        a.a_stride_b, a.a_stride_l, a.a_stride_d = img_features.stride()
+        a.captions = captions.data_ptr()
+        a.cap_stride = captions.stride(0)
+        a.dropout_mask = None if dropout_mask is None else dropout_mask.data_ptr()
+        # parameters are views into flat_param (fixed addresses) unless the caller re-assigned .data: re-read the pointers
+        # only when the parameter objects' storage moved
+        ptrs = self._param_ptrs()
+        if ptrs is not self._a_ptrs:
+            for field, ptr in ptrs:
+                setattr(a, field, ptr)
+            self._a_ptrs = ptrs
         a.stream = torch.cuda.current_stream(dev).cuda_stream
         return a
+
+    def _param_ptrs(self):
+        """[(C field, device pointer)] of every parameter; the list object is reused while no pointer changed."""
+        named = self._named
+        cur = tuple(p.data_ptr() for p in named.values())
+        if cur != self._ptr_sig:
+            self._ptr_sig = cur
+            self._ptr_list = [(field, None if named.get(_lib.PARAM_KEYS[field]) is None else named[_lib.PARAM_KEYS[field]].data_ptr())
+                              for field in _lib.PARAM_FIELDS]
+        return self._ptr_list
 
     def sync_grads(self):
         """The one exchange step of data-parallel training: sum the flat gradient buffer over the ranks (NCCL over
@@ -107,26 +138,48 @@ class FusedTrainStep:
         named = dict(self.dec.named_parameters())
         return [(k, (named[k].data_ptr() - base) // 4, named[k].numel()) for k in self.train_keys]
 
+    def _grad_struct(self):
+        if self._grads is None:
+            g = _lib.DecoderGrads()
+            g.struct_bytes = C.sizeof(_lib.DecoderGrads)
+            for field in _lib.PARAM_FIELDS:
+                v = self.grad_views.get(_lib.PARAM_KEYS[field])
+                setattr(g, field, None if v is None else v.data_ptr())
+            self._grads = g
+        return self._grads
+
+    def _fresh_mask(self, B, T, device):
+        """Scaled keep mask of nn.Dropout(p) (decoder.py:67): Bernoulli(1-p) / (1-p), two launches."""
+        p = self.dec.dropout.p
+        if not self.dec.training or p <= 0.0:
+            return None
+        return torch.empty(B, T, self.dec.embedding_size, device=device, dtype=torch.float32).bernoulli_(1.0 - p).mul_(1.0 / (1.0 - p))
+
     def step(self, img_features, captions, dropout_mask=None, optimizer_step=True):
         """One training step; returns the device tensor [ce, alpha_reg, total] (no host sync)."""
         dec = self.dec
         L = _lib.lib()
         captions = dec._check_inputs(img_features, captions)
-        if dropout_mask is None and dec.training:
-            dropout_mask = dec._dropout_mask(img_features.shape[0], captions.shape[1] - 1, img_features.device, None)
+        B, T = img_features.shape[0], captions.shape[1] - 1
+        own_mask = dropout_mask is None and dec.training
+        if own_mask:
+            # the mask of this step was drawn at the end of the previous one (behind its Adam kernel), so a step starts
+            # with its first CUDA kernel instead of four small RNG launches
+            m = self._next_mask
+            if m is None or m.shape[0] != B or m.shape[1] != T or m.device != img_features.device:
+                m = self._fresh_mask(B, T, img_features.device)
+            dropout_mask, self._next_mask = m, None
         a = self._args(img_features, captions, dropout_mask)
         _lib.check(L.sat_decoder_forward(C.byref(a)), "sat_decoder_forward")
-        g = _lib.DecoderGrads()
-        g.struct_bytes = C.sizeof(_lib.DecoderGrads)
-        for field in _lib.PARAM_FIELDS:
-            v = self.grad_views.get(_lib.PARAM_KEYS[field])
-            setattr(g, field, None if v is None else v.data_ptr())
-        _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(g)), "sat_decoder_backward")
+        _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(self._grad_struct())), "sat_decoder_backward")
         self.sync_grads()
         if optimizer_step:
             self.step_count += 1
             _lib.check(L.sat_adam_step(self.flat_param.data_ptr(), self.flat_grad.data_ptr(), self.exp_avg.data_ptr(),
                                        self.exp_avg_sq.data_ptr(), self.n, self.lr, self.betas[0], self.betas[1], self.eps,
                                        0.0, self.step_count, 1.0 / self.world, a.stream), "sat_adam_step")
+        if own_mask:
+            self._mask_in_use = dropout_mask          # keep it alive until the kernels that read it have been enqueued
+            self._next_mask = self._fresh_mask(B, T, img_features.device)
         self.last_alphas = self.alphas
         return self.loss

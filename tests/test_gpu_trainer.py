@@ -14,6 +14,7 @@ CASES = [
     dict(V=2531, D=512, B=9, L=196, T=5, ado=False, attention=True),      # small batch: cut partition + combine kernels
     dict(V=1003, D=2048, B=66, L=196, T=4, ado=False, attention=True),    # whole-item partition, V not a multiple of 8
     dict(V=640, D=512, B=6, L=49, T=4, ado=False, attention=False),
+    dict(V=300, D=512, B=144, L=196, T=3, ado=False, attention=True),     # B >= 128: recurrent loop as two half-batches on two streams
 ]
 
 
@@ -75,3 +76,41 @@ def test_fused_train_step_vs_oracle_adam(cfg, dt):
             assert err <= 0.05 * lr, (k, err)
         else:
             assert (got - ref.detach()).abs().max().item() <= 2.5 * lr * 2, k        # both moved at most ~lr per step
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16], ids=["fp32", "bf16"])
+@pytest.mark.parametrize("B,D", [(128, 2048), (272, 512)])
+def test_half_batch_pipelining_matches_single_stream(dt, B, D):
+    """sat_set_decoder_split: the two-stream half-batch loop and the single-stream loop compute the same step (only the
+    GEMM tile shapes differ with the row count): loss, alphas and every gradient agree to rounding (fp32 1e-5 of the
+    tensor's max, bf16 2e-2), and repeated split runs reproduce themselves (no race between the streams)."""
+    from sat_b200 import _lib
+    from sat_b200.decoder import Decoder
+    from sat_b200.trainer import FusedTrainStep
+    V, Hd, L, T = 333, 512, 196, 4
+    P = synth.make_params(V, D, Hd, seed=5, emb_scale=0.5)
+    a, cap = synth.make_inputs(B, L, D, T, V, seed=5)
+    masks = synth.make_dropout_masks(B, T, Hd).cuda()
+    ad, capd = a.cuda().to(dt), cap.cuda()
+    out = {}
+    try:
+        for mode in (0, 1, 1):
+            _lib.lib().sat_set_decoder_split(mode)
+            dec = Decoder(V, D, tf=True, attention=True, compute_dtype=dt)
+            dec.load_state_dict(P, strict=True)
+            dec = dec.cuda().train()
+            tr = FusedTrainStep(dec, lr=1e-3, distributed=False)
+            loss = tr.step(ad, capd, dropout_mask=masks, optimizer_step=False)
+            torch.cuda.synchronize()
+            res = (loss.clone(), tr.alphas.clone(), tr.flat_grad.clone())
+            if mode == 1 and 1 in out:
+                assert torch.equal(out[1][1], res[1])        # alphas: bit-identical
+                # gradients: identical up to the fp32 atomics of the embedding scatter-add
+                assert (out[1][2] - res[2]).abs().max().item() <= 1e-6 * out[1][2].abs().max().item()
+            out[mode] = res
+    finally:
+        _lib.lib().sat_set_decoder_split(0)
+    tol = 1e-5 if dt == torch.float32 else 2e-2
+    for x, y in zip(out[0], out[1]):
+        assert (x - y).abs().max().item() <= tol * max(1e-6, x.abs().max().item())
+    assert (out[1][1].sum(2) - 1).abs().max().item() < 1e-5
