@@ -38,6 +38,10 @@ int sat_set_gemm_static_weights(int on);
  * (sum over t + dW_att on the caller's stream, the small weight-gradient GEMMs / column sums on an internal side stream that
  * is joined back before the call returns), 0 = one chain */
 int sat_set_tail_overlap(int on);
+/* debug instrumentation: arm (on = 1) / disarm the %globaltimer phase stamps that CTA (0,0,0) of the two big in-loop GEMMs
+ * leaves (id 0 = gate GEMM, id 1 = dz GEMM; phases: 0 entry, 1 after the PDL wait, 2 first operand stage landed, 3 last MMA
+ * issued, 4 accumulator complete, 5 split-K exchange done, 6 epilogue done); out (16 values) receives the latest stamps */
+int sat_gemm_phase_stamps(int on, unsigned long long* out);
 /* tuning knob (default 0, see DESIGN.md for the measurements): 1 = sat_decoder_forward / sat_decoder_backward run the recurrent loop of a teacher-forced batch
  * (B >= 128, streaming attention shapes) as two half-batches on two streams, so that one half's latency-bound skinny GEMMs
  * overlap the other half's HBM-bound attention kernel; 0 = whole batch on the caller's stream */

@@ -79,6 +79,18 @@ int sat_set_gemm_splitk(int max_split) { g_gemm_max_split = max_split >= 1 ? max
 int sat_set_pdl(int on) { g_pdl = on ? 1 : 0; return SAT_OK; }
 int sat_set_gemm_static_weights(int on) { g_gemm_static_b = on ? 1 : 0; return SAT_OK; }
 int sat_set_tail_overlap(int on) { g_tail_overlap = on ? 1 : 0; return SAT_OK; }
+/* debug: on = 1 arms the phase stamps of the in-loop GEMMs (gate GEMM = id 1, dz GEMM = id 2); the call also copies the last
+ * stamps (nanoseconds of %globaltimer, 8 per id) into out[2][8] when out is not NULL (synchronises the device) */
+int sat_gemm_phase_stamps(int on, unsigned long long* out) {
+    if (out) {
+        unsigned long long all[4][8];
+        SAT_CHECK_CUDA(cudaDeviceSynchronize());
+        SAT_CHECK_CUDA(cudaMemcpyFromSymbol(all, g_gemm_dbg, sizeof(all)));
+        for (int i = 0; i < 2; ++i) for (int j = 0; j < 8; ++j) out[i * 8 + j] = all[i + 1][j];
+    }
+    SAT_CHECK_CUDA(cudaMemcpyToSymbol(g_gemm_dbg_on, &on, sizeof(int)));
+    return SAT_OK;
+}
 int sat_set_decoder_split(int on) { g_dec_split = on ? 1 : 0; g_split_chain = on == 2 ? 0 : 1; return SAT_OK; }
 int sat_set_decoder_split_sms(int attn_ctas, int gemm_sms) {
     g_split_attn_ctas = attn_ctas > 0 ? attn_ctas : 0; g_split_gemm_sms = gemm_sms > 0 ? gemm_sms : 0; return SAT_OK;

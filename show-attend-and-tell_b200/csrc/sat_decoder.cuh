@@ -11,6 +11,12 @@
 #include "sat_misc.cuh"
 
 extern int g_force_simt, g_gemm_static_b;
+// phase-stamp ids of the two big in-loop GEMMs (debug instrumentation in sat_gemm_tc.cuh)
+template <typename T, bool P> struct EpiDbgId<EpiLstm<T, P>> { static constexpr int value = 1; };
+template <typename T, bool P> struct EpiDbgId<EpiDzGate<T, P>> { static constexpr int value = 2; };
+// ... and both drain their accumulator through the coalesced path (sat_gemm_tc.cuh)
+template <typename T, bool P> struct EpiCoalesce<EpiLstm<T, P>> { static constexpr bool value = true; };
+template <typename T, bool P> struct EpiCoalesce<EpiDzGate<T, P>> { static constexpr bool value = true; };
 
 template <typename T> struct IsF32 { static constexpr bool value = std::is_same<T, float>::value; };
 

@@ -19,6 +19,21 @@ constexpr int BM = 128, BK = 64, UMMA_K = 16;
 constexpr int NPROD = SAT_GEMM_NPROD;
 }  // namespace tc
 extern int g_gemm_max_split;    // tuning knob (sat_set_gemm_splitk): largest split-K cluster size, 1 = never split
+// Debug instrumentation (sat_gemm_phase_stamps): when the flag is set, CTA (0,0,0) of a GEMM whose epilogue carries a
+// DBG_ID > 0 leaves %globaltimer stamps of its phases: 0 entry, 1 after the PDL wait, 2 first operand stage landed,
+// 3 last MMA issued, 4 accumulator complete (epilogue released), 5 split-K exchange done, 6 epilogue done.
+__device__ int g_gemm_dbg_on = 0;
+__device__ unsigned long long g_gemm_dbg[4][8];
+__device__ __forceinline__ unsigned long long gtimer() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+template <typename Epi> struct EpiDbgId { static constexpr int value = 0; };
+// Epilogues that read / write several global arrays per element (LSTM cell, gate backward) opt in to the COALESCED drain: the
+// accumulator tile is staged in the (dead) operand ring and re-read with consecutive lanes on consecutive 4-column chunks of
+// one row, so a warp's global access covers whole 128-byte segments instead of 32 different rows (phase stamps of the in-loop
+// GEMMs, profiles/r1_gemm_phases_*.txt: the row-per-thread drain was 7.8 of 15.4 us in the gate GEMM, 9.2 of 16.5 us in dz).
+template <typename Epi> struct EpiCoalesce { static constexpr bool value = false; };
+#define SAT_GEMM_STAMP(slot)                                                                         \
+    do { if (EpiDbgId<Epi>::value > 0 && (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && g_gemm_dbg_on)  \
+             g_gemm_dbg[EpiDbgId<Epi>::value][slot] = gtimer(); } while (0)
 namespace tc {
 #ifndef SAT_GEMM_EPI_GROUPS
 #define SAT_GEMM_EPI_GROUPS 4
@@ -119,6 +134,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) SAT_GEMM_STAMP(0);
     const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
     const int nk_all = (K + BK - 1) / BK;
     const int zsp = SPLIT > 1 ? (int)blockIdx.z : 0;
@@ -176,6 +192,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     // kernel's tail; its results are needed from here on.  Let the next kernel start its own prologue right away.
     pdl_wait();
     pdl_launch_dependents();
+    if (threadIdx.x == 0) SAT_GEMM_STAMP(1);
 
     if (producer) {
         for (int kb = kb_first; kb < nk; kb += NPROD) {
@@ -202,6 +219,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
                 const uint32_t ph = (kb / C::STAGES) & 1;
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after();
+                if (kb == 0) SAT_GEMM_STAMP(2);
                 const uint32_t a_addr = smem_u32(sA + s * C::A_BYTES);
                 const uint32_t b_addr = smem_u32(sB + s * C::B_BYTES);
 #pragma unroll
@@ -215,6 +233,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
                 }
                 umma_commit(&empty_bar[s]);          // frees the smem stage when these MMAs retire
             }
+            SAT_GEMM_STAMP(3);
             umma_commit(tmem_full_bar);              // accumulator complete
         }
     } else {
@@ -229,7 +248,33 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         }
         mbar_wait(tmem_full_bar, 0);
         tc_fence_after();
-        if constexpr (SPLIT == 1) {
+        if (warp == 2 && lane == 0) SAT_GEMM_STAMP(4);
+        if constexpr (SPLIT == 1 && EpiCoalesce<Epi>::value) {
+            constexpr int XP = BN + 4;               // padded row pitch: float4 accesses of 8 consecutive rows hit distinct banks
+            constexpr int PW0 = (BN / EPI_GROUPS > 8) ? BN / EPI_GROUPS : 8;
+            constexpr int PW = PW0 > 32 ? 32 : PW0;  // staging piece: 8, 16 or 32 columns
+            static_assert(BN % PW == 0 && BM * XP * 4 <= C::STAGES * C::STAGE_BYTES, "staging buffer must fit in the stage ring");
+            float* xbuf = reinterpret_cast<float*>(smem);     // the accumulator is complete: every MMA has read its stage
+            const int row = q * 32 + lane;
+#pragma unroll 1
+            for (int p = grp; p < BN / PW; p += EPI_GROUPS) {
+                float v[PW];
+                const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(p * PW);
+                if constexpr (PW == 32) tmem_ld32(ta, v); else if constexpr (PW == 16) tmem_ld16(ta, v); else tmem_ld8(ta, v);
+                float4* dst = reinterpret_cast<float4*>(xbuf + (size_t)row * XP + p * PW);
+#pragma unroll
+                for (int c4 = 0; c4 < PW / 4; ++c4) dst[c4] = make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
+            }
+            asm volatile("bar.sync 2, %0;" ::"n"(EPI_WARPS * 32) : "memory");      // epilogue warps only
+            constexpr int C4 = BN / 4;
+            for (int c = (warp - 2) * 32 + lane; c < BM * C4; c += EPI_WARPS * 32) {
+                const int r = c / C4, c4 = c - r * C4;
+                const float4 t = *reinterpret_cast<const float4*>(xbuf + (size_t)r * XP + c4 * 4);
+                const float acc[4] = {t.x, t.y, t.z, t.w};
+                const int n = n0 + c4 * 4;
+                if (n < N) epi.template apply<4>(m0 + r, n, acc);
+            }
+        } else if constexpr (SPLIT == 1) {
             constexpr int NC = BN / 32;
             if constexpr (NC >= EPI_GROUPS) {        // whole 32-column chunks, dealt round-robin to the groups
 #pragma unroll 1
@@ -277,6 +322,21 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
             __syncwarp();
             cluster_arrive_release();                // #2: my slices are in every peer's buffer ...
             cluster_wait_acquire();                  //     ... and every peer's slices are in mine
+            if (warp == 2 && lane == 0) SAT_GEMM_STAMP(5);
+            if constexpr (EpiCoalesce<Epi>::value) {
+                constexpr int C4 = CW / 4;
+                for (int c = (warp - 2) * 32 + lane; c < BM * C4; c += EPI_WARPS * 32) {
+                    const int r = c / C4, c4 = c - r * C4;
+                    float acc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+                    for (int sp = 0; sp < SPLIT; ++sp) {             // fixed order: deterministic
+                        const float4 t = *reinterpret_cast<const float4*>(xbuf + ((size_t)sp * BM + r) * XP + c4 * 4);
+                        acc[0] += t.x; acc[1] += t.y; acc[2] += t.z; acc[3] += t.w;
+                    }
+                    const int n = n0 + zsp * CW + c4 * 4;
+                    if (n < N) epi.template apply<4>(m0 + r, n, acc);
+                }
+            } else
 #pragma unroll 1
             for (int r = grp; r < CW / RW; r += EPI_GROUPS) {
                 float acc[RW];
@@ -306,6 +366,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     }
     tc_fence_before();
     __syncthreads();
+    if (threadIdx.x == 0) SAT_GEMM_STAMP(6);
     if (warp == 1) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(BN) : "memory");
     }

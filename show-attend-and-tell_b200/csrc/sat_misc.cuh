@@ -197,9 +197,12 @@ int sum_over_t(cudaStream_t s, T* out, const T* src, int64_t n, int Tn) {
 // rows of H columns; a block is `rpb` whole rows of 16-byte vectors wide, so with a grid stride that is a multiple of the
 // row length a thread meets the same columns every iteration and keeps their sums in registers.
 // part[block][H] holds per-block partial column sums (fp32, taken before rounding to T); colsum_final_kernel adds them.
-template <typename T>
-__global__ void sum_over_t_colsum_kernel(T* __restrict__ out, const T* __restrict__ src, int64_t nvec, int64_t n, int Tn, int H,
-                                         float* __restrict__ part) {
+// SHARE: the launch leaves room on every SM for a tcgen05 GEMM CTA of the other stream (608 threads x 80 registers): one
+// block of 256 threads x <= 64 registers per SM, eight loads in flight per thread (148 x 256 x 8 x 16 B = 4.8 MB in flight).
+template <typename T, bool SHARE>
+__global__ void __launch_bounds__(256, 4)
+sum_over_t_colsum_kernel(T* __restrict__ out, const T* __restrict__ src, int64_t nvec, int64_t n, int Tn, int H,
+                         float* __restrict__ part) {
     constexpr int VEC = Vec16<T>::N;
     extern __shared__ float red[];                 // [blockDim][VEC]
     const int cpr = H / VEC;                       // vectors per row
@@ -210,8 +213,21 @@ __global__ void sum_over_t_colsum_kernel(T* __restrict__ out, const T* __restric
         float acc[VEC];
 #pragma unroll
         for (int k = 0; k < VEC; ++k) acc[k] = 0.0f;
-#pragma unroll 5
-        for (int t = 0; t < Tn; ++t) {
+        constexpr int U = SHARE ? 8 : 5;
+        int t = 0;
+        for (; t + U <= Tn; t += U) {
+            uint4 raw[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) raw[u] = ldg_stream16(src + (size_t)(t + u) * n + i * VEC);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                float f[VEC];
+                Vec16<T>::unpack(raw[u], f);
+#pragma unroll
+                for (int k = 0; k < VEC; ++k) acc[k] += f[k];
+            }
+        }
+        for (; t < Tn; ++t) {
             float f[VEC];
             Vec16<T>::unpack(ldg_stream16(src + (size_t)t * n + i * VEC), f);
 #pragma unroll
@@ -238,7 +254,7 @@ __global__ void colsum_final_kernel(const float* __restrict__ part, int S, int N
 // out (rows x H, T) = sum_t src[t];  colsum_out[H] = column sums of that (fp32)
 template <typename T>
 int sum_over_t_colsum(cudaStream_t s, T* out, const T* src, int64_t rows, int H, int Tn, float* colsum_out, float* scratch,
-                      int64_t scratch_floats) {
+                      int64_t scratch_floats, bool share_sms = false) {
     constexpr int VEC = Vec16<T>::N;
     SAT_REQUIRE(H % VEC == 0 && H / VEC <= 1024, "sum_over_t_colsum: H must be a multiple of %d", VEC);
     const int cpr = H / VEC;
@@ -246,10 +262,23 @@ int sum_over_t_colsum(cudaStream_t s, T* out, const T* src, int64_t rows, int H,
     const int threads = cpr * rpb;
     const int64_t n = rows * H, nvec = n / VEC;
     int64_t blocks = sat_cdiv64(nvec, threads);
-    if (blocks > 4 * 148) blocks = 4 * 148;
+    share_sms = share_sms && threads == 256;
+    const int64_t cap = share_sms ? 148 : 4 * 148;
+    if (blocks > cap) blocks = cap;
     if (blocks * H > scratch_floats) blocks = scratch_floats / H;
     SAT_REQUIRE(blocks >= 1, "sum_over_t_colsum: scratch too small");
-    sum_over_t_colsum_kernel<T><<<(int)blocks, threads, (size_t)threads * VEC * 4, s>>>(out, src, nvec, n, Tn, H, scratch);
+    if (share_sms) {
+        // an SM cannot change its L1 / shared-memory split while blocks are resident: ask for the all-shared split so that a
+        // GEMM CTA (~200 KB of shared memory) can land beside this kernel's block
+        static bool configured = false;
+        if (!configured) {
+            SAT_CHECK_CUDA(cudaFuncSetAttribute(sum_over_t_colsum_kernel<T, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                                cudaSharedmemCarveoutMaxShared));
+            configured = true;
+        }
+        sum_over_t_colsum_kernel<T, true><<<(int)blocks, threads, (size_t)threads * VEC * 4, s>>>(out, src, nvec, n, Tn, H, scratch);
+    }
+    else sum_over_t_colsum_kernel<T, false><<<(int)blocks, threads, (size_t)threads * VEC * 4, s>>>(out, src, nvec, n, Tn, H, scratch);
     colsum_final_kernel<<<sat_cdiv(H, 32), 256, 0, s>>>(scratch, (int)blocks, H, colsum_out, 0);
     SAT_CHECK_CUDA(cudaGetLastError());
     return SAT_OK;
