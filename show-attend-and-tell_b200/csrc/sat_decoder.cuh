@@ -17,6 +17,8 @@ template <typename T, bool P> struct EpiDbgId<EpiDzGate<T, P>> { static constexp
 // ... and both drain their accumulator through the coalesced path (sat_gemm_tc.cuh)
 template <typename T, bool P> struct EpiCoalesce<EpiLstm<T, P>> { static constexpr bool value = true; };
 template <typename T, bool P> struct EpiCoalesce<EpiDzGate<T, P>> { static constexpr bool value = true; };
+// (EpiLinear too: measured on the whole c2 step 4.00 -> 3.94 ms, K1 + Xg + vocabulary GEMMs 238 -> 216 us)
+template <typename T, bool P> struct EpiCoalesce<EpiLinear<T, P>> { static constexpr bool value = true; };
 
 template <typename T> struct IsF32 { static constexpr bool value = std::is_same<T, float>::value; };
 
