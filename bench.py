@@ -29,6 +29,9 @@ WORKLOAD = ("c2: teacher-forced bf16 train step of the soft-attention LSTM decod
 METRIC, UNIT = "train_captions_per_s", "captions/s"
 
 
+_JSON_OUT = None
+
+
 def read_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -392,7 +395,7 @@ def run_ours(args, rank, world, local_rank):
                     "h2d_alone_ms": h2d_ms, "h2d_alone_gbs": host[0][0].numel() * 2 / h2d_ms / 1e6},
             "gpu_launches": None if launches is None else launches * args.steps,
             "roofline": roofline, "cpu_baseline": cpu, "beam": beam}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_JSON_OUT or sys.stdout, flush=True)
 
 
 def main():
@@ -409,6 +412,11 @@ def main():
         run_reference(args, rank)
         return
     args.warmup = max(args.warmup, 3)
+    # libraries (NCCL's version banner) write to fd 1: keep the real stdout for the ONE JSON line, send the rest to stderr
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")

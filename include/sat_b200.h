@@ -63,6 +63,11 @@ int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes);
 int sat_profile(int on);
 int sat_profile_read(float* ms, int* counts);
 
+/* train.py:144-145 / utils.py:44-80 `sequence_accuracy(preds, targets, k)`: rank[r] = number of logits of row r strictly above
+ * the logit of targets[r] (rows x V fp32 logits, row pitch ld; a target outside [0, V) gets rank V).  The target is in the top k
+ * iff rank < k, so top-1 and top-5 come out of ONE pass over the logits (the reference runs topk twice). */
+int sat_logit_rank(const float* logits, int64_t ld, int64_t rows, int V, const int64_t* targets, int32_t* rank, void* stream);
+
 /* Generic GEMM  C[M,N] = act(A[M,K] * B[N,K]^T + bias[N])  (nn.Linear: attention.py:15-16, decoder.py:99,125,139-145).
  * a_kmajor: A[m*lda+k] (1) or A[k*lda+m] (0); same for B.  Cf (fp32) and/or Ct (dtype) outputs, either may be NULL. */
 int sat_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, int a_kmajor, const void* B, int64_t ldb,
@@ -150,6 +155,9 @@ typedef struct sat_decoder_grads {
 } sat_decoder_grads;
 
 int sat_decoder_workspace_bytes(const sat_decoder_args* args, int64_t* bytes);
+/* The (B, T, ld) fp32 logits the last sat_decoder_forward call with these args produced: args->preds, or the padded copy in
+ * the workspace when the loss was fused (preds == NULL). */
+int sat_decoder_logits(const sat_decoder_args* args, const float** logits, int64_t* ld);
 int sat_decoder_forward(const sat_decoder_args* args);
 int sat_decoder_backward(const sat_decoder_args* args, const sat_decoder_grads* grads);
 

@@ -197,3 +197,14 @@ def caption(P: Params, a1: torch.Tensor, beam_size: int, *, ado: bool, attention
         return [0], alpha, True
     idx = done_p.index(max(done_p))                                         # decoder.py:265 (first max)
     return done_s[idx], done_a[idx], False
+
+
+def sequence_accuracy(preds: torch.Tensor, targets: torch.Tensor, k: int, ignore_index: int = 0) -> float:
+    """utils.py:44-80 restated: accuracy at k in percent over the tokens that are not `ignore_index`.
+    preds (B, T, V), targets (B, T); train.py:144-145 calls it with targets = captions[:, 1:] and k = 1, 5."""
+    _, topk = preds.topk(k, dim=2, largest=True, sorted=True)                  # utils.py:55
+    mask = targets.ne(ignore_index)                                            # utils.py:61
+    correct = topk.eq(targets.unsqueeze(-1).expand_as(topk)) * mask.unsqueeze(-1)   # utils.py:64-65
+    correct_total = correct.any(dim=2).float().sum()                           # utils.py:68-71
+    n = mask.sum()                                                             # utils.py:77
+    return (correct_total.item() * 100.0 / n.item()) if n.item() > 0 else 0    # utils.py:80

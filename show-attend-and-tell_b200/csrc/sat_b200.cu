@@ -113,6 +113,33 @@ int sat_profile_read(float* ms, int* counts) {
     return SAT_OK;
 }
 
+/* utils.py:44-80 (sequence_accuracy) in one pass: rank[r] = #{v : logits[r, v] > logits[r, targets[r]]} for `rows` rows of V
+ * logits with row pitch ld.  The target is among the top k exactly when rank < k (a tie counts for the target). */
+int sat_logit_rank(const float* logits, int64_t ld, int64_t rows, int V, const int64_t* targets, int32_t* rank, void* stream) {
+    SAT_TRY(require_sm100());
+    SAT_REQUIRE(logits && targets && rank && V > 0 && ld >= V && rows >= 0, "sat_logit_rank: bad arguments");
+    if (rows == 0) return SAT_OK;
+    SAT_REQUIRE(rows < (int64_t)1 << 31, "sat_logit_rank: too many rows");
+    misc::logit_rank_kernel<<<(unsigned)rows, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(logits, ld, V, targets, rank);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+/* Where the (B, T, ld) fp32 logits of the last sat_decoder_forward with these args live: args->preds when it was given, else
+ * the padded copy inside the workspace (fused loss). */
+int sat_decoder_logits(const sat_decoder_args* a, const float** logits, int64_t* ld) {
+    SAT_TRY(check_args(a));
+    SAT_REQUIRE(logits && ld, "sat_decoder_logits: null output");
+    if (a->dtype == SAT_DTYPE_F32) {
+        DecWs<float> w; carve<float>(*a, w, reinterpret_cast<uint8_t*>(a->workspace));
+        *logits = a->preds ? a->preds : w.logits_tmp; *ld = w.ldl;
+    } else {
+        DecWs<bf16> w; carve<bf16>(*a, w, reinterpret_cast<uint8_t*>(a->workspace));
+        *logits = a->preds ? a->preds : w.logits_tmp; *ld = w.ldl;
+    }
+    return SAT_OK;
+}
+
 int sat_gemm(int dtype, int M, int N, int K, const void* A, int64_t lda, int a_kmajor, const void* B, int64_t ldb,
              int b_kmajor, const float* bias, int act, float* Cf, int64_t ldcf, void* Ct, int64_t ldct, int bn_override,
              void* stream) {

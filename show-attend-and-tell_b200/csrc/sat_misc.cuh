@@ -99,6 +99,30 @@ struct PackList {
         return SAT_OK;
     }
 };
+// rank[r] = number of logits in row r strictly above the target's logit (utils.py:44-80 sequence_accuracy asks whether the
+// target is among the top k = whether rank < k; one pass over the logits instead of two topk passes).  A target outside
+// [0, V) gets rank V (never correct).  One block per row.
+__global__ void __launch_bounds__(256) logit_rank_kernel(const float* __restrict__ logits, int64_t ld, int V,
+                                                         const int64_t* __restrict__ targets, int32_t* __restrict__ rank) {
+    __shared__ int red[8];
+    const int64_t r = blockIdx.x;
+    const int64_t tgt = targets[r];
+    if (tgt < 0 || tgt >= V) { if (threadIdx.x == 0) rank[r] = V; return; }
+    const float* p = logits + r * ld;
+    const float x = p[tgt];
+    int n = 0;
+    for (int v = threadIdx.x; v < V; v += blockDim.x) n += (p[v] > x) ? 1 : 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < 8; ++w) t += red[w];
+        rank[r] = t;
+    }
+}
+
 // inverse of pack_weight for gradients: dst_fp32[r, c0 + c] = src[perm(r), c]   (dst row pitch ld_dst)
 __global__ void unpack_grad_kernel(float* __restrict__ dst, int64_t ld_dst, const float* __restrict__ src, int64_t ld_src,
                                    int rows, int cols, int c0, int ilH) {

@@ -183,3 +183,23 @@ class FusedTrainStep:
             self._next_mask = self._fresh_mask(B, T, img_features.device)
         self.last_alphas = self.alphas
         return self.loss
+
+    def accuracy_counts(self, captions, ks=(1, 5), ignore_index=3):
+        """train.py:144-145 for the step just run: device tensor [correct@1, correct@5, non-padding tokens] over
+        targets = captions[:, 1:] (all T positions, utils.py:44-80), from the logits still in the workspace.  One pass over
+        the logits, no host sync; accuracy in percent = 100 * correct / tokens.  ignore_index: `<pad>` = 3 in the plain
+        vocabulary (generate_json_data.py:44-48), 0 for BERT."""
+        from . import metrics
+        if self._a is None:
+            raise RuntimeError("accuracy_counts() needs a step() first")
+        L = _lib.lib()
+        ptr, ld = C.c_void_p(), C.c_int64()
+        _lib.check(L.sat_decoder_logits(C.byref(self._a), C.byref(ptr), C.byref(ld)), "sat_decoder_logits")
+        a = self._a
+        targets = captions[:, 1:].to(torch.int64).contiguous()
+        if targets.shape != (a.B, a.T):
+            raise RuntimeError(f"captions {tuple(captions.shape)} do not belong to the last step (B={a.B}, T={a.T})")
+        rank = torch.empty(a.B, a.T, device=targets.device, dtype=torch.int32)
+        _lib.check(L.sat_logit_rank(ptr.value, ld.value, a.B * a.T, a.V, targets.data_ptr(), rank.data_ptr(),
+                                    torch.cuda.current_stream(targets.device).cuda_stream), "sat_logit_rank")
+        return metrics.accuracy_counts(rank, targets, ks, ignore_index)

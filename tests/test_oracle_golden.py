@@ -47,3 +47,19 @@ def test_caption_matches_reference(path):
             assert fb == bool(z[f"fallback{i}"][0])
             got = alpha.numpy() if torch.is_tensor(alpha) else np.array(alpha, dtype=np.float32)
             np.testing.assert_allclose(got, z[f"alpha{i}"], rtol=1e-4, atol=1e-6)
+
+
+def test_oracle_sequence_accuracy_matches_reference_golden():
+    """oracle.sequence_accuracy (utils.py:44-80 restated) against values the live reference function returned
+    (tests/golden/make_golden_accuracy.py): exact to float rounding."""
+    import os
+    import numpy as np
+    import torch
+    from oracle import sat_oracle as O
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "acc_sequence_accuracy.npz"))
+    for i in range(3):
+        pad = int(z[f"case{i}_cfg"][3])
+        preds, targets = torch.from_numpy(z[f"case{i}_preds"]), torch.from_numpy(z[f"case{i}_targets"])
+        got = [O.sequence_accuracy(preds, targets, k, ignore_index=pad) for k in (1, 3, 5)]
+        np.testing.assert_allclose(got, z[f"case{i}_acc"], rtol=0, atol=1e-9)
+    assert O.sequence_accuracy(torch.randn(2, 3, 9), torch.zeros(2, 3, dtype=torch.long), 1) == z["empty_acc"][0] == 0
