@@ -229,6 +229,8 @@ def run_ours(args, rank, world, local_rank):
     L = _lib.lib()
     if "SAT_DEC_SPLIT" in os.environ:                      # A/B switch for the half-batch pipelining (default on)
         L.sat_set_decoder_split(int(os.environ["SAT_DEC_SPLIT"]))
+    if "SAT_FUSE_CELL" in os.environ:
+        L.sat_set_fused_cell_backward(int(os.environ["SAT_FUSE_CELL"]))
     if "SAT_TAIL" in os.environ:
         L.sat_set_tail_overlap(int(os.environ["SAT_TAIL"]))
     if "SAT_STATIC_W" in os.environ:

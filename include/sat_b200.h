@@ -38,6 +38,9 @@ int sat_set_gemm_static_weights(int on);
  * (sum over t + dW_att on the caller's stream, the small weight-gradient GEMMs / column sums on an internal side stream that
  * is joined back before the call returns), 0 = one chain */
 int sat_set_tail_overlap(int on);
+/* tuning knob: 1 (default) = with attention on, the LSTM cell backward of step t-1 runs in the epilogue of step t's dh GEMM;
+ * 0 = the pointwise kernel is launched every step */
+int sat_set_fused_cell_backward(int on);
 /* debug instrumentation: arm (on = 1) / disarm the %globaltimer phase stamps that CTA (0,0,0) of the two big in-loop GEMMs
  * leaves (id 0 = gate GEMM, id 1 = dz GEMM; phases: 0 entry, 1 after the PDL wait, 2 first operand stage landed, 3 last MMA
  * issued, 4 accumulator complete, 5 split-K exchange done, 6 epilogue done); out (16 values) receives the latest stamps */

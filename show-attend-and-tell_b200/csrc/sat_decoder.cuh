@@ -17,6 +17,7 @@ template <typename T, bool P> struct EpiDbgId<EpiDzGate<T, P>> { static constexp
 // ... and both drain their accumulator through the coalesced path (sat_gemm_tc.cuh)
 template <typename T, bool P> struct EpiCoalesce<EpiLstm<T, P>> { static constexpr bool value = true; };
 template <typename T, bool P> struct EpiCoalesce<EpiDzGate<T, P>> { static constexpr bool value = true; };
+template <typename T, bool P> struct EpiCoalesce<EpiDhCell<T, P>> { static constexpr bool value = true; };
 // (EpiLinear too: measured on the whole c2 step 4.00 -> 3.94 ms, K1 + Xg + vocabulary GEMMs 238 -> 216 us)
 template <typename T, bool P> struct EpiCoalesce<EpiLinear<T, P>> { static constexpr bool value = true; };
 
@@ -44,7 +45,7 @@ static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 // space; a half is only a row range [b0, b0 + nb) of every time-major slice.  The side stream and its two events are
 // created once per host thread and device; the caller's stream forks into it before the loop and joins after it.
 // ---------------------------------------------------------------------------------------------------
-extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap;
+extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd;
 struct SideStream { cudaStream_t s; cudaEvent_t fork, join, attn_done[2]; bool ok; };
 static inline int side_stream(SideStream** out) {
     static thread_local SideStream cache[32] = {};
@@ -480,8 +481,10 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         const size_t r = (size_t)t * B + b0;       // first time-major row of this half at step t
         float* dzh = w.dZH + (size_t)b0 * zw;
         float* dh_carry = w.dh_carry + (size_t)b0 * H;
-        // (the cell backward stays a kernel of its own: fused into the 16-CTA dh GEMM below it ran 3x slower)
-        {
+        // The cell backward of step t runs in the epilogue of the previous iteration's dh GEMM (EpiDhCell) when attention is on;
+        // only the first iteration (t = T-1, dh_carry = 0) and the no-attention decoder launch the pointwise kernel.
+        const bool cell_fused = g_fuse_cell_bwd && a.attention;
+        if (!cell_fused || t == Tn - 1) {
             cudaLaunchConfig_t cfg;
             cudaLaunchAttribute attr[1];
             pdl_config(&cfg, attr, dim3(sat_cdiv(H, 128), nb), dim3(128), 0, s);
@@ -531,8 +534,23 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
             SAT_TRY((attn_step_bwd<T, PRECISE>(p, s)));
             if (rec_ev) SAT_CHECK_CUDA(cudaEventRecord(rec_ev, s));
             // dh_prev = dZH[:, D:] + [dUh | dfb] [U ; f_beta]
-            auto e = lin<T>(nb, H, nullptr, SAT_ACT_NONE, dh_carry, H, nullptr, 0, dzh + D, zw);
-            SAT_TRY(gemm<T>(s, w.dUF + r * (H + D), H + D, true, w.w_uf, H, false, nb, H, H + D, e, 0, gsm, 1));
+            if (cell_fused && t > 0) {
+                const size_t rp = (size_t)(t - 1) * B + b0;      // rows of step t-1
+                EpiDhCell<T, PRECISE> e;
+                e.addend = dzh + D; e.ld_add = zw;
+                e.gates = w.Gates + rp * 4 * H; e.ld_g = 4 * H;
+                e.c_prev = w.Cst + rp * H; e.ld_cp = H;
+                e.c_new = w.Cst + r * H; e.ld_cn = H;            // Cst[t] = state leaving step t-1
+                e.dhd = w.dHd + rp * H; e.ld_dhd = H;
+                e.mask = a.dropout_mask ? a.dropout_mask + ((size_t)b0 * Tn + (t - 1)) * H : nullptr; e.ld_mask = (int64_t)Tn * H;
+                e.dc_carry = w.dc_carry + (size_t)b0 * H; e.ld_dc = H;
+                e.dG = w.dG + rp * 4 * H; e.ld_dg = 4 * H;
+                e.M = nb; e.H = H;
+                SAT_TRY(gemm<T>(s, w.dUF + r * (H + D), H + D, true, w.w_uf, H, false, nb, H, H + D, e, 0, gsm, 1));
+            } else {
+                auto e = lin<T>(nb, H, nullptr, SAT_ACT_NONE, dh_carry, H, nullptr, 0, dzh + D, zw);
+                SAT_TRY(gemm<T>(s, w.dUF + r * (H + D), H + D, true, w.w_uf, H, false, nb, H, H + D, e, 0, gsm, 1));
+            }
         } else {
             // no attention: z is the constant mean feature; only the hidden path carries on
             SAT_CHECK_CUDA(cudaMemcpy2DAsync(dh_carry, (size_t)H * 4, dzh + D, (size_t)zw * 4, (size_t)H * 4, nb,

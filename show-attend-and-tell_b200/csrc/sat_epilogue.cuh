@@ -143,6 +143,79 @@ struct EpiDzGate {
     }
 };
 
+// Epilogue of the BPTT GEMM  d h_{t-1} = dZH[:, D:] + [dUh | dfb] [U ; f_beta]  with the LSTM cell backward of step t-1 fused in
+// (the pointwise kernel misc::lstm_bwd_kernel, same arithmetic): column n is hidden unit n, so the epilogue turns d h_{t-1} of
+// a (row, unit) straight into the four gate gradients of step t-1 and the carried d c, and one launch per BPTT step goes away.
+//   dh   = acc + addend + dhd * mask            (dhd = gradient from the output layer at step t-1, through dropout)
+//   d_o  = dh tanh(c) o (1-o) ;  dc = dh o (1 - tanh(c)^2) + dc_carry
+//   d_i  = dc g i (1-i) ;  d_f = dc c_prev f (1-f) ;  d_g = dc i (1-g^2) ;  dc_carry <- dc f
+template <typename T, bool PRECISE>
+struct EpiDhCell {
+    const float* addend;     // fp32 [M, ld_add]: direct d h_prev of this step (dZH[:, D:])
+    int64_t ld_add;
+    const T* gates;          // [M, ld_g] activated gates of step t-1 (interleaved i,f,g,o per unit)
+    int64_t ld_g;
+    const float* c_prev;     // fp32 [M, ld_cp] cell state entering step t-1
+    int64_t ld_cp;
+    const float* c_new;      // fp32 [M, ld_cn] cell state leaving step t-1
+    int64_t ld_cn;
+    const float* dhd;        // fp32 [M, ld_dhd] or null
+    int64_t ld_dhd;
+    const float* mask;       // fp32 [M, ld_mask] scaled keep mask or null
+    int64_t ld_mask;
+    float* dc_carry;         // fp32 [M, ld_dc], read-modify-write
+    int64_t ld_dc;
+    T* dG;                   // [M, ld_dg] gate gradients of step t-1 (interleaved)
+    int64_t ld_dg;
+    int M, H;
+
+    __device__ __forceinline__ void prefetch(int m, int n, int nc) const {
+        if (m >= M) return;
+        for (int c = 0; c < 4 * nc; c += 128 / (int)sizeof(T)) l2_prefetch(gates + (int64_t)m * ld_g + 4 * n + c);
+        l2_prefetch(c_prev + (int64_t)m * ld_cp + n);
+        l2_prefetch(c_new + (int64_t)m * ld_cn + n);
+        if (dhd) l2_prefetch(dhd + (int64_t)m * ld_dhd + n);
+        if (mask) l2_prefetch(mask + (int64_t)m * ld_mask + n);
+    }
+
+    template <int NV>
+    __device__ __forceinline__ void apply(int m, int n0, const float* acc) const {
+        if (m >= M) return;
+#pragma unroll
+        for (int q = 0; q < NV / 4; ++q) {
+            const int n = n0 + 4 * q;
+            if (n >= H) return;                       // H is a multiple of 8: groups of four units are all-in or all-out
+            float dh[4], cp[4], cn[4], dcc[4];
+            load4<float>(addend + (int64_t)m * ld_add + n, dh);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) dh[i] += acc[4 * q + i];
+            if (dhd) {
+                float d[4], mk[4] = {1.0f, 1.0f, 1.0f, 1.0f};
+                load4<float>(dhd + (int64_t)m * ld_dhd + n, d);
+                if (mask) load4<float>(mask + (int64_t)m * ld_mask + n, mk);
+#pragma unroll
+                for (int i = 0; i < 4; ++i) dh[i] += d[i] * mk[i];
+            }
+            load4<float>(c_prev + (int64_t)m * ld_cp + n, cp);
+            load4<float>(c_new + (int64_t)m * ld_cn + n, cn);
+            load4<float>(dc_carry + (int64_t)m * ld_dc + n, dcc);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                float g[4];
+                load4<T>(gates + (int64_t)m * ld_g + 4 * (n + i), g);
+                const float gi = g[0], gf = g[1], gg = g[2], go = g[3];
+                const float tc = tanhf(cn[i]);
+                const float d_o = dh[i] * tc * go * (1.0f - go);
+                const float dc = dh[i] * go * (1.0f - tc * tc) + dcc[i];
+                const float o4[4] = {dc * gg * gi * (1.0f - gi), dc * cp[i] * gf * (1.0f - gf), dc * gi * (1.0f - gg * gg), d_o};
+                dcc[i] = dc * gf;
+                store4<T>(dG + (int64_t)m * ld_dg + 4 * (n + i), o4);
+            }
+            *reinterpret_cast<float4*>(dc_carry + (int64_t)m * ld_dc + n) = make_float4(dcc[0], dcc[1], dcc[2], dcc[3]);
+        }
+    }
+};
+
 // LSTM cell epilogue (a7: decoder.py:115 nn.LSTMCell).  The gate GEMM's N axis is gate-interleaved:
 // column n = 4*j + g with g in (i,f,g,o) for hidden unit j, so one group of 4 columns is one unit.
 template <typename T, bool PRECISE>
