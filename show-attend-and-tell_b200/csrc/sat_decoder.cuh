@@ -45,7 +45,7 @@ static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 // space; a half is only a row range [b0, b0 + nb) of every time-major slice.  The side stream and its two events are
 // created once per host thread and device; the caller's stream forks into it before the loop and joins after it.
 // ---------------------------------------------------------------------------------------------------
-extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd;
+extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap;
 struct SideStream { cudaStream_t s; cudaEvent_t fork, join, attn_done[2]; bool ok; };
 static inline int side_stream(SideStream** out) {
     static thread_local SideStream cache[32] = {};
@@ -292,35 +292,52 @@ int decoder_forward_t(const sat_decoder_args& a) {
         else
             SAT_TRY((misc::cast3d<bf16, T>(st, w.a_c, reinterpret_cast<const bf16*>(a.img_features), B, L, D, a.a_stride_b, a.a_stride_l, a.a_stride_d)));
     }
-    // initial state (decoder.py:137-147): [h0 | c0] = tanh(abar [init_h; init_c]^T + b)
-    SAT_TRY(misc::mean_l<T>(st, w.a_c, w.abar_f, w.abar, B, L, D, w.mean_part, (int64_t)4 * B * D));
-    {
-        auto e = lin<T>(B, 2 * H, w.b_init, SAT_ACT_TANH, w.hc0, 2 * H, nullptr, 0);
-        SAT_TRY(gemm<T>(st, w.abar, D, true, w.w_init, D, true, B, 2 * H, D, e));
-        misc::init_state_scatter_kernel<T><<<sat_cdiv(B * H, 256), 256, 0, st>>>(w.hc0, w.ZH + D, zw, w.Cst, H, B, H);
-        SAT_CHECK_CUDA(cudaGetLastError());
+    // Before the loop, two independent pieces: K1 (tensor-bound, 42 registers per thread, one CTA per SM) on the caller's stream
+    // and, with attention on, everything else -- mean over L, initial state, embeddings and their gate share -- on the side
+    // stream.  The HBM-bound mean_l blocks fit on the SMs BESIDE the K1 CTAs and read the same features K1 is pulling through L2.
+    const bool head_overlap = g_head_overlap && a.attention;
+    SideStream* hd = nullptr;
+    cudaStream_t sh = st;
+    if (head_overlap) {
+        SAT_TRY(side_stream(&hd));
+        sh = hd->s;
+        SAT_CHECK_CUDA(cudaEventRecord(hd->fork, st));
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(sh, hd->fork, 0));
     }
     if (a.attention) {
         // K1: hoisted encoder projection Wa = a W^T + b_W (attention.py:16, Q3)
         auto e = lin<T>(B * L, H, a.att_W_b, SAT_ACT_NONE, nullptr, 0, w.wa, H);
         SAT_TRY(gemm<T>(st, w.a_c, D, true, w.w_att, D, true, B * L, H, D, e));
-    } else {
+    }
+    // initial state (decoder.py:137-147): [h0 | c0] = tanh(abar [init_h; init_c]^T + b)
+    SAT_TRY(misc::mean_l<T>(sh, w.a_c, w.abar_f, w.abar, B, L, D, w.mean_part, (int64_t)4 * B * D));
+    {
+        auto e = lin<T>(B, 2 * H, w.b_init, SAT_ACT_TANH, w.hc0, 2 * H, nullptr, 0);
+        SAT_TRY(gemm<T>(sh, w.abar, D, true, w.w_init, D, true, B, 2 * H, D, e));
+        misc::init_state_scatter_kernel<T><<<sat_cdiv(B * H, 256), 256, 0, sh>>>(w.hc0, w.ZH + D, zw, w.Cst, H, B, H);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    }
+    if (!a.attention) {
         // decoder.py:101-105: alpha = 1/L, context = mean(a), no gate; identical for every step
         dim3 g(Tn, B);
-        misc::bcast_rows_kernel<T><<<g, 128, 0, st>>>(w.ZH, (int64_t)B * zw, zw, w.abar, D, Tn);
-        misc::bcast_rows_kernel<T><<<g, 128, 0, st>>>(w.Ctx, (int64_t)B * D, D, w.abar, D, Tn);
-        misc::fill_kernel<<<misc::grid_for((int64_t)B * Tn * L), 256, 0, st>>>(a.alphas, (int64_t)B * Tn * L, 1.0f / (float)L);
+        misc::bcast_rows_kernel<T><<<g, 128, 0, sh>>>(w.ZH, (int64_t)B * zw, zw, w.abar, D, Tn);
+        misc::bcast_rows_kernel<T><<<g, 128, 0, sh>>>(w.Ctx, (int64_t)B * D, D, w.abar, D, Tn);
+        misc::fill_kernel<<<misc::grid_for((int64_t)B * Tn * L), 256, 0, sh>>>(a.alphas, (int64_t)B * Tn * L, 1.0f / (float)L);
         SAT_CHECK_CUDA(cudaGetLastError());
     }
     // embeddings (decoder.py:85-89) and their share of the gate pre-activations, batched over t when teacher forcing
     if (a.tf) {
-        misc::gather_bt_kernel<T><<<B * Tn, 128, 0, st>>>(w.E, a.embedding, H, a.captions, a.cap_stride, B, V);
+        misc::gather_bt_kernel<T><<<B * Tn, 128, 0, sh>>>(w.E, a.embedding, H, a.captions, a.cap_stride, B, V);
         SAT_CHECK_CUDA(cudaGetLastError());
         auto e = lin<T>(B * Tn, 4 * H, w.b_g, SAT_ACT_NONE, w.Xg, 4 * H, nullptr, 0);
-        SAT_TRY(gemm<T>(st, w.E, H, true, w.w_gx, H, true, B * Tn, 4 * H, H, e));
+        SAT_TRY(gemm<T>(sh, w.E, H, true, w.w_gx, H, true, B * Tn, 4 * H, H, e));
     } else {
-        misc::fill_tokens_kernel<<<sat_cdiv(B, 128), 128, 0, st>>>(w.tok_in, B, (int64_t)a.start_token);
+        misc::fill_tokens_kernel<<<sat_cdiv(B, 128), 128, 0, sh>>>(w.tok_in, B, (int64_t)a.start_token);
         SAT_CHECK_CUDA(cudaGetLastError());
+    }
+    if (head_overlap) {
+        SAT_CHECK_CUDA(cudaEventRecord(hd->join, sh));
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(st, hd->join, 0));
     }
     // one decode step for the captions [b0, b0 + nb) on stream s
     auto fwd_step = [&](int t, int b0, int nb, cudaStream_t s, uint8_t* scratch, cudaEvent_t wait_ev, cudaEvent_t rec_ev) -> int {
