@@ -37,7 +37,8 @@ int sat_set_gemm_static_weights(int on);
 /* tuning knob: 1 (default) = sat_decoder_backward runs the work after the BPTT loop as two independent chains on two streams
  * (sum over t + dW_att on the caller's stream, the small weight-gradient GEMMs / column sums on an internal side stream that
  * is joined back before the call returns), and sat_decoder_forward runs the initial-state / embedding work on that side
- * stream beside the encoder-projection GEMM; 0 = one chain */
+ * stream beside the encoder-projection GEMM; 0 = one chain; 2 = like 1 with a register-thin, shared-memory-staged sum over t
+ * that GEMM CTAs of the side chain can run beside (experimental: measured slower) */
 int sat_set_tail_overlap(int on);
 /* tuning knob: 1 (default) = with attention on, the LSTM cell backward of step t-1 runs in the epilogue of step t's dh GEMM;
  * 0 = the pointwise kernel is launched every step */

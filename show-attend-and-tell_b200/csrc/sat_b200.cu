@@ -80,7 +80,7 @@ int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes) {
 int sat_set_gemm_splitk(int max_split) { g_gemm_max_split = max_split >= 1 ? max_split : 1; return SAT_OK; }
 int sat_set_pdl(int on) { g_pdl = on ? 1 : 0; return SAT_OK; }
 int sat_set_gemm_static_weights(int on) { g_gemm_static_b = on ? 1 : 0; return SAT_OK; }
-int sat_set_tail_overlap(int on) { g_tail_overlap = on ? 1 : 0; g_head_overlap = on ? 1 : 0; return SAT_OK; }
+int sat_set_tail_overlap(int on) { g_tail_overlap = on == 2 ? 2 : (on ? 1 : 0); g_head_overlap = on ? 1 : 0; return SAT_OK; }
 int sat_set_fused_cell_backward(int on) { g_fuse_cell_bwd = on ? 1 : 0; return SAT_OK; }
 /* debug: on = 1 arms the phase stamps of the in-loop GEMMs (gate GEMM = id 1, dz GEMM = id 2); the call also copies the last
  * stamps (nanoseconds of %globaltimer, 8 per id) into out[2][8] when out is not NULL (synchronises the device) */

@@ -614,7 +614,7 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         bool att_W_b_done = false;
         if (w.attn_stream) {
             if (g.att_W_b) {     // one pass: sum over t + the bias gradient's column sums
-                SAT_TRY(misc::sum_over_t_colsum<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L, H, Tn, g.att_W_b, w.csum, w.csum_floats));
+                SAT_TRY(misc::sum_over_t_colsum<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L, H, Tn, g.att_W_b, w.csum, w.csum_floats, g_tail_overlap == 2));
                 att_W_b_done = true;
             } else {
                 SAT_TRY(misc::sum_over_t<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L * H, Tn));

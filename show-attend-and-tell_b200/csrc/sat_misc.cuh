@@ -221,10 +221,12 @@ int sum_over_t(cudaStream_t s, T* out, const T* src, int64_t n, int Tn) {
 // rows of H columns; a block is `rpb` whole rows of 16-byte vectors wide, so with a grid stride that is a multiple of the
 // row length a thread meets the same columns every iteration and keeps their sums in registers.
 // part[block][H] holds per-block partial column sums (fp32, taken before rounding to T); colsum_final_kernel adds them.
-// SHARE: the launch leaves room on every SM for a tcgen05 GEMM CTA of the other stream (608 threads x 80 registers): one
-// block of 256 threads x <= 64 registers per SM, eight loads in flight per thread (148 x 256 x 8 x 16 B = 4.8 MB in flight).
+// SHARE: the launch leaves room on every SM for a tcgen05 GEMM CTA of the other stream (19 warps x 80 registers).  The register
+// file is split per SM sub-partition (16 K registers each): the GEMM's 5 warps there take 12 800, so this kernel's 2 warps per
+// sub-partition must stay at <= 48 registers (2 x 1536 = 3072; at 64 registers the 4096 did NOT fit and the GEMM CTA was never
+// co-scheduled, profiles/r1_tail_overlap.txt).  One block of 256 threads per SM, six loads in flight per thread.
 template <typename T, bool SHARE>
-__global__ void __launch_bounds__(256, 4)
+__global__ void __launch_bounds__(256, SHARE ? 5 : 4)
 sum_over_t_colsum_kernel(T* __restrict__ out, const T* __restrict__ src, int64_t nvec, int64_t n, int Tn, int H,
                          float* __restrict__ part) {
     constexpr int VEC = Vec16<T>::N;
@@ -237,7 +239,7 @@ sum_over_t_colsum_kernel(T* __restrict__ out, const T* __restrict__ src, int64_t
         float acc[VEC];
 #pragma unroll
         for (int k = 0; k < VEC; ++k) acc[k] = 0.0f;
-        constexpr int U = SHARE ? 8 : 5;
+        constexpr int U = SHARE ? 6 : 5;
         int t = 0;
         for (; t + U <= Tn; t += U) {
             uint4 raw[U];
@@ -274,6 +276,68 @@ sum_over_t_colsum_kernel(T* __restrict__ out, const T* __restrict__ src, int64_t
         }
     }
 }
+// The same pass built to run BESIDE a tcgen05 GEMM CTA of another stream (backward tail, sat_decoder.cuh): the bytes in flight
+// live in shared memory instead of registers.  One 256-thread block per SM (<= 48 registers: the GEMM leaves 3.5 K registers per
+// SM sub-partition), two cp.async stages of Tn x CV vectors (~26 KB, what a 193 KB GEMM CTA leaves free).  A chunk is CV
+// consecutive 16-byte vectors, shorter than a row, so its vectors are distinct columns: column sums accumulate in shared memory.
+template <typename T>
+__global__ void __launch_bounds__(256, 5)
+sum_over_t_async_kernel(T* __restrict__ out, const T* __restrict__ src, int64_t nvec, int64_t n, int Tn, int H, int CV,
+                        float* __restrict__ part) {
+    constexpr int VEC = Vec16<T>::N;
+    extern __shared__ __align__(16) uint8_t sm_raw[];
+    uint4* stage = reinterpret_cast<uint4*>(sm_raw);                       // [2][Tn][CV]
+    float* cs = reinterpret_cast<float*>(sm_raw + (size_t)2 * Tn * CV * 16);   // [H]
+    const int cpr = H / VEC;
+    for (int i = threadIdx.x; i < H; i += blockDim.x) cs[i] = 0.0f;
+    const int64_t nchunks = (nvec + CV - 1) / CV;
+    auto issue = [&](int64_t k, int s) {
+        if (k < nchunks) {
+            const int64_t v0 = k * CV;
+            const int valid = (int)((nvec - v0) < CV ? (nvec - v0) : CV);
+            for (int e = threadIdx.x; e < Tn * CV; e += blockDim.x) {
+                const int t = e / CV, v = e - t * CV;
+                if (v < valid) {
+                    const uint32_t dst = smem_u32(stage + ((size_t)s * Tn + t) * CV + v);
+                    const T* g = src + (size_t)t * n + (v0 + v) * VEC;
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(g) : "memory");
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int64_t k = blockIdx.x;
+    issue(k, 0);
+    issue(k + gridDim.x, 1);
+    for (int it = 0; k < nchunks; k += gridDim.x, ++it) {
+        const int s = it & 1;
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncthreads();
+        const int64_t v0 = k * CV;
+        const int valid = (int)((nvec - v0) < CV ? (nvec - v0) : CV);
+        if ((int)threadIdx.x < valid) {
+            float acc[VEC];
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) acc[j] = 0.0f;
+            for (int t = 0; t < Tn; ++t) {
+                float f[VEC];
+                Vec16<T>::unpack(stage[((size_t)s * Tn + t) * CV + threadIdx.x], f);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) acc[j] += f[j];
+            }
+            const int64_t vi = v0 + threadIdx.x;
+            *reinterpret_cast<uint4*>(out + vi * VEC) = Vec16<T>::pack(acc);
+            float* c = cs + (int)(vi % cpr) * VEC;
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) c[j] += acc[j];
+        }
+        __syncthreads();
+        issue(k + 2 * (int64_t)gridDim.x, s);
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    for (int i = threadIdx.x; i < H; i += blockDim.x) part[(size_t)blockIdx.x * H + i] = cs[i];
+}
 __global__ void colsum_final_kernel(const float* __restrict__ part, int S, int N, float* __restrict__ out, int ilH);
 // out (rows x H, T) = sum_t src[t];  colsum_out[H] = column sums of that (fp32)
 template <typename T>
@@ -292,15 +356,25 @@ int sum_over_t_colsum(cudaStream_t s, T* out, const T* src, int64_t rows, int H,
     if (blocks * H > scratch_floats) blocks = scratch_floats / H;
     SAT_REQUIRE(blocks >= 1, "sum_over_t_colsum: scratch too small");
     if (share_sms) {
-        // an SM cannot change its L1 / shared-memory split while blocks are resident: ask for the all-shared split so that a
-        // GEMM CTA (~200 KB of shared memory) can land beside this kernel's block
-        static bool configured = false;
-        if (!configured) {
-            SAT_CHECK_CUDA(cudaFuncSetAttribute(sum_over_t_colsum_kernel<T, true>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                                cudaSharedmemCarveoutMaxShared));
-            configured = true;
+        // chunk length: two stages of Tn x CV vectors in ~25 KB, CV <= 256 threads and shorter than a row
+        int CV = (int)(12800 / ((int64_t)Tn * 16));
+        if (CV > cpr - 1) CV = cpr - 1;
+        if (CV > 256) CV = 256;
+        if (CV >= 4) {
+            CV &= ~3;
+            // an SM cannot change its L1 / shared-memory split while blocks are resident: ask for the all-shared split so that
+            // a GEMM CTA (~193 KB of shared memory) can land beside this kernel's block
+            static bool configured = false;
+            if (!configured) {
+                SAT_CHECK_CUDA(cudaFuncSetAttribute(sum_over_t_async_kernel<T>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                                    cudaSharedmemCarveoutMaxShared));
+                configured = true;
+            }
+            const size_t smem = (size_t)2 * Tn * CV * 16 + (size_t)H * 4;
+            sum_over_t_async_kernel<T><<<(int)blocks, 256, smem, s>>>(out, src, nvec, n, Tn, H, CV, scratch);
+        } else {
+            sum_over_t_colsum_kernel<T, true><<<(int)blocks, threads, (size_t)threads * VEC * 4, s>>>(out, src, nvec, n, Tn, H, scratch);
         }
-        sum_over_t_colsum_kernel<T, true><<<(int)blocks, threads, (size_t)threads * VEC * 4, s>>>(out, src, nvec, n, Tn, H, scratch);
     }
     else sum_over_t_colsum_kernel<T, false><<<(int)blocks, threads, (size_t)threads * VEC * 4, s>>>(out, src, nvec, n, Tn, H, scratch);
     colsum_final_kernel<<<sat_cdiv(H, 32), 256, 0, s>>>(scratch, (int)blocks, H, colsum_out, 0);

@@ -26,6 +26,8 @@ def main():
     CFG = bench.CFG
     dev = torch.device("cuda", 0)
     _lib.lib().sat_set_decoder_split(args.split)
+    if "SAT_TAIL" in os.environ:                       # 0 = one chain, 1 = two chains, 2 = two chains + register-thin sum over t
+        _lib.lib().sat_set_tail_overlap(int(os.environ["SAT_TAIL"]))
     dec = Decoder(CFG["V"], CFG["D"], tf=True, attention=True, compute_dtype=torch.bfloat16)
     dec.load_state_dict(synth.make_params(CFG["V"], CFG["D"], CFG["H"], seed=42))
     dec = dec.to(dev).train()
