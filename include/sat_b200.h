@@ -163,6 +163,11 @@ int sat_decoder_workspace_bytes(const sat_decoder_args* args, int64_t* bytes);
 /* The (B, T, ld) fp32 logits the last sat_decoder_forward call with these args produced: args->preds, or the padded copy in
  * the workspace when the loss was fused (preds == NULL). */
 int sat_decoder_logits(const sat_decoder_args* args, const float** logits, int64_t* ld);
+/* Data-parallel overlap (no upstream equivalent; the reference is single-device): `stream` waits until the last
+ * sat_decoder_backward of this host thread on the current device has written the gradients of init_h / init_c (weight, bias) and
+ * lstm.weight_ih / weight_hh, which are final ~160 us before the call's last kernel; a caller can all-reduce that bucket under the
+ * rest of the backward pass.  No-op before the first backward. */
+int sat_wait_early_grads(void* stream);
 int sat_decoder_forward(const sat_decoder_args* args);
 int sat_decoder_backward(const sat_decoder_args* args, const sat_decoder_grads* grads);
 

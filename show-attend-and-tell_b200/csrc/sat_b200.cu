@@ -116,6 +116,17 @@ int sat_profile_read(float* ms, int* counts) {
     return SAT_OK;
 }
 
+/* Data-parallel overlap: make `stream` wait until the last sat_decoder_backward of this host thread and device has written the
+ * gradients of init_h / init_c (weights and biases) and lstm.weight_ih / weight_hh -- they are final well before the call's
+ * remaining work (embedding, attention, output-layer gradients) is done.  No-op before the first backward. */
+int sat_wait_early_grads(void* stream) {
+    SAT_TRY(require_sm100());
+    SideStream* ss = nullptr;
+    SAT_TRY(side_stream(&ss));
+    SAT_CHECK_CUDA(cudaStreamWaitEvent(reinterpret_cast<cudaStream_t>(stream), ss->early, 0));
+    return SAT_OK;
+}
+
 /* utils.py:44-80 (sequence_accuracy) in one pass: rank[r] = #{v : logits[r, v] > logits[r, targets[r]]} for `rows` rows of V
  * logits with row pitch ld.  The target is among the top k exactly when rank < k (a tie counts for the target). */
 int sat_logit_rank(const float* logits, int64_t ld, int64_t rows, int V, const int64_t* targets, int32_t* rank, void* stream) {

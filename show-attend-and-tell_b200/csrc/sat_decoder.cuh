@@ -46,7 +46,7 @@ static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 // created once per host thread and device; the caller's stream forks into it before the loop and joins after it.
 // ---------------------------------------------------------------------------------------------------
 extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap;
-struct SideStream { cudaStream_t s; cudaEvent_t fork, join, attn_done[2]; bool ok; };
+struct SideStream { cudaStream_t s; cudaEvent_t fork, join, attn_done[2], early; bool ok; };
 static inline int side_stream(SideStream** out) {
     static thread_local SideStream cache[32] = {};
     int dev = 0;
@@ -59,6 +59,7 @@ static inline int side_stream(SideStream** out) {
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.attn_done[0], cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.attn_done[1], cudaEventDisableTiming));
+        SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.early, cudaEventDisableTiming));
         ss.ok = true;
     }
     *out = &ss;
@@ -656,6 +657,9 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         auto e2 = lin<T>(4 * H, H, nullptr, SAT_ACT_NONE, w.gscratch, H, nullptr, 0);
         SAT_TRY(gemm<T>(sb, w.dG, 4 * H, false, w.E, H, false, 4 * H, H, BT, e2));
         if (g.lstm_w_ih) SAT_TRY(misc::unpack_grad(sb, g.lstm_w_ih, H + D, w.gscratch, H, 4 * H, H, 0, H));
+        // The initial-state and LSTM weight gradients (62 % of the gradient bytes at c2) are final here, ~160 us before the
+        // tail ends: data-parallel callers start their all-reduce on this event (sat_wait_early_grads) under the rest of it.
+        SAT_CHECK_CUDA(cudaEventRecord(tl->early, sb));
         // d b_ih = d b_hh = column sums of dG: computed once, copied
         float* gb = g.lstm_b_ih ? g.lstm_b_ih : g.lstm_b_hh;
         if (gb) SAT_TRY(misc::colsum<T>(sb, w.dG, 4 * H, BT, 4 * H, gb, csb, w.csum_floats, H));

@@ -19,6 +19,9 @@ from . import _lib
 
 
 class FusedTrainStep:
+    # gradients that are final ~160 us before sat_decoder_backward's last kernel (sat_wait_early_grads): 62 % of the bytes at c2
+    EARLY_KEYS = ("init_h.weight", "init_h.bias", "init_c.weight", "init_c.bias", "lstm.weight_ih", "lstm.weight_hh")
+
     def __init__(self, decoder, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, alpha_c=1.0, process_group=None,
                  distributed=None):
         self.dec = decoder
@@ -27,7 +30,10 @@ class FusedTrainStep:
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if self.distributed else 1
         unused = decoder.unused_parameter_keys()
-        self.train_keys = [n for n, p in decoder.named_parameters() if p.requires_grad and n not in unused]
+        keys = [n for n, p in decoder.named_parameters() if p.requires_grad and n not in unused]
+        # the gradients sat_decoder_backward finishes early go first in the flat buffer: one contiguous all-reduce bucket
+        early = [k for k in keys if k in self.EARLY_KEYS]
+        self.train_keys = early + [k for k in keys if k not in self.EARLY_KEYS]
         named = dict(decoder.named_parameters())
         dev = next(decoder.parameters()).device
         offsets, off = {}, 0
@@ -35,6 +41,9 @@ class FusedTrainStep:
             offsets[k] = off
             off = (off + named[k].numel() + 3) & ~3          # keep every tensor 16-byte aligned
         n = off
+        self.n_early = max([offsets[k] + ((named[k].numel() + 3) & ~3) for k in early], default=0)
+        self.overlap_allreduce = True
+        self._comm_stream = None
         # flat buffers; each parameter becomes a view into `flat_param` (state_dict keys/shapes unchanged)
         self.flat_param = torch.zeros(n, device=dev, dtype=torch.float32)
         self.flat_grad = torch.zeros(n, device=dev, dtype=torch.float32)
@@ -129,8 +138,22 @@ class FusedTrainStep:
     def sync_grads(self):
         """The one exchange step of data-parallel training: sum the flat gradient buffer over the ranks (NCCL over
         NVLink on GPUs).  The 1/world of the mean is folded into the Adam kernel (grad_scale)."""
-        if self.world > 1:
+        if self.world <= 1:
+            return
+        if not (self.overlap_allreduce and self.flat_grad.is_cuda and 0 < self.n_early < self.n):
             dist.all_reduce(self.flat_grad, group=self.pg)
+            return
+        # two buckets: the early one is reduced on a side stream as soon as the backward pass has written it (under the rest
+        # of the backward tail), the rest on the current stream after the pass; Adam then waits for both
+        dev = self.flat_grad.device
+        if self._comm_stream is None:
+            self._comm_stream = torch.cuda.Stream(dev)
+        cs = self._comm_stream
+        _lib.check(_lib.lib().sat_wait_early_grads(cs.cuda_stream), "sat_wait_early_grads")
+        with torch.cuda.stream(cs):
+            early = dist.all_reduce(self.flat_grad[:self.n_early], group=self.pg, async_op=True)
+        dist.all_reduce(self.flat_grad[self.n_early:], group=self.pg)
+        early.wait()                                   # the current stream waits for the early bucket
 
     def layout_signature(self):
         """(key, offset, numel) of every trainable tensor in the flat buffers; must be identical on all ranks."""
