@@ -20,6 +20,9 @@ extern "C" {
 #define SAT_DTYPE_F32 0   /* storage + arithmetic fp32 (true-fp32 FMA GEMMs): bit-exact beam tokens, config c1/c4 */
 #define SAT_DTYPE_BF16 1  /* bf16 storage / tensor-core operands, fp32 accumulate, fp32 softmax/alphas/cell state */
 
+/* device-side status bits of a sequence-driver call (sat_decoder_args.loss[3]) */
+#define SAT_STATUS_BAD_TOKEN 1   /* a caption id outside [0, V): nn.Embedding / CrossEntropyLoss raise IndexError upstream */
+
 const char* sat_last_error(void);
 int sat_version(void);
 /* debug knob: 1 = run bf16 GEMMs on the SIMT kernel (bring-up cross-check of the tcgen05 kernel) */
@@ -68,9 +71,10 @@ int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes);
 int sat_profile(int on);
 int sat_profile_read(float* ms, int* counts);
 
-/* train.py:144-145 / utils.py:44-80 `sequence_accuracy(preds, targets, k)`: rank[r] = number of logits of row r strictly above
- * the logit of targets[r] (rows x V fp32 logits, row pitch ld; a target outside [0, V) gets rank V).  The target is in the top k
- * iff rank < k, so top-1 and top-5 come out of ONE pass over the logits (the reference runs topk twice). */
+/* train.py:144-145 / utils.py:44-80 `sequence_accuracy(preds, targets, k)`: rank[r] = position of targets[r]'s logit in row r's
+ * descending order, ties broken towards the lower index (rows x V fp32 logits, row pitch ld; a target outside [0, V) or a NaN
+ * target logit gets rank V).  The target is in the top k iff rank < k, so top-1 and top-5 come out of ONE pass over the logits
+ * (the reference runs topk twice), and a tied block admits at most k entries like topk does. */
 int sat_logit_rank(const float* logits, int64_t ld, int64_t rows, int V, const int64_t* targets, int32_t* rank, void* stream);
 
 /* Generic GEMM  C[M,N] = act(A[M,K] * B[N,K]^T + bias[N])  (nn.Linear: attention.py:15-16, decoder.py:99,125,139-145).
@@ -88,9 +92,10 @@ int sat_attn_step_fwd(int dtype, int NI, int NB, int L, int D, int H, const void
                       int64_t scratch_bytes, void* stream);
 
 /* Scratch of the streaming attention kernels (persistent CTAs over an equal split of all locations; an image cut by
- * the split is finished by the last of its CTAs).  0 bytes = this shape runs on the generic cluster kernels, which
- * need none.  The caller zeroes the buffer once; the kernels leave it zeroed.  Without scratch (NULL) the generic
- * kernels run.  ctx_f32 (optional, streaming only) receives the fp32 un-gated context the streaming backward needs. */
+ * the split leaves one partial record per piece in this buffer and a small combine kernel finishes it).  0 bytes = this
+ * shape runs on the generic cluster kernels, which need none.  The buffer needs NO initialisation (every record is written
+ * before it is read; tests/test_gpu_attention.py fills it with 0xFF).  Without scratch (NULL) the generic kernels run.
+ * ctx_f32 (optional, streaming only) receives the fp32 un-gated context the streaming backward needs. */
 int sat_attn_scratch_bytes(int NI, int NB, int L, int D, int H, int64_t* bytes);
 
 /* K2 backward (autograd of the lines above inside loss.backward(), train.py:163).
@@ -117,7 +122,8 @@ typedef struct sat_decoder_args {
     int32_t fused_loss;         /* 1: also compute the train.py:150-162 loss (+ its gradient seed) on device */
     int32_t a_dtype;            /* dtype of img_features (SAT_DTYPE_*) */
     float alpha_c;              /* train.py:154 */
-    float reserved0;
+    int32_t need_dfeat;         /* 1: sat_decoder_backward will be asked for the gradient wrt img_features (train.py:132 runs the
+                                 * encoder outside no_grad, so loss.backward() reaches it); sizes the workspace, set it in both calls */
     const void* img_features;   /* (B,L,D), arbitrary strides in elements (Q20) */
     int64_t a_stride_b, a_stride_l, a_stride_d;
     const int64_t* captions;    /* (B, T+1) int64, row stride cap_stride */
@@ -135,7 +141,7 @@ typedef struct sat_decoder_args {
     /* outputs */
     float* preds;               /* (B,T,V) fp32 (decoder.py:92); may be NULL only with fused_loss */
     float* alphas;              /* (B,T,L) fp32 (decoder.py:93) */
-    float* loss;                /* [3] fp32: CE mean, alpha regulariser, total (fused_loss) */
+    float* loss;                /* [4] fp32: CE mean, alpha regulariser, total, status (SAT_FLAG_* bits as a float; 0 = clean) (fused_loss) */
     /* workspace (PyTorch-owned) */
     void* workspace;
     int64_t workspace_bytes;
@@ -156,7 +162,7 @@ typedef struct sat_decoder_grads {
     float* lstm_w_ih; float* lstm_w_hh; float* lstm_b_ih; float* lstm_b_hh;
     float* deep_w; float* deep_b;
     float* f_h_w; float* f_h_b; float* f_z_w; float* f_z_b; float* f_out_w; float* f_out_b;
-    float* img_features;        /* (B,L,D) fp32 contiguous grad or NULL */
+    float* img_features;        /* (B,L,D) fp32 contiguous gradient wrt img_features, or NULL (needs args->need_dfeat) */
 } sat_decoder_grads;
 
 int sat_decoder_workspace_bytes(const sat_decoder_args* args, int64_t* bytes);
@@ -210,6 +216,26 @@ int sat_beam_search(const sat_beam_args* args);
 /* N1 (next row): fused multi-tensor Adam over flat fp32 buffers (train.py:71,164). */
 int sat_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, float lr, float beta1,
                   float beta2, float eps, float weight_decay, int step, float grad_scale, void* stream);
+
+/* The same update with every step-dependent scalar in DEVICE memory (CUDA-graph friendly): hyper = [lr, beta1, beta2, eps,
+ * weight_decay, grad_scale] fp32; *step_count = updates done so far, incremented by the call.  StepLR (train.py:72,100) is a
+ * host-side write of hyper[0] between steps. */
+int sat_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, const float* hyper,
+                      int32_t* step_count, void* stream);
+
+/* N1: utils.py:101-107 `calculate_caption_lengths(captions, skip_tokens)` (train.py:174-177) without the .item(): out[0] (device
+ * int64) = number of ids in the (rows, cols) grid, row pitch `stride`, equal to none of skip0..2 (-1 = unused). */
+int sat_count_tokens(const int64_t* tokens, int64_t rows, int64_t cols, int64_t stride, int64_t skip0, int64_t skip1, int64_t skip2,
+                     int64_t* out, void* stream);
+
+/* N4: greedy decode of the evaluation path, train.py:272,297 `torch.max(preds, dim=2)[1]`: first maximum per row. */
+int sat_argmax_rows(const float* logits, int64_t ld, int64_t rows, int V, int64_t* out, void* stream);
+
+/* N2: HBM-resident feature cache (VGG19 is frozen, encoder.py:29-31, so train.py:132 recomputes constants every epoch):
+ * out[i] = store[idx[i]] for items of item_bytes bytes (multiple of 16).  err_flag: optional device int set to 1 on an index
+ * outside [0, n_items) (that item is zero-filled). */
+int sat_gather_items(const void* store, int64_t item_bytes, int64_t n_items, const int64_t* idx, int64_t n_idx, void* out,
+                     int32_t* err_flag, void* stream);
 
 #ifdef __cplusplus
 }

@@ -79,7 +79,7 @@ def _step(P: Params, a, h, c, emb, *, attention: bool, gate: bool = True):
         else:                       # build extension: gating scalar disabled
             gated = context
     else:
-        alpha = torch.full((B, L), 1.0 / L, dtype=a.dtype)                  # decoder.py:103
+        alpha = torch.full((B, L), 1.0 / L, dtype=a.dtype, device=a.device)                # decoder.py:103
         context = a.mean(dim=1)                                             # decoder.py:104
         gated = context                                                     # decoder.py:105
     x = torch.cat((emb, gated), dim=1)                                      # decoder.py:109/112
@@ -89,10 +89,13 @@ def _step(P: Params, a, h, c, emb, *, attention: bool, gate: bool = True):
 
 def decoder_forward(P: Params, a: torch.Tensor, captions: torch.Tensor, *, tf: bool, ado: bool,
                     attention: bool, gate: bool = True, start_token: int = 0,
-                    dropout_masks: Optional[torch.Tensor] = None):
+                    dropout_masks: Optional[torch.Tensor] = None, feed_tokens: Optional[torch.Tensor] = None):
     """decoder.py:69-135.  `dropout_masks` (B,T,H) holds the *scaled* keep mask
     (0 or 1/(1-p)) applied to h before the output layer (decoder.py:121-125);
-    None means eval mode (identity)."""
+    None means eval mode (identity).  Tensors are created on `a.device`, so the same restatement runs on the GPU
+    for the full-size parity tests.  `feed_tokens` (B,T), free-running mode only: feed these ids as step inputs
+    instead of this function's own argmax (decoder.py:132) -- the teacher-style check of SURVEY 7.2: a bf16 run's
+    near-tie argmax may legitimately differ from the fp32 one, after which the two trajectories are incomparable."""
     B = a.shape[0]
     h, c = init_lstm_state(P, a)                                            # decoder.py:74
     T = captions.shape[1] - 1                                               # decoder.py:77
@@ -100,10 +103,10 @@ def decoder_forward(P: Params, a: torch.Tensor, captions: torch.Tensor, *, tf: b
     if tf:
         cap_emb = E[captions]                                               # decoder.py:87
     else:
-        prev = E[torch.full((B,), start_token, dtype=torch.long)]           # decoder.py:79-82,89
+        prev = E[torch.full((B,), start_token, dtype=torch.long, device=a.device)]   # decoder.py:79-82,89
     V = P["deep_output.weight"].shape[0]
-    preds = torch.zeros(B, T, V, dtype=a.dtype)                             # decoder.py:92
-    alphas = torch.zeros(B, T, a.shape[1], dtype=a.dtype)                   # decoder.py:93
+    preds = torch.zeros(B, T, V, dtype=a.dtype, device=a.device)            # decoder.py:92
+    alphas = torch.zeros(B, T, a.shape[1], dtype=a.dtype, device=a.device)  # decoder.py:93
     for t in range(T):                                                      # decoder.py:96
         emb = cap_emb[:, t] if tf else prev
         h, c, context, alpha = _step(P, a, h, c, emb, attention=attention, gate=gate)
@@ -115,7 +118,7 @@ def decoder_forward(P: Params, a: torch.Tensor, captions: torch.Tensor, *, tf: b
         preds[:, t] = out                                                   # decoder.py:127
         alphas[:, t] = alpha                                                # decoder.py:128
         if not tf:
-            prev = E[out.max(1)[1]]                                         # decoder.py:132-133
+            prev = E[out.max(1)[1] if feed_tokens is None or t + 1 >= T else feed_tokens[:, t + 1]]   # decoder.py:132-133
     return preds, alphas
 
 
@@ -147,10 +150,10 @@ def caption(P: Params, a1: torch.Tensor, beam_size: int, *, ado: bool, attention
     a = a1.unsqueeze(0).expand(beam_size, L, a1.shape[1])                   # generate_caption.py:89
     E = P["embedding.weight"]
     V = (P["f_out.weight"] if ado else P["deep_output.weight"]).shape[0]
-    prev_words = torch.full((beam_size,), start_token, dtype=torch.long)    # decoder.py:166-169
+    prev_words = torch.full((beam_size,), start_token, dtype=torch.long, device=a1.device)    # decoder.py:166-169
     sentences = prev_words.unsqueeze(1)
-    top_preds = torch.zeros(beam_size, 1, dtype=a1.dtype)
-    alphas = torch.ones(beam_size, 1, L, dtype=a1.dtype)
+    top_preds = torch.zeros(beam_size, 1, dtype=a1.dtype, device=a1.device)
+    alphas = torch.ones(beam_size, 1, L, dtype=a1.dtype, device=a1.device)
     done_s: List[List[int]] = []
     done_a: List[List[List[float]]] = []
     done_p: List[float] = []

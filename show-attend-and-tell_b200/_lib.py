@@ -42,7 +42,7 @@ class DecoderArgs(C.Structure):
         [("struct_bytes", _i32), ("dtype", _i32)]
         + [(n, _i32) for n in ("B", "L", "D", "H", "V", "T", "tf", "ado", "attention", "gate", "start_token",
                                "need_grad", "fused_loss", "a_dtype")]
-        + [("alpha_c", _f32), ("reserved0", _f32)]
+        + [("alpha_c", _f32), ("need_dfeat", _i32)]
         + [("img_features", _vp), ("a_stride_b", _i64), ("a_stride_l", _i64), ("a_stride_d", _i64),
            ("captions", _vp), ("cap_stride", _i64), ("dropout_mask", _vp)]
         + [(n, _vp) for n in PARAM_FIELDS]
@@ -74,7 +74,8 @@ _LIB = None
 
 EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_set_attn_generic", "sat_set_attn_partition", "sat_set_pdl", "sat_set_gemm_static_weights", "sat_set_tail_overlap", "sat_set_fused_cell_backward", "sat_gemm_phase_stamps", "sat_set_decoder_split", "sat_set_decoder_split_sms", "sat_set_gemm_splitk", "sat_set_attn_l2_policy", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_bwd", "sat_attn_scratch_bytes",
            "sat_decoder_workspace_bytes", "sat_decoder_logits", "sat_wait_early_grads", "sat_logit_rank", "sat_decoder_forward", "sat_decoder_backward", "sat_beam_workspace_bytes",
-           "sat_beam_search", "sat_adam_step", "sat_profile", "sat_profile_read"]
+           "sat_beam_search", "sat_adam_step", "sat_adam_step_dev", "sat_count_tokens", "sat_argmax_rows", "sat_gather_items",
+           "sat_profile", "sat_profile_read"]
 
 
 def lib():
@@ -104,6 +105,10 @@ def lib():
         L.sat_beam_workspace_bytes.argtypes = [C.POINTER(BeamArgs), C.POINTER(_i64)]
         L.sat_beam_search.argtypes = [C.POINTER(BeamArgs)]
         L.sat_adam_step.argtypes = [_vp, _vp, _vp, _vp, _i64, _f32, _f32, _f32, _f32, _f32, C.c_int, _f32, _vp]
+        L.sat_adam_step_dev.argtypes = [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _vp]
+        L.sat_count_tokens.argtypes = [_vp, _i64, _i64, _i64, _i64, _i64, _i64, _vp, _vp]
+        L.sat_argmax_rows.argtypes = [_vp, _i64, _i64, C.c_int, _vp, _vp]
+        L.sat_gather_items.argtypes = [_vp, _i64, _i64, _vp, _i64, _vp, _vp, _vp]
         _LIB = L
     return _LIB
 

@@ -620,8 +620,12 @@ template <typename T, int NBG, bool PRECISE>
 int launch_fwd_t(FwdParams p, cudaStream_t stream) {
     constexpr int VEC = Vec16<T>::N;
     auto kern = fwd_kernel<T, NBG, PRECISE>;
-    static int maxc = 0;
-    if (!maxc) SAT_TRY(kernel_setup(kern, &maxc));
+    static int maxc_dev[64];          // per device (kernel attributes belong to a device context)
+    static SatPerDevice configured;
+    int dev = 0;
+    SAT_CHECK_CUDA(cudaGetDevice(&dev));
+    SAT_TRY(configured.once([&]() -> int { return kernel_setup(kern, &maxc_dev[dev & 63]); }));
+    const int maxc = maxc_dev[dev & 63];
     pick_cluster(p.L, (size_t)(p.D + p.H) * sizeof(T), STAGE_TARGET, maxc, &p.C, &p.Lc);
     const int nchunks = p.D / VEC;
     p.G = 1;
@@ -650,8 +654,12 @@ int launch_bwd(BwdParams p, cudaStream_t stream) {
     SAT_REQUIRE(p.D % VEC == 0 && p.H % VEC == 0, "attention: D and H must be multiples of %d", VEC);
     SAT_REQUIRE(p.H / VEC <= THREADS, "attention bwd: H=%d too wide for this build", p.H);
     auto kern = bwd_kernel<T, PRECISE>;
-    static int maxc = 0;
-    if (!maxc) SAT_TRY(kernel_setup(kern, &maxc));
+    static int maxc_dev[64];          // per device (kernel attributes belong to a device context)
+    static SatPerDevice configured;
+    int dev = 0;
+    SAT_CHECK_CUDA(cudaGetDevice(&dev));
+    SAT_TRY(configured.once([&]() -> int { return kernel_setup(kern, &maxc_dev[dev & 63]); }));
+    const int maxc = maxc_dev[dev & 63];
     pick_cluster(p.L, (size_t)(p.D + p.H) * sizeof(T), STAGE_TARGET, maxc, &p.C, &p.Lc);
     p.Ds = (p.D + p.C - 1) / p.C;
     p.Hs = (p.H + p.C - 1) / p.C;

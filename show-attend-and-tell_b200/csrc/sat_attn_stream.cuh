@@ -925,11 +925,11 @@ template <typename T, int D, int H, int NBG, bool PRECISE>
 int launch_fwd_inst(const FwdParams& p, cudaStream_t stream) {
     using G = Geo<T, D, H>;
     auto kern = fwd_stream_kernel<T, D, H, NBG, PRECISE>;
-    static bool configured = false;
-    if (!configured) {
+    static SatPerDevice configured;
+    SAT_TRY(configured.once([&]() -> int {
         SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX));
-        configured = true;
-    }
+        return SAT_OK;
+    }));
     const Smem sl = fwd_smem<T, D, H, NBG>(p.L);
     SAT_REQUIRE(sl.nslots >= CWARPS && sl.total <= SMEM_MAX, "attention fwd (streaming): shared memory budget exceeded (L=%d)", p.L);
     const int ngroups = (p.NB + NBG - 1) / NBG, spi = (p.L + G::LS - 1) / G::LS;
@@ -984,11 +984,11 @@ int launch_bwd_inst(const BwdParams& p_in, cudaStream_t stream) {
         p.dz = p.s_dctx; p.ld_dz = D; p.dz_is_dctx = 1;
     }
     auto kern = bwd_stream_kernel<T, D, H, PRECISE>;
-    static bool configured = false;
-    if (!configured) {
+    static SatPerDevice configured;
+    SAT_TRY(configured.once([&]() -> int {
         SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_MAX));
-        configured = true;
-    }
+        return SAT_OK;
+    }));
     const Smem sl = bwd_smem<T, D, H>(p.L);
     SAT_REQUIRE(sl.nslots >= CWARPS && sl.total <= SMEM_MAX, "attention bwd (streaming): shared memory budget exceeded (L=%d)", p.L);
     const int spi = (p.L + G::LS - 1) / G::LS;

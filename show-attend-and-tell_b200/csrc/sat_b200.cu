@@ -50,25 +50,31 @@ SatProfScope::~SatProfScope() {
 }
 
 static int require_sm100() {
-    static int ok = -1;
-    if (ok < 0) {
-        int dev = 0;
-        cudaDeviceProp prop;
-        if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&prop, dev) != cudaSuccess) {
+    static signed char ok[64];          // per device: 0 = unknown, 1 = sm_100, -1 = something else
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) {
+        sat_set_error("no CUDA device: sat_b200 has no CPU fallback");
+        return SAT_ERR_CUDA;
+    }
+    signed char& st = ok[dev & 63];
+    if (st == 0) {
+        int major = 0, minor = 0;
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&minor, cudaDevAttrComputeCapabilityMinor, dev) != cudaSuccess) {
             sat_set_error("no CUDA device: sat_b200 has no CPU fallback");
             return SAT_ERR_CUDA;
         }
-        ok = (prop.major == 10) ? 1 : 0;
-        if (!ok) sat_set_error("sat_b200 kernels are built for sm_100a only; found sm_%d%d", prop.major, prop.minor);
+        st = (major == 10) ? 1 : -1;
+        if (st < 0) sat_set_error("sat_b200 kernels are built for sm_100a only; found sm_%d%d", major, minor);
     }
-    if (!ok) { sat_set_error("sat_b200 kernels are built for sm_100a only"); return SAT_ERR_UNSUPPORTED; }
+    if (st < 0) { sat_set_error("sat_b200 kernels are built for sm_100a only"); return SAT_ERR_UNSUPPORTED; }
     return SAT_OK;
 }
 
 extern "C" {
 
 const char* sat_last_error(void) { return g_err; }
-int sat_version(void) { return 100; }
+int sat_version(void) { return 200; }
 int sat_set_force_simt(int on) { g_force_simt = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_generic(int on) { g_attn_generic = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes) {
@@ -282,6 +288,81 @@ int sat_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
     const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
     adam_kernel<<<misc::grid_for(n), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1,
                                                                                       beta2, eps, weight_decay, bc1, bc2, grad_scale);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+/* Same update with the step-dependent scalars read from DEVICE memory, so that a whole train step can live in a CUDA graph:
+ * hyper = [lr, beta1, beta2, eps, weight_decay, grad_scale]; *step_count is the number of updates done so far (the kernel uses
+ * step_count + 1 for the bias corrections, a one-thread kernel increments it afterwards).  StepLR (train.py:72,100) then is a
+ * host-side write of hyper[0] between steps. */
+__global__ void adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                                int64_t n, const float* __restrict__ hyper, const int32_t* __restrict__ step_count) {
+    const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], gs = hyper[5];
+    const float step = (float)(step_count[0] + 1);
+    const float bc1 = 1.0f - powf(b1, step), bc2 = 1.0f - powf(b2, step);
+    const float inv_sbc2 = 1.0f / sqrtf(bc2), slr = lr / bc1;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        float gr = g[i] * gs;
+        const float pv = p[i];
+        if (wd != 0.0f) gr += wd * pv;
+        const float mi = b1 * m[i] + (1.0f - b1) * gr;
+        const float vi = b2 * v[i] + (1.0f - b2) * gr * gr;
+        m[i] = mi; v[i] = vi;
+        p[i] = pv - slr * (mi / (sqrtf(vi) * inv_sbc2 + eps));
+    }
+}
+__global__ void adam_tick_kernel(int32_t* step_count) { step_count[0] += 1; }
+
+int sat_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, const float* hyper,
+                      int32_t* step_count, void* stream) {
+    SAT_TRY(require_sm100());
+    SAT_REQUIRE(hyper && step_count, "sat_adam_step_dev: null hyper / step_count");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (n > 0) adam_dev_kernel<<<misc::grid_for(n), 256, 0, st>>>(param, grad, exp_avg, exp_avg_sq, n, hyper, step_count);
+    adam_tick_kernel<<<1, 1, 0, st>>>(step_count);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+/* utils.py:101-107 / train.py:174-177: tokens of the (rows, cols) int64 grid (row pitch `stride`) that are none of the three
+ * skip ids (pass -1 for an unused one); the int64 count is written to out[0] on the device. */
+int sat_count_tokens(const int64_t* tokens, int64_t rows, int64_t cols, int64_t stride, int64_t skip0, int64_t skip1, int64_t skip2,
+                     int64_t* out, void* stream) {
+    SAT_TRY(require_sm100());
+    SAT_REQUIRE(tokens && out && rows >= 0 && cols >= 0, "sat_count_tokens: bad arguments");
+    misc::count_tokens_kernel<<<1, 1024, 0, reinterpret_cast<cudaStream_t>(stream)>>>(tokens, rows, cols, stride, skip0, skip1, skip2, out);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+/* train.py:272,297 `torch.max(preds, dim=2)[1]`: first maximum of every row of (rows, V) fp32 logits with row pitch ld. */
+int sat_argmax_rows(const float* logits, int64_t ld, int64_t rows, int V, int64_t* out, void* stream) {
+    SAT_TRY(require_sm100());
+    SAT_REQUIRE(logits && out && V > 0 && ld >= V && rows >= 0 && rows < ((int64_t)1 << 31), "sat_argmax_rows: bad arguments");
+    if (rows == 0) return SAT_OK;
+    misc::argmax_rows_kernel<<<(unsigned)rows, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(logits, ld, V, out, 1);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
+/* N2 feature cache: out[i] = store[idx[i]] for items of item_bytes bytes (a multiple of 16; both buffers 16-byte aligned).
+ * err_flag (device int, optional) receives 1 if an index is outside [0, n_items); that item is zero-filled. */
+int sat_gather_items(const void* store, int64_t item_bytes, int64_t n_items, const int64_t* idx, int64_t n_idx, void* out,
+                     int32_t* err_flag, void* stream) {
+    SAT_TRY(require_sm100());
+    SAT_REQUIRE(store && idx && out && item_bytes > 0 && item_bytes % 16 == 0 && n_items > 0 && n_idx >= 0, "sat_gather_items: bad arguments");
+    SAT_REQUIRE(al16(store) && al16(out), "sat_gather_items: buffers must be 16-byte aligned");
+    if (n_idx == 0) return SAT_OK;
+    SAT_REQUIRE(n_idx < 65536, "sat_gather_items: at most 65535 indices per call");
+    const int64_t rv = item_bytes / 16;
+    int bx = (int)(sat_cdiv64(rv, 256 * 4));          // ~4 vectors per thread
+    const int64_t cap = sat_cdiv64((int64_t)148 * 16, n_idx);
+    if (bx > cap) bx = (int)cap;
+    if (bx < 1) bx = 1;
+    dim3 grid(bx, (unsigned)n_idx);
+    misc::gather_items_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const uint4*>(store), rv, n_items, idx, reinterpret_cast<uint4*>(out), err_flag);
     SAT_CHECK_CUDA(cudaGetLastError());
     return SAT_OK;
 }

@@ -354,11 +354,11 @@ int beam_search_t(const sat_beam_args& a) {
     size_t topk_smem = (size_t)NB * V * 4;
     if (topk_smem > 200 * 1024) topk_smem = 0;
     {
-        static size_t configured = 0;
-        if (topk_smem > configured) {
+        static SatPerDevice configured;
+        SAT_TRY(configured.once([&]() -> int {
             SAT_CHECK_CUDA(cudaFuncSetAttribute(beam::topk_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            configured = 200 * 1024;
-        }
+            return SAT_OK;
+        }));
     }
     for (int step = 1; step <= S; ++step) {
         SAT_TRY(misc::gather_rows<T>(st, w.X, xw, a.embedding, H, w.prev_word, 1, R, V));                  // decoder.py:183

@@ -17,6 +17,8 @@ void sat_set_error(const char* fmt, ...);
 #define SAT_ERR_ARG -1
 #define SAT_ERR_CUDA -2
 #define SAT_ERR_UNSUPPORTED -3
+// device-side status bits of a sequence-driver call (sat_decoder_args.loss[3], sat_decoder_status)
+#define SAT_FLAG_BAD_TOKEN 1     /* a caption id outside [0, V): the reference raises IndexError (nn.Embedding / CrossEntropyLoss) */
 
 #define SAT_CHECK_CUDA(expr)                                                                  \
     do {                                                                                      \
@@ -40,6 +42,25 @@ void sat_set_error(const char* fmt, ...);
         int _r = (expr);                                                                      \
         if (_r != SAT_OK) return _r;                                                          \
     } while (0)
+
+// Kernel attributes (cudaFuncSetAttribute) belong to a device context, not to the process: a function-local `static bool`
+// would configure only the first device a process touches.  One of these per call site; `first()` is true exactly once per
+// device (thread-safe: the caller configures while holding the lock).
+#include <mutex>
+struct SatPerDevice {
+    std::mutex mu;
+    unsigned long long done = 0;
+    template <typename F> int once(F&& fn) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+        const unsigned long long bit = 1ull << (dev & 63);
+        std::lock_guard<std::mutex> lk(mu);
+        if (done & bit) return SAT_OK;
+        const int r = fn();
+        if (r == SAT_OK) done |= bit;
+        return r;
+    }
+};
 
 static inline int sat_cdiv(int a, int b) { return (a + b - 1) / b; }
 static inline int64_t sat_cdiv64(int64_t a, int64_t b) { return (a + b - 1) / b; }

@@ -99,6 +99,7 @@ struct DecWs {
     float* hc0;      // (B,2H)      [h0 | c0]
     T *P1, *P2, *Comb;   // ado (T,B,H)
     int64_t* tok_in; // (T,B) token fed to each step (free-running mode)
+    int* flags;      // [4] device-side status bits of the call (SAT_FLAG_*)
     float* rowloss;  // (B*T)
     float* loss_part; // (2 * LOSS_PARTS) partial sums of the loss reduction
     float* logits_tmp;   // (B,T,Vp) when preds == NULL: row pitch padded to 8 so the GEMM epilogue stores 16-byte vectors
@@ -107,7 +108,8 @@ struct DecWs {
     T* dlog;         // (T,B,Vp)
     float* dHd;      // (T,B,H)
     T* dG;           // (T,B,4H)
-    float* dZH;      // (B,D+H)
+    float* dZH;      // (B,D+H), or (T,B,D+H) when the gradient wrt img_features is wanted (every step's dctx is kept)
+    float* dabar;    // (B,D)  gradient wrt the mean feature (need_dfeat)
     T* dUF;          // (T,B,H+D)
     float *dh_carry, *dc_carry;
     float* dwa_acc;  // (B,L,H)      generic attention backward: fp32 accumulator over time
@@ -163,11 +165,12 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
     TK(ZH, B * (Tn + 1) * (D + H), T); TK(Cst, B * (Tn + 1) * H, float);
     TK(Gates, B * Tn * 4 * H, T); TK(Ctx, B * Tn * D, T); TK(Hdrop, B * Tn * H, T); TK(hc0, B * 2 * H, float);
     TK(P1, a.ado ? B * Tn * H : 0, T); TK(P2, a.ado ? B * Tn * H : 0, T); TK(Comb, a.ado ? B * Tn * H : 0, T);
-    TK(tok_in, B * Tn, int64_t); TK(rowloss, B * Tn, float); TK(loss_part, 2 * misc::LOSS_PARTS, float);
+    TK(tok_in, B * Tn, int64_t); TK(flags, 4, int); TK(rowloss, B * Tn, float); TK(loss_part, 2 * misc::LOSS_PARTS, float);
     TK(logits_tmp, a.preds ? 0 : B * Tn * w.Vp, float);
     w.ldl = a.preds ? (int64_t)V : w.Vp;
     if (a.need_grad) {
-        TK(dlog, B * Tn * w.Vp, T); TK(dHd, B * Tn * H, float); TK(dG, B * Tn * 4 * H, T); TK(dZH, B * (D + H), float);
+        TK(dlog, B * Tn * w.Vp, T); TK(dHd, B * Tn * H, float); TK(dG, B * Tn * 4 * H, T); TK(dZH, (a.need_dfeat ? Tn : 1) * B * (D + H), float);
+        TK(dabar, a.need_dfeat ? B * D : 0, float);
         TK(dUF, B * Tn * (H + D), T); TK(dh_carry, B * H, float); TK(dc_carry, B * H, float);
         TK(dwa_acc, (a.attention && !w.attn_stream) ? B * L * H : 0, float); TK(dwa_t, a.attention ? B * L * H : 0, T);
         TK(dpre_all, w.attn_stream ? Tn * B * L * H : 0, T);
@@ -197,7 +200,6 @@ static inline int check_args(const sat_decoder_args* a) {
     SAT_REQUIRE(a->dtype == SAT_DTYPE_F32 || a->dtype == SAT_DTYPE_BF16, "bad dtype %d", a->dtype);
     SAT_REQUIRE(a->B > 0 && a->L > 0 && a->D > 0 && a->H > 0 && a->V > 0 && a->T > 0, "bad dims");
     SAT_REQUIRE(a->D % 8 == 0 && a->H % 8 == 0, "D (%d) and H (%d) must be multiples of 8", a->D, a->H);
-    SAT_REQUIRE(!(a->fused_loss && a->ado), "fused_loss with ado is not supported yet");
     SAT_REQUIRE(a->alphas != nullptr && (a->preds != nullptr || a->fused_loss), "missing output buffers");
     return SAT_OK;
 }
@@ -284,6 +286,7 @@ int decoder_forward_t(const sat_decoder_args& a) {
     SAT_REQUIRE(((uintptr_t)a.workspace & 255) == 0, "workspace must be 256B aligned");
     const int B = a.B, L = a.L, D = a.D, H = a.H, V = a.V, Tn = a.T;
     const int64_t zw = D + H;
+    SAT_CHECK_CUDA(cudaMemsetAsync(w.flags, 0, 4 * sizeof(int), st));
     SAT_TRY(prep_weights<T>(a, w, st));
 
     // features in compute dtype, contiguous (Q20)
@@ -328,7 +331,7 @@ int decoder_forward_t(const sat_decoder_args& a) {
     }
     // embeddings (decoder.py:85-89) and their share of the gate pre-activations, batched over t when teacher forcing
     if (a.tf) {
-        misc::gather_bt_kernel<T><<<B * Tn, 128, 0, sh>>>(w.E, a.embedding, H, a.captions, a.cap_stride, B, V);
+        misc::gather_bt_kernel<T><<<B * Tn, 128, 0, sh>>>(w.E, a.embedding, H, a.captions, a.cap_stride, B, V, w.flags);
         SAT_CHECK_CUDA(cudaGetLastError());
         auto e = lin<T>(B * Tn, 4 * H, w.b_g, SAT_ACT_NONE, w.Xg, 4 * H, nullptr, 0);
         SAT_TRY(gemm<T>(sh, w.E, H, true, w.w_gx, H, true, B * Tn, 4 * H, H, e));
@@ -421,9 +424,14 @@ int decoder_forward_t(const sat_decoder_args& a) {
         // with need_grad the same pass also leaves d loss / d logits for a unit upstream gradient (what the fused train step
         // feeds back); sat_decoder_backward recomputes it only when it is handed a dloss scalar
         misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, w.rowloss,
-                                                        a.need_grad ? w.dlog : (T*)nullptr, w.Vp, nullptr, 1.0f / (float)(B * (Tn - 1)));
+                                                        a.need_grad ? w.dlog : (T*)nullptr, w.Vp, nullptr, 1.0f / (float)(B * (Tn - 1)),
+                                                        a.ado, w.flags);
         misc::loss_partial_kernel<<<misc::LOSS_PARTS, 256, 0, st>>>(w.rowloss, B * Tn, a.alphas, B, Tn, L, w.loss_part);
-        misc::loss_finalize_kernel<<<1, 256, 0, st>>>(w.loss_part, misc::LOSS_PARTS, B * (Tn - 1), a.alphas != nullptr, B, L, a.alpha_c, a.loss);
+        misc::loss_finalize_kernel<<<1, 256, 0, st>>>(w.loss_part, misc::LOSS_PARTS, B * (Tn - 1), a.alphas != nullptr, B, L, a.alpha_c, a.loss,
+                                                      w.flags);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    } else if (a.loss) {
+        misc::status_kernel<<<1, 32, 0, st>>>(a.loss, w.flags);
         SAT_CHECK_CUDA(cudaGetLastError());
     }
     return SAT_OK;
@@ -451,7 +459,8 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     if (a.fused_loss) {
         const float scale = 1.0f / (float)(B * (Tn - 1));
         if (g.dloss)     // otherwise the forward's unit-gradient dlogits are still in the workspace
-            misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, nullptr, w.dlog, Vp, g.dloss, scale);
+            misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, nullptr, w.dlog, Vp, g.dloss, scale,
+                                                            a.ado, nullptr);
         if (a.attention) {
             misc::alpha_reg_grad_kernel<<<sat_cdiv(B * L, 128), 128, 0, st>>>(a.alphas, w.galpha, B, Tn, L, a.alpha_c, g.dloss);
             galpha = w.galpha;
@@ -497,7 +506,8 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     auto bwd_step = [&](int t, int b0, int nb, cudaStream_t s, uint8_t* scratch, cudaEvent_t wait_ev, cudaEvent_t rec_ev) -> int {
         const int gsm = nb < B ? g_split_gemm_sms : 0, actas = nb < B ? g_split_attn_ctas : 0;
         const size_t r = (size_t)t * B + b0;       // first time-major row of this half at step t
-        float* dzh = w.dZH + (size_t)b0 * zw;
+        // need_dfeat keeps every step's d[z | h] (the post-loop d img_features pass re-reads the dctx columns)
+        float* dzh = w.dZH + ((a.need_dfeat ? (size_t)t * B : (size_t)0) + b0) * zw;
         float* dh_carry = w.dh_carry + (size_t)b0 * H;
         // The cell backward of step t runs in the epilogue of the previous iteration's dh GEMM (EpiDhCell) when attention is on;
         // only the first iteration (t = T-1, dh_carry = 0) and the no-attention decoder launch the pointwise kernel.
@@ -538,7 +548,10 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
             p.galpha = galpha ? galpha + ((size_t)b0 * Tn + t) * L : nullptr; p.ld_ga = (int64_t)Tn * L;
             p.duf = w.dUF + r * (H + D); p.ld_duf = H + D;
             p.dwa_acc = w.dwa_acc ? w.dwa_acc + (size_t)b0 * L * H : nullptr;
-            p.dv_acc = w.dv_acc + (size_t)b0 * H; p.dbv_acc = w.dbv_acc + b0; p.da_acc = nullptr;
+            p.dv_acc = w.dv_acc + (size_t)b0 * H; p.dbv_acc = w.dbv_acc + b0;
+            // generic kernels: sum_t alpha_t (x) dctx_t accumulates straight into the caller's gradient buffer; the streaming
+            // kernels leave that term to dfeat_kernel after the loop (dctx_t stays in dZH[t])
+            p.da_acc = (g.img_features && !w.attn_stream) ? g.img_features + (size_t)b0 * L * D : nullptr;
             if (w.attn_stream) {
                 p.dpre_out = w.dpre_all + ((size_t)t * B + b0) * L * H;
                 p.ctx32 = w.Ctx32 + r * D; p.ld_c32 = D;
@@ -633,6 +646,12 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         }
         if (g.att_v_w) SAT_TRY(misc::colsum<float>(st, w.dv_acc, H, B, H, g.att_v_w, w.csum, w.csum_floats));
         if (g.att_v_b) SAT_TRY(misc::colsum<float>(st, w.dbv_acc, 1, B, 1, g.att_v_b, w.csum, w.csum_floats));
+        if (g.img_features) {
+            // d img_features, projection share: (sum_t dpre) W   ((B L) x D; added to the generic kernels' running sum)
+            auto e3 = lin<T>(B * L, D, nullptr, SAT_ACT_NONE, g.img_features, D, nullptr, 0,
+                             w.attn_stream ? nullptr : g.img_features, D);
+            SAT_TRY(gemm<T>(st, w.dwa_t, H, true, w.w_att, D, false, B * L, D, H, e3));
+        }
     }
 
     // ---- side chain: initial state (decoder.py:137-147) ------------------------------------------------------------
@@ -646,6 +665,10 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         SAT_TRY(misc::colsum<T>(sb, w.dpre0, 2 * H, B, 2 * H, w.gscratch, csb, w.csum_floats));
         if (g.init_h_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_h_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, sb));
         if (g.init_c_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.init_c_b, w.gscratch + H, (size_t)H * 4, cudaMemcpyDeviceToDevice, sb));
+        if (g.img_features) {     // d abar = dpre0 [init_h ; init_c]   (decoder.py:139-145)
+            auto e2 = lin<T>(B, D, nullptr, SAT_ACT_NONE, w.dabar, D, nullptr, 0);
+            SAT_TRY(gemm<T>(sb, w.dpre0, 2 * H, true, w.w_init, D, false, B, D, 2 * H, e2));
+        }
     }
     // ---- side chain: batched weight gradients (contraction over k = t*B + b) -----------------------------------------
     {
@@ -694,6 +717,19 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     if (g_tail_overlap) {
         SAT_CHECK_CUDA(cudaEventRecord(tl->join, sb));
         SAT_CHECK_CUDA(cudaStreamWaitEvent(st, tl->join, 0));
+    }
+    if (g.img_features) {
+        // d img_features (train.py:132 leaves the encoder outside no_grad): the remaining shares, after both chains.
+        //   attention on : += sum_t alpha[b,t,l] dctx_t[b,d] (streaming kernels only)  + d abar[b,d] / L
+        //   attention off: z_t = ctx_t = abar for every t (decoder.py:101-105): (d abar + sum_t (dz_t + dctx_t)) / L
+        SAT_REQUIRE(a.need_dfeat, "grads->img_features needs args->need_dfeat = 1 in both calls");
+        misc::DfeatParams q;
+        q.da = g.img_features; q.alphas = a.alphas; q.dzh = w.dZH; q.ld_dzh = zw; q.dctx_extra = a.ado ? w.dctx_all : nullptr;
+        q.dabar = w.dabar; q.B = B; q.Tn = Tn; q.L = L; q.D = D;
+        q.mode = !a.attention ? 2 : (w.attn_stream ? 1 : 0);
+        dim3 grid(sat_cdiv(D, 256), B);
+        misc::dfeat_kernel<<<grid, 256, 0, st>>>(q);
+        SAT_CHECK_CUDA(cudaGetLastError());
     }
     return SAT_OK;
 }

@@ -412,11 +412,11 @@ template <int BN, bool A_MN, bool B_MN, typename Epi, int SPLIT>
 int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB, int M, int N, int K, const Epi& epi, int b_static) {
     auto kern = gemm_kernel<BN, A_MN, B_MN, Epi, SPLIT>;
     constexpr int smem = Cfg<BN>::SMEM_BYTES;
-    static bool configured = false;
-    if (!configured) {
+    static SatPerDevice configured;
+    SAT_TRY(configured.once([&]() -> int {
         SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        configured = true;
-    }
+        return SAT_OK;
+    }));
     dim3 grid(sat_cdiv(N, BN), sat_cdiv(M, BM), SPLIT);
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[2];

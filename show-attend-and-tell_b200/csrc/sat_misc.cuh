@@ -99,9 +99,11 @@ struct PackList {
         return SAT_OK;
     }
 };
-// rank[r] = number of logits in row r strictly above the target's logit (utils.py:44-80 sequence_accuracy asks whether the
-// target is among the top k = whether rank < k; one pass over the logits instead of two topk passes).  A target outside
-// [0, V) gets rank V (never correct).  One block per row.
+// rank[r] = position of the target's logit in row r's descending order (utils.py:44-80 sequence_accuracy asks whether the
+// target is among the top k = whether rank < k; one pass over the logits instead of two topk passes).  Ties are broken
+// towards the LOWER index, so at most k entries of a tied block are admitted, like `preds.topk(k)` (which entries of a tie
+// topk returns is unspecified upstream; in ado mode the final ReLU, decoder.py:158, makes blocks of exact zeros the norm).
+// A target outside [0, V) or a NaN target logit gets rank V (never correct).  One block per row.
 __global__ void __launch_bounds__(256) logit_rank_kernel(const float* __restrict__ logits, int64_t ld, int V,
                                                          const int64_t* __restrict__ targets, int32_t* __restrict__ rank) {
     __shared__ int red[8];
@@ -110,8 +112,12 @@ __global__ void __launch_bounds__(256) logit_rank_kernel(const float* __restrict
     if (tgt < 0 || tgt >= V) { if (threadIdx.x == 0) rank[r] = V; return; }
     const float* p = logits + r * ld;
     const float x = p[tgt];
+    if (x != x) { if (threadIdx.x == 0) rank[r] = V; return; }
     int n = 0;
-    for (int v = threadIdx.x; v < V; v += blockDim.x) n += (p[v] > x) ? 1 : 0;
+    for (int v = threadIdx.x; v < V; v += blockDim.x) {
+        const float y = p[v];
+        n += (y > x || (y == x && v < (int)tgt) || y != y) ? 1 : 0;       // a NaN logit sorts above everything (torch.topk)
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = n;
@@ -120,6 +126,46 @@ __global__ void __launch_bounds__(256) logit_rank_kernel(const float* __restrict
         int t = 0;
         for (int w = 0; w < 8; ++w) t += red[w];
         rank[r] = t;
+    }
+}
+
+// utils.py:101-107 calculate_caption_lengths: number of tokens not in {skip0, skip1, skip2} (train.py:174-177 passes pad / start /
+// eos).  One block, fixed reduction order; the count stays on the device (the reference does .item() every batch).
+__global__ void __launch_bounds__(1024) count_tokens_kernel(const int64_t* __restrict__ tok, int64_t rows, int64_t cols, int64_t stride,
+                                                            int64_t s0, int64_t s1, int64_t s2, int64_t* __restrict__ out) {
+    __shared__ int red[32];
+    int n = 0;
+    const int64_t total = rows * cols;
+    for (int64_t i = threadIdx.x; i < total; i += blockDim.x) {
+        const int64_t r = i / cols, c = i - r * cols;
+        const int64_t t = tok[r * stride + c];
+        n += (t != s0 && t != s1 && t != s2) ? 1 : 0;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) n += __shfl_xor_sync(0xffffffffu, n, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = n;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int64_t t = 0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        out[0] = t;
+    }
+}
+
+// N2 feature cache: out[i, :] = store[idx[i], :] for rows of `row_vec16` 16-byte vectors (frozen-encoder features kept in HBM,
+// encoder.py:29-31 / train.py:132).  An index outside [0, n_items) gives a zero row and sets *err_flag.
+__global__ void __launch_bounds__(256) gather_items_kernel(const uint4* __restrict__ store, int64_t row_vec16, int64_t n_items,
+                                                           const int64_t* __restrict__ idx, uint4* __restrict__ out, int* __restrict__ err_flag) {
+    const int64_t i = blockIdx.y;
+    const int64_t src = idx[i];
+    const bool ok = (src >= 0 && src < n_items);
+    if (!ok && err_flag && threadIdx.x == 0 && blockIdx.x == 0) atomicOr(err_flag, 1);
+    const uint4* s = store + src * row_vec16;
+    uint4* d = out + i * row_vec16;
+    for (int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; v < row_vec16; v += (int64_t)gridDim.x * blockDim.x) {
+        uint4 x = make_uint4(0u, 0u, 0u, 0u);
+        if (ok) x = ldg_stream16(s + v);
+        asm volatile("st.global.cs.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(d + v), "r"(x.x), "r"(x.y), "r"(x.z), "r"(x.w) : "memory");
     }
 }
 
@@ -364,12 +410,12 @@ int sum_over_t_colsum(cudaStream_t s, T* out, const T* src, int64_t rows, int H,
             CV &= ~3;
             // an SM cannot change its L1 / shared-memory split while blocks are resident: ask for the all-shared split so that
             // a GEMM CTA (~193 KB of shared memory) can land beside this kernel's block
-            static bool configured = false;
-            if (!configured) {
+            static SatPerDevice configured;
+            SAT_TRY(configured.once([&]() -> int {
                 SAT_CHECK_CUDA(cudaFuncSetAttribute(sum_over_t_async_kernel<T>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                                     cudaSharedmemCarveoutMaxShared));
-                configured = true;
-            }
+                return SAT_OK;
+            }));
             const size_t smem = (size_t)2 * Tn * CV * 16 + (size_t)H * 4;
             sum_over_t_async_kernel<T><<<(int)blocks, 256, smem, s>>>(out, src, nvec, n, Tn, H, CV, scratch);
         } else {
@@ -437,9 +483,11 @@ template <typename TO>
 __global__ void gather_rows_kernel(TO* __restrict__ out, int64_t ld_out, const float* __restrict__ table, int H,
                                    const int64_t* __restrict__ idx, int64_t idx_stride, int V) {
     const int r = blockIdx.x;
-    int64_t tok = idx[(int64_t)r * idx_stride];
-    if (tok < 0) tok = 0;
-    if (tok >= V) tok = V - 1;
+    const int64_t tok = idx[(int64_t)r * idx_stride];
+    if (tok < 0 || tok >= V) {       // ids produced on the device (argmax / top-k) are always in range; a zero row otherwise
+        for (int h = threadIdx.x; h < H; h += blockDim.x) out[(int64_t)r * ld_out + h] = from_f32<TO>(0.0f);
+        return;
+    }
     const float* src = table + (size_t)tok * H;
     for (int h = threadIdx.x; h < H; h += blockDim.x) out[(int64_t)r * ld_out + h] = from_f32<TO>(src[h]);
 }
@@ -451,13 +499,18 @@ int gather_rows(cudaStream_t s, TO* out, int64_t ld_out, const float* table, int
     return SAT_OK;
 }
 // 2-D gather for (B, T) token grids written TIME-MAJOR to (T, B, H): row r = t*B + b reads cap[b*cap_stride + t]
+// A token outside [0, V) (nn.Embedding raises IndexError upstream) gathers a zero row -- matching the scatter below, which
+// skips it -- and sets SAT_FLAG_BAD_TOKEN in *err_flag; the host wrapper turns the flag into an exception.
 template <typename TO>
 __global__ void gather_bt_kernel(TO* __restrict__ out, const float* __restrict__ table, int H,
-                                 const int64_t* __restrict__ cap, int64_t cap_stride, int B, int V) {
+                                 const int64_t* __restrict__ cap, int64_t cap_stride, int B, int V, int* __restrict__ err_flag) {
     const int r = blockIdx.x, t = r / B, b = r - t * B;
-    int64_t tok = cap[(int64_t)b * cap_stride + t];
-    if (tok < 0) tok = 0;
-    if (tok >= V) tok = V - 1;
+    const int64_t tok = cap[(int64_t)b * cap_stride + t];
+    if (tok < 0 || tok >= V) {
+        if (err_flag && threadIdx.x == 0) atomicOr(err_flag, SAT_FLAG_BAD_TOKEN);
+        for (int h = threadIdx.x; h < H; h += blockDim.x) out[(int64_t)r * H + h] = from_f32<TO>(0.0f);
+        return;
+    }
     const float* src = table + (size_t)tok * H;
     for (int h = threadIdx.x; h < H; h += blockDim.x) out[(int64_t)r * H + h] = from_f32<TO>(src[h]);
 }
@@ -604,11 +657,14 @@ __global__ void argmax_rows_kernel(const float* __restrict__ x, int64_t ld, int 
 
 // ---- cross entropy over logits rows (train.py:150-151,161; Q10) ------------------------------------
 // row r = b*T + t of logits (B*T, V).  Rows with t == T-1 are excluded.  rowloss[r] = lse - logit[target].
-// Optionally writes dlogits = (softmax - onehot) * scale (T dtype), zero rows for t == T-1.
+// Optionally writes dlogits = (softmax - onehot) * scale (T dtype), zero rows for t == T-1.  relu_mask != 0: the logits went
+// through the final ReLU of the advanced deep output (decoder.py:158, Q8), so the gradient handed to the V-projection is
+// zero wherever the logit is not positive.  A target outside [0, V) (the reference raises IndexError) sets *err_flag and
+// contributes neither loss nor one-hot.
 template <typename TO>
 __global__ void ce_rows_kernel(const float* __restrict__ logits, int64_t ld, int V, int Tn, const int64_t* __restrict__ cap,
                                int64_t cap_stride, float* __restrict__ rowloss, TO* __restrict__ dlog, int64_t ld_d,
-                               const float* __restrict__ scale_ptr, float scale_mul) {
+                               const float* __restrict__ scale_ptr, float scale_mul, int relu_mask, int* __restrict__ err_flag) {
     __shared__ float red[32];
     const int r = blockIdx.x, b = r / Tn, t = r - b * Tn;
     const int B = gridDim.x / Tn;
@@ -644,14 +700,18 @@ __global__ void ce_rows_kernel(const float* __restrict__ logits, int64_t ld, int
     __syncthreads();
     s = red[0];
     const int64_t tgt = cap[(int64_t)b * cap_stride + t + 1];
+    const bool tgt_ok = (tgt >= 0 && tgt < V);
+    if (!tgt_ok && err_flag && threadIdx.x == 0) atomicOr(err_flag, SAT_FLAG_BAD_TOKEN);
     const float lse = m + logf(s);
-    if (rowloss && threadIdx.x == 0) rowloss[r] = lse - p[tgt];
+    if (rowloss && threadIdx.x == 0) rowloss[r] = tgt_ok ? lse - p[tgt] : 0.0f;
     if (dlog) {
         const float sc = (scale_ptr ? scale_ptr[0] : 1.0f) * scale_mul;
         const float inv = 1.0f / s;
         for (int v = threadIdx.x; v < V; v += blockDim.x) {
-            float g = expf(p[v] - m) * inv;
+            const float x = p[v];
+            float g = expf(x - m) * inv;
             if (v == tgt) g -= 1.0f;
+            if (relu_mask && !(x > 0.0f)) g = 0.0f;
             dlog[ro * ld_d + v] = from_f32<TO>(g * sc);
         }
     }
@@ -688,7 +748,7 @@ __global__ void loss_partial_kernel(const float* __restrict__ rowloss, int rows,
     if (threadIdx.x == 0) { part[2 * blockIdx.x] = ce; part[2 * blockIdx.x + 1] = reg; }
 }
 __global__ void loss_finalize_kernel(const float* __restrict__ part, int nparts, int n_active, int has_alphas, int B, int L,
-                                     float alpha_c, float* __restrict__ loss) {
+                                     float alpha_c, float* __restrict__ loss, const int* __restrict__ err_flag) {
     __shared__ float red[2][32];
     float ce = 0.0f, reg = 0.0f;
     for (int i = threadIdx.x; i < nparts; i += blockDim.x) { ce += part[2 * i]; reg += part[2 * i + 1]; }
@@ -697,6 +757,7 @@ __global__ void loss_finalize_kernel(const float* __restrict__ part, int nparts,
         loss[0] = n_active > 0 ? ce / (float)n_active : 0.0f;
         loss[1] = has_alphas ? alpha_c * reg / (float)(B * L) : 0.0f;
         loss[2] = loss[0] + loss[1];
+        loss[3] = err_flag ? (float)err_flag[0] : 0.0f;      // SAT_FLAG_* bits of this call (0 = clean)
     }
 }
 
@@ -757,6 +818,46 @@ __global__ void add_into_kernel(T* __restrict__ y, const float* __restrict__ x, 
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         y[i] = from_f32<T>(to_f32<T>(y[i]) + x[i]);
 }
+// loss[3] = status bits of a call that did not fuse the loss
+__global__ void status_kernel(float* __restrict__ loss, const int* __restrict__ flags) {
+    if (threadIdx.x == 0) { loss[0] = loss[1] = loss[2] = 0.0f; loss[3] = (float)flags[0]; }
+}
+
+// d img_features, the shares that are not a GEMM (see sat_decoder_backward).  One thread per (b, d) column keeps the T dctx
+// values of its column in registers / L1 and walks the L locations.
+//   mode 0: da[b,l,d] += dabar[b,d] / L                                   (generic attention kernels summed alpha (x) dctx)
+//   mode 1: da[b,l,d] += sum_t alphas[b,t,l] dzh[t,b,d] + dabar[b,d] / L   (streaming attention kernels)
+//   mode 2: da[b,l,d]  = (dabar[b,d] + sum_t (dzh[t,b,d] + extra[t,b,d])) / L   (no attention)
+struct DfeatParams {
+    float* da; const float* alphas; const float* dzh; int64_t ld_dzh; const float* dctx_extra; const float* dabar;
+    int B, Tn, L, D, mode;
+};
+__global__ void __launch_bounds__(256) dfeat_kernel(const DfeatParams q) {
+    const int d = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (d >= q.D) return;
+    const float invL = 1.0f / (float)q.L;
+    const float mean_share = q.dabar[(size_t)b * q.D + d] * invL;
+    float* col = q.da + (size_t)b * q.L * q.D + d;
+    if (q.mode == 0) {
+        for (int l = 0; l < q.L; ++l) col[(size_t)l * q.D] += mean_share;
+    } else if (q.mode == 2) {
+        float s = 0.0f;
+        for (int t = 0; t < q.Tn; ++t) {
+            s += q.dzh[((size_t)t * q.B + b) * q.ld_dzh + d];
+            if (q.dctx_extra) s += q.dctx_extra[((size_t)t * q.B + b) * q.D + d];
+        }
+        const float v = mean_share + s * invL;
+        for (int l = 0; l < q.L; ++l) col[(size_t)l * q.D] = v;
+    } else {
+        for (int l = 0; l < q.L; ++l) {
+            float s = mean_share;
+            for (int t = 0; t < q.Tn; ++t)       // alphas[b,t,l] is a warp-wide broadcast load
+                s = fmaf(q.alphas[((size_t)b * q.Tn + t) * q.L + l], q.dzh[((size_t)t * q.B + b) * q.ld_dzh + d], s);
+            col[(size_t)l * q.D] += s;
+        }
+    }
+}
+
 inline int grid_for(int64_t n) { return (int)(sat_cdiv64(n, 256) < (int64_t)(148 * 16) ? sat_cdiv64(n, 256) : (int64_t)(148 * 16)); }
 
 }  // namespace misc

@@ -58,6 +58,9 @@ class _DecoderFn(torch.autograd.Function):
         a.gate = int(module.use_gate)
         a.start_token = int(module.start_token)
         a.need_grad = int(need_grad)
+        # train.py:132 runs the encoder outside no_grad: the gradient reaches img_features when it requires grad
+        need_dfeat = bool(need_grad and ctx.needs_input_grad[1])
+        a.need_dfeat = int(need_dfeat)
         a.fused_loss = int(fused)
         a.alpha_c = float(alpha_c)
         a.a_dtype = _lib.dtype_code(img_features.dtype)
@@ -69,16 +72,18 @@ class _DecoderFn(torch.autograd.Function):
         keep = _fill_params(a, module)
         preds = torch.empty(B, T, V, device=dev, dtype=torch.float32)          # decoder.py:92
         alphas = torch.empty(B, T, Lloc, device=dev, dtype=torch.float32)      # decoder.py:93
-        loss = torch.zeros(3, device=dev, dtype=torch.float32)
+        loss = torch.zeros(4, device=dev, dtype=torch.float32)          # [ce, alpha regulariser, total, status bits]
         a.preds, a.alphas, a.loss = preds.data_ptr(), alphas.data_ptr(), loss.data_ptr()
         nbytes = C.c_int64(0)
-        _lib.check(L.sat_decoder_workspace_bytes(C.byref(a), C.byref(nbytes)), "sat_decoder_workspace_bytes")
-        ws = torch.empty(nbytes.value + 256, device=dev, dtype=torch.uint8)
-        off = (-ws.data_ptr()) % 256
-        a.workspace = ws.data_ptr() + off
-        a.workspace_bytes = nbytes.value
-        a.stream = torch.cuda.current_stream(dev).cuda_stream
-        _lib.check(L.sat_decoder_forward(C.byref(a)), "sat_decoder_forward")
+        with torch.cuda.device(dev):
+            _lib.check(L.sat_decoder_workspace_bytes(C.byref(a), C.byref(nbytes)), "sat_decoder_workspace_bytes")
+            ws = torch.empty(nbytes.value + 256, device=dev, dtype=torch.uint8)
+            off = (-ws.data_ptr()) % 256
+            a.workspace = ws.data_ptr() + off
+            a.workspace_bytes = nbytes.value
+            a.stream = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(L.sat_decoder_forward(C.byref(a)), "sat_decoder_forward")
+        ctx.need_dfeat = need_dfeat
         ctx.args = a
         ctx.keep = (keep, ws, img_features, captions, dropout_mask, preds, alphas, loss)
         ctx.module = module
@@ -131,12 +136,20 @@ class _DecoderFn(torch.autograd.Function):
             gt = torch.empty_like(p, dtype=torch.float32)
             grads[key] = gt
             setattr(g, field, gt.data_ptr())
-        a.stream = torch.cuda.current_stream(dev).cuda_stream
-        _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(g)), "sat_decoder_backward")
+        dfeat = None
+        if ctx.need_dfeat:
+            feats = ctx.keep[2]
+            dfeat = torch.empty(feats.shape, device=dev, dtype=torch.float32)
+            g.img_features = dfeat.data_ptr()
+        with torch.cuda.device(dev):
+            a.stream = torch.cuda.current_stream(dev).cuda_stream
+            _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(g)), "sat_decoder_backward")
+        if dfeat is not None and dfeat.dtype != ctx.keep[2].dtype:
+            dfeat = dfeat.to(ctx.keep[2].dtype)
         out = []
         for name, p in module.named_parameters():
             out.append(grads.get(name))       # None reproduces the reference's grad=None pattern (Q6, Q7)
-        return (None, None, None, None, None, None, None, *out)
+        return (None, dfeat, None, None, None, None, None, *out)
 
 
 class Decoder(nn.Module):
@@ -150,6 +163,7 @@ class Decoder(nn.Module):
         self.use_gate = gate
         self.compute_dtype = compute_dtype
         self.encoder_dim = encoder_dim
+        self.validate_tokens = True
 
         if bert:  # decoder.py:21-36
             from transformers import BertModel, BertTokenizer
@@ -197,7 +211,7 @@ class Decoder(nn.Module):
             unused |= {"f_beta.weight", "f_beta.bias"}
         return unused
 
-    def _check_inputs(self, img_features, captions=None):
+    def _check_inputs(self, img_features, captions=None, check_tokens=None):
         _lib.require_cuda(img_features, "img_features")
         if img_features.dim() != 3 or img_features.shape[2] != self.encoder_dim:
             raise RuntimeError(f"img_features must be (B, L, {self.encoder_dim}); got {tuple(img_features.shape)}")
@@ -210,6 +224,17 @@ class Decoder(nn.Module):
                 captions = captions.to(img_features.device)
             if captions.stride(1) != 1:
                 captions = captions.contiguous()
+            if self.validate_tokens and check_tokens is not None and captions.shape[1] > 1:
+                # nn.Embedding (decoder.py:87) / CrossEntropyLoss (train.py:161) raise IndexError on an id outside [0, V); the
+                # kernels only flag it (loss[3]) and read a zero row.  Columns the reference touches: [0, T) as step inputs
+                # under teacher forcing (free-running decoding uses `captions` for its length only, decoder.py:77), [1, T) as
+                # targets of the fused loss.  One tiny reduction + host sync per call; `decoder.validate_tokens = False`
+                # skips it (FusedTrainStep checks the device flag lazily instead).
+                used = captions[:, :-1] if self.use_tf else (captions[:, 1:-1] if check_tokens == "loss" else None)
+                if used is not None and used.numel():
+                    lo, hi = torch.aminmax(used)
+                    if int(lo) < 0 or int(hi) >= self.vocabulary_size:
+                        raise IndexError(f"caption token out of range [0, {self.vocabulary_size}): min {int(lo)}, max {int(hi)}")
         return captions
 
     def _dropout_mask(self, B, T, device, dropout_masks):
@@ -224,21 +249,21 @@ class Decoder(nn.Module):
         return keep.to(torch.float32) / (1.0 - p)
 
     def forward(self, img_features, captions, *, dropout_masks=None):
-        captions = self._check_inputs(img_features, captions)
+        captions = self._check_inputs(img_features, captions, "forward")
         B, T = img_features.shape[0], captions.shape[1] - 1
         mask = self._dropout_mask(B, T, img_features.device, dropout_masks)
         params = tuple(p for _, p in self.named_parameters())
-        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
-        return _DecoderFn.apply(self, img_features.detach(), captions, mask, False, 0.0, need_grad, *params)
+        need_grad = torch.is_grad_enabled() and (img_features.requires_grad or any(p.requires_grad for p in params))
+        return _DecoderFn.apply(self, img_features, captions, mask, False, 0.0, need_grad, *params)
 
     def forward_loss(self, img_features, captions, alpha_c=1.0, *, dropout_masks=None):
         """Extension: forward + the train.py:150-162 loss fused on device.  Returns (loss, preds, alphas)."""
-        captions = self._check_inputs(img_features, captions)
+        captions = self._check_inputs(img_features, captions, "loss")
         B, T = img_features.shape[0], captions.shape[1] - 1
         mask = self._dropout_mask(B, T, img_features.device, dropout_masks)
         params = tuple(p for _, p in self.named_parameters())
-        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
-        return _DecoderFn.apply(self, img_features.detach(), captions, mask, True, float(alpha_c), need_grad, *params)
+        need_grad = torch.is_grad_enabled() and (img_features.requires_grad or any(p.requires_grad for p in params))
+        return _DecoderFn.apply(self, img_features, captions, mask, True, float(alpha_c), need_grad, *params)
 
     # ------------------------------------------------------------------------------------------
     def get_init_lstm_state(self, img_features):
@@ -248,7 +273,7 @@ class Decoder(nn.Module):
         dev = img_features.device
         dt = self.compute_dtype
         code = _lib.dtype_code(dt)
-        with torch.no_grad():
+        with torch.no_grad(), torch.cuda.device(dev):
             avg = img_features.to(torch.float32).mean(dim=1).to(dt).contiguous()
             w = torch.cat((self.init_h.weight, self.init_c.weight), 0).to(dt).contiguous()
             b = torch.cat((self.init_h.bias, self.init_c.bias), 0).float().contiguous()
@@ -294,7 +319,8 @@ class Decoder(nn.Module):
         a.workspace = ws.data_ptr() + ((-ws.data_ptr()) % 256)
         a.workspace_bytes = nbytes.value
         a.stream = torch.cuda.current_stream(dev).cuda_stream
-        with torch.no_grad():
+        with torch.no_grad(), torch.cuda.device(dev):
+            a.stream = torch.cuda.current_stream(dev).cuda_stream
             _lib.check(L.sat_beam_search(C.byref(a)), "sat_beam_search")
         lens, status, live = out_len.cpu().tolist(), out_status.cpu().tolist(), out_live.cpu().tolist()
         toks, alph = out_tokens.cpu(), out_alphas.cpu()

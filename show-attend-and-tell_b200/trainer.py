@@ -4,9 +4,18 @@
 
 = sat_decoder_forward (with the train.py:150-162 loss fused) -> sat_decoder_backward writing gradients straight
 into one flat fp32 buffer -> (world > 1) one NCCL all-reduce of that buffer over NVLink -> fused Adam
-(sat_adam_step) on the flat parameter buffer.  It bypasses autograd: no tape, no per-tensor optimizer launches.
+(sat_adam_step_dev) on the flat parameter buffer.  It bypasses autograd: no tape, no per-tensor optimizer launches.
 Data parallelism is one process per GPU, batch-sharded, gradients averaged; parameters the
 reference leaves with grad=None (Q6, Q7) are simply not part of the flat buffer.
+
+Every step-dependent scalar (learning rate, Adam step count) lives in device memory, so the whole step -- dropout mask,
+forward, loss, backward, all-reduce, Adam -- can be captured ONCE into a CUDA graph per (feature buffer, caption buffer)
+pair and replayed with a single launch (`use_cuda_graph=True`): a training loop that reads the loss back every step
+(train.py:179) otherwise pays the host cost of ~165 kernel launches at the start of every step.
+
+The gradient wrt img_features is not produced here: train.py:71 hands only decoder.parameters() to Adam, so although
+train.py:132 runs the encoder outside no_grad nothing ever consumes that gradient in a training step
+(`Decoder.forward` produces it on request for callers that do want it).
 """
 from __future__ import annotations
 
@@ -23,9 +32,9 @@ class FusedTrainStep:
     EARLY_KEYS = ("init_h.weight", "init_h.bias", "init_c.weight", "init_c.bias", "lstm.weight_ih", "lstm.weight_hh")
 
     def __init__(self, decoder, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, alpha_c=1.0, process_group=None,
-                 distributed=None):
+                 distributed=None, step_size=None, gamma=0.1, use_cuda_graph=False):
         self.dec = decoder
-        self.lr, self.betas, self.eps, self.alpha_c = lr, betas, eps, alpha_c
+        self.base_lr, self.betas, self.eps, self.alpha_c = float(lr), betas, eps, alpha_c
         self.distributed = dist.is_initialized() if distributed is None else distributed
         self.pg = process_group
         self.world = dist.get_world_size(process_group) if self.distributed else 1
@@ -36,11 +45,13 @@ class FusedTrainStep:
         self.train_keys = early + [k for k in keys if k not in self.EARLY_KEYS]
         named = dict(decoder.named_parameters())
         dev = next(decoder.parameters()).device
+        self.device = dev
         offsets, off = {}, 0
         for k in self.train_keys:
             offsets[k] = off
             off = (off + named[k].numel() + 3) & ~3          # keep every tensor 16-byte aligned
         n = off
+        self.offsets = offsets
         self.n_early = max([offsets[k] + ((named[k].numel() + 3) & ~3) for k in early], default=0)
         self.overlap_allreduce = True
         self._comm_stream = None
@@ -57,7 +68,14 @@ class FusedTrainStep:
             p.data = self.flat_param[o:o + m].view_as(p)
             self.grad_views[k] = self.flat_grad[o:o + m].view_as(p)
         self.n = off
+        # optimizer state on the device: [lr, beta1, beta2, eps, weight_decay, grad_scale] and the update counter
+        self.hyper = torch.tensor([self.base_lr, betas[0], betas[1], eps, 0.0, 1.0 / self.world], device=dev, dtype=torch.float32)
+        self.step_dev = torch.zeros(1, device=dev, dtype=torch.int32)
         self.step_count = 0
+        # StepLR (train.py:72: optim.lr_scheduler.StepLR(optimizer, args.step_size), default gamma 0.1; stepped once per
+        # epoch at train.py:100)
+        self.step_size, self.gamma, self.epoch = step_size, float(gamma), 0
+        self.lr = self.base_lr
         self._ws = None
         self._ws_key = None
         self._a = None
@@ -68,6 +86,39 @@ class FusedTrainStep:
         self._grads = None
         self._next_mask = None
         self.last_alphas = None
+        self.use_cuda_graph = bool(use_cuda_graph)
+        self._graphs = {}             # (feature ptr, caption ptr, shapes, training) -> (CUDAGraph, tensors kept alive)
+        self._seen = {}               # the same key -> number of eager steps run so far (capture on the third)
+        self.graph_replays = 0
+        if self.world > 1:
+            self._sync_replicas()
+
+    # ---- data-parallel replica consistency ------------------------------------------------------------------------
+    def _sync_replicas(self):
+        """Every rank starts from rank 0's weights and the same flat layout.  Gradients are summed every step, so replicas
+        that start equal stay equal; a replica built with a different seed / init would otherwise drift silently."""
+        sig = self.layout_signature()
+        sigs = [None] * self.world
+        dist.all_gather_object(sigs, sig, group=self.pg)
+        for r, s in enumerate(sigs):
+            if s != sig:
+                raise RuntimeError(f"FusedTrainStep: flat parameter layout differs between rank {dist.get_rank(self.pg)} and rank {r}")
+        dist.broadcast(self.flat_param, src=dist.get_global_rank(self.pg, 0) if self.pg is not None else 0, group=self.pg)
+        # parameters outside the flat buffer (frozen BERT embedding, modules the flags leave unused) are inputs too
+        for k, p in self._named.items():
+            if k not in self.offsets:
+                dist.broadcast(p.data, src=dist.get_global_rank(self.pg, 0) if self.pg is not None else 0, group=self.pg)
+
+    def _check_param_storage(self, cur):
+        """A `dec.to()`, `.bfloat16()` or `load_state_dict(assign=True)` after construction moves a parameter out of the flat
+        buffer: the forward pass would follow the new storage while Adam kept updating the old one.  Fail loudly instead."""
+        base = self.flat_param.data_ptr()
+        for (k, p), ptr in zip(self._named.items(), cur):
+            o = self.offsets.get(k)
+            if o is not None and ptr != base + 4 * o:
+                raise RuntimeError(
+                    f"FusedTrainStep: parameter '{k}' no longer lives in the flat parameter buffer (was the decoder moved, cast "
+                    "or re-assigned after FusedTrainStep was built?).  Use load_state_dict() (copies in place) or rebuild the trainer.")
 
     def _args(self, img_features, captions, dropout_mask):
         """The sat_decoder_args of this step.  The struct is built once per (shape, dtype, flags) and kept; a step only
@@ -91,14 +142,14 @@ class FusedTrainStep:
             a.tf, a.ado, a.attention, a.gate = (int(dec.use_tf), int(dec.use_advanced_deep_output), int(dec.use_attention),
                                                 int(dec.use_gate))
             a.start_token = int(dec.start_token)
-            a.need_grad, a.fused_loss = 1, 1
+            a.need_grad, a.fused_loss, a.need_dfeat = 1, 1, 0
             a.a_dtype = a_dtype
             a.img_features = img_features.data_ptr()
             a.a_stride_b, a.a_stride_l, a.a_stride_d = img_features.stride()
             a.captions = captions.data_ptr()
             a.cap_stride = captions.stride(0)
             self.alphas = torch.empty(B, T, Lloc, device=dev, dtype=torch.float32)
-            self.loss = torch.zeros(3, device=dev, dtype=torch.float32)
+            self.loss = torch.zeros(4, device=dev, dtype=torch.float32)      # [ce, alpha regulariser, total, status bits]
             # no (B,T,V) preds tensor: the fused loss reads the logits from the workspace (padded row pitch)
             a.preds, a.alphas, a.loss = None, self.alphas.data_ptr(), self.loss.data_ptr()
             nbytes = C.c_int64(0)
@@ -108,6 +159,8 @@ class FusedTrainStep:
             a.workspace_bytes = nbytes.value
             self._a = a
             self._ws_key = key
+            self._graphs.clear()          # captured graphs point into the old workspace
+            self._seen.clear()
         a = self._a
         a.alpha_c = float(self.alpha_c)
         a.img_features = img_features.data_ptr()
@@ -115,8 +168,7 @@ class FusedTrainStep:
         a.captions = captions.data_ptr()
         a.cap_stride = captions.stride(0)
         a.dropout_mask = None if dropout_mask is None else dropout_mask.data_ptr()
-        # parameters are views into flat_param (fixed addresses) unless the caller re-assigned .data: re-read the pointers
-        # only when the parameter objects' storage moved
+        # parameters are views into flat_param (fixed addresses): re-read the pointers only when a storage moved
         ptrs = self._param_ptrs()
         if ptrs is not self._a_ptrs:
             for field, ptr in ptrs:
@@ -130,9 +182,12 @@ class FusedTrainStep:
         named = self._named
         cur = tuple(p.data_ptr() for p in named.values())
         if cur != self._ptr_sig:
+            self._check_param_storage(cur)
             self._ptr_sig = cur
             self._ptr_list = [(field, None if named.get(_lib.PARAM_KEYS[field]) is None else named[_lib.PARAM_KEYS[field]].data_ptr())
                               for field in _lib.PARAM_FIELDS]
+            self._graphs.clear()
+            self._seen.clear()
         return self._ptr_list
 
     def sync_grads(self):
@@ -178,34 +233,104 @@ class FusedTrainStep:
             return None
         return torch.empty(B, T, self.dec.embedding_size, device=device, dtype=torch.float32).bernoulli_(1.0 - p).mul_(1.0 / (1.0 - p))
 
-    def step(self, img_features, captions, dropout_mask=None, optimizer_step=True):
-        """One training step; returns the device tensor [ce, alpha_reg, total] (no host sync)."""
-        dec = self.dec
+    # ---- learning-rate schedule (train.py:72,100) --------------------------------------------------------------------
+    def set_lr(self, lr):
+        self.lr = float(lr)
+        self.hyper[0:1].fill_(self.lr)        # a stream-ordered device write: graphs replayed afterwards read the new value
+
+    def scheduler_step(self):
+        """`scheduler.step()` of StepLR(optimizer, step_size, gamma=0.1), called once per epoch (train.py:100):
+        lr = base_lr * gamma ** (epoch // step_size)."""
+        self.epoch += 1
+        if self.step_size:
+            self.set_lr(self.base_lr * self.gamma ** (self.epoch // int(self.step_size)))
+        return self.lr
+
+    # ---- one step ------------------------------------------------------------------------------------------------------
+    def _run(self, img_features, captions, dropout_mask, optimizer_step):
         L = _lib.lib()
-        captions = dec._check_inputs(img_features, captions)
-        B, T = img_features.shape[0], captions.shape[1] - 1
-        own_mask = dropout_mask is None and dec.training
-        if own_mask:
-            # the mask of this step was drawn at the end of the previous one (behind its Adam kernel), so a step starts
-            # with its first CUDA kernel instead of four small RNG launches
-            m = self._next_mask
-            if m is None or m.shape[0] != B or m.shape[1] != T or m.device != img_features.device:
-                m = self._fresh_mask(B, T, img_features.device)
-            dropout_mask, self._next_mask = m, None
         a = self._args(img_features, captions, dropout_mask)
         _lib.check(L.sat_decoder_forward(C.byref(a)), "sat_decoder_forward")
         _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(self._grad_struct())), "sat_decoder_backward")
         self.sync_grads()
         if optimizer_step:
+            _lib.check(L.sat_adam_step_dev(self.flat_param.data_ptr(), self.flat_grad.data_ptr(), self.exp_avg.data_ptr(),
+                                           self.exp_avg_sq.data_ptr(), self.n, self.hyper.data_ptr(), self.step_dev.data_ptr(),
+                                           a.stream), "sat_adam_step_dev")
+
+    def step(self, img_features, captions, dropout_mask=None, optimizer_step=True):
+        """One training step; returns the device tensor [ce, alpha_reg, total, status] (no host sync)."""
+        dec = self.dec
+        captions = dec._check_inputs(img_features, captions)      # token ids are checked lazily: check_status()
+        B, T = img_features.shape[0], captions.shape[1] - 1
+        with torch.cuda.device(img_features.device):
+            if self.use_cuda_graph and dropout_mask is None and optimizer_step:
+                self._graph_step(img_features, captions)
+            else:
+                own_mask = dropout_mask is None and dec.training
+                if own_mask:
+                    # the mask of this step was drawn at the end of the previous one (behind its Adam kernel), so a step
+                    # starts with its first CUDA kernel instead of four small RNG launches
+                    m = self._next_mask
+                    if m is None or m.shape[0] != B or m.shape[1] != T or m.device != img_features.device:
+                        m = self._fresh_mask(B, T, img_features.device)
+                    dropout_mask, self._next_mask = m, None
+                self._run(img_features, captions, dropout_mask, optimizer_step)
+                if own_mask:
+                    self._mask_in_use = dropout_mask          # keep it alive until the kernels that read it have been enqueued
+                    self._next_mask = self._fresh_mask(B, T, img_features.device)
+        if optimizer_step:
             self.step_count += 1
-            _lib.check(L.sat_adam_step(self.flat_param.data_ptr(), self.flat_grad.data_ptr(), self.exp_avg.data_ptr(),
-                                       self.exp_avg_sq.data_ptr(), self.n, self.lr, self.betas[0], self.betas[1], self.eps,
-                                       0.0, self.step_count, 1.0 / self.world, a.stream), "sat_adam_step")
-        if own_mask:
-            self._mask_in_use = dropout_mask          # keep it alive until the kernels that read it have been enqueued
-            self._next_mask = self._fresh_mask(B, T, img_features.device)
         self.last_alphas = self.alphas
         return self.loss
+
+    def _graph_step(self, img_features, captions):
+        """Replay (or, on the third step with the same buffers, capture) the CUDA graph of one whole step.  The graph is
+        tied to the addresses of the feature and caption buffers: feed a training loop from a fixed set of device buffers
+        (double buffering = two graphs)."""
+        key = (img_features.data_ptr(), captions.data_ptr(), tuple(img_features.shape), tuple(img_features.stride()),
+               img_features.dtype, tuple(captions.shape), captions.stride(0), bool(self.dec.training))
+        g = self._graphs.get(key)
+        if g is not None:
+            g[0].replay()
+            self.graph_replays += 1
+            return
+        B, T = img_features.shape[0], captions.shape[1] - 1
+        seen = self._seen.get(key, 0)
+        self._seen[key] = seen + 1
+        if seen < 2 or self._ws_key is None:
+            # eager steps first: they allocate the workspace, create the library's side streams / events and set the kernels'
+            # shared-memory attributes -- none of which may happen during stream capture
+            self._run(img_features, captions, self._fresh_mask(B, T, img_features.device), True)
+            return
+        if len(self._graphs) >= 8:
+            self._graphs.pop(next(iter(self._graphs)))
+        graph = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize(img_features.device)
+        with torch.cuda.graph(graph):
+            mask = self._fresh_mask(B, T, img_features.device)      # drawn inside the graph: a fresh mask every replay
+            self._run(img_features, captions, mask, True)
+        self._graphs[key] = (graph, mask, img_features, captions)
+        graph.replay()              # capture records, it does not execute
+        self.graph_replays += 1
+
+    def check_status(self, loss_host=None):
+        """Raise what the reference raises eagerly: IndexError for a caption id outside [0, V) (nn.Embedding /
+        CrossEntropyLoss).  The kernels only set a flag (loss[3]); call this wherever the loss is read back anyway
+        (pass the host copy to avoid another sync)."""
+        flags = int((self.loss if loss_host is None else loss_host)[3])
+        if flags & 1:
+            raise IndexError(f"caption token out of range [0, {self.dec.vocabulary_size}) in the last step")
+
+    def logits(self):
+        """(B, T, V) fp32 view of the logits the last step left in the workspace (row pitch padded to 8 floats)."""
+        if self._a is None:
+            raise RuntimeError("logits() needs a step() first")
+        ptr, ld = C.c_void_p(), C.c_int64()
+        _lib.check(_lib.lib().sat_decoder_logits(C.byref(self._a), C.byref(ptr), C.byref(ld)), "sat_decoder_logits")
+        a = self._a
+        off = (ptr.value - self._ws.data_ptr()) // 4
+        return torch.as_strided(self._ws.view(torch.float32), (a.B, a.T, a.V), (a.T * ld.value, ld.value, 1), off)
 
     def accuracy_counts(self, captions, ks=(1, 5), ignore_index=3):
         """train.py:144-145 for the step just run: device tensor [correct@1, correct@5, non-padding tokens] over
@@ -223,6 +348,7 @@ class FusedTrainStep:
         if targets.shape != (a.B, a.T):
             raise RuntimeError(f"captions {tuple(captions.shape)} do not belong to the last step (B={a.B}, T={a.T})")
         rank = torch.empty(a.B, a.T, device=targets.device, dtype=torch.int32)
-        _lib.check(L.sat_logit_rank(ptr.value, ld.value, a.B * a.T, a.V, targets.data_ptr(), rank.data_ptr(),
-                                    torch.cuda.current_stream(targets.device).cuda_stream), "sat_logit_rank")
+        with torch.cuda.device(targets.device):
+            _lib.check(L.sat_logit_rank(ptr.value, ld.value, a.B * a.T, a.V, targets.data_ptr(), rank.data_ptr(),
+                                        torch.cuda.current_stream(targets.device).cuda_stream), "sat_logit_rank")
         return metrics.accuracy_counts(rank, targets, ks, ignore_index)

@@ -1,0 +1,210 @@
+"""GPU: parity at the FULL sizes BASELINE.json's configurations name (c1 .. c5), against the oracle run on the GPU in fp32
+(`oracle/sat_oracle.py` creates its tensors on the input's device; TF32 is off, so its matmuls are true fp32).
+
+Bars ("next round" item 1):
+  * loss: rtol 2e-5 (fp32 mode) / 3e-2 (bf16 mode);
+  * every parameter gradient: relative L2 error <= 2e-3 (fp32) / 5e-2 (bf16) of the oracle's gradient;
+  * sum over L of alpha = 1 +- 1e-5 in both modes; alphas / logits elementwise at the tolerances written below;
+  * free-running decoding (c5) is checked teacher-style: the oracle is fed OUR greedy tokens, so a bf16 near-tie
+    argmax cannot hide (or fake) a divergence; our token must also be an argmax of the oracle's logits within the logit tolerance;
+  * c4: fp32 beam-search tokens bit-exact against the oracle's `caption` on a 16-image sample of a 128-image batch.
+Every case also writes its measured errors to gpurun_out/fullsize_parity.jsonl (evidence; copied to profiles/).
+"""
+import json
+import os
+
+import pytest
+import torch
+
+from oracle import sat_oracle as O
+from sat_b200 import synth
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _log(rec):
+    try:
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", "fullsize_parity.jsonl"), "a") as f:
+            f.write(json.dumps(rec) + "\n")
+    except OSError:
+        pass
+
+
+def _rel_l2(got, ref):
+    return (got.double() - ref.double()).norm().item() / (ref.double().norm().item() + 1e-30)
+
+
+def _make_decoder(cfg, P, dt):
+    from sat_b200.decoder import Decoder
+    if cfg.get("bert"):
+        H.stub_bert()
+    dec = Decoder(cfg["V"], cfg["D"], tf=cfg["tf"], ado=cfg["ado"], bert=cfg.get("bert", False), attention=True,
+                  compute_dtype=dt, gate=cfg.get("gate", True))
+    dec.load_state_dict(P, strict=True)
+    return dec.cuda()
+
+
+def _oracle_step(cfg, P, a, cap, masks, feed_tokens=None):
+    """Oracle forward + train.py loss + backward on the GPU, fp32.  Returns (preds, alphas, loss, grads)."""
+    Pr = {k: v.cuda().clone().requires_grad_(True) for k, v in P.items()}
+    pr, ar = O.decoder_forward(Pr, a, cap, tf=cfg["tf"], ado=cfg["ado"], attention=True, gate=cfg.get("gate", True),
+                               start_token=cfg.get("start_token", 0), dropout_masks=masks, feed_tokens=feed_tokens)
+    loss = O.train_loss(pr, ar, cap, 1.0)
+    loss.backward()
+    grads = {k: v.grad for k, v in Pr.items()}
+    return pr.detach(), ar.detach(), loss.item(), grads
+
+
+# name, config, compute dtype
+FULL = [
+    ("c1_fp32", dict(B=32, D=512, H=512, V=2531, T=20, tf=True, ado=False), torch.float32),
+    ("c1_fp32_ado", dict(B=32, D=512, H=512, V=2531, T=20, tf=True, ado=True), torch.float32),      # train_models.py: --tf --ado --attention
+    ("c2_bf16", dict(B=256, D=2048, H=512, V=2531, T=20, tf=True, ado=False), torch.bfloat16),      # the bench workload
+    ("c2_bf16_ado", dict(B=256, D=2048, H=512, V=2531, T=20, tf=True, ado=True), torch.bfloat16),
+    ("c3_bf16_D512", dict(B=128, D=512, H=512, V=10000, T=50, tf=True, ado=False), torch.bfloat16),
+    ("c3_bf16_D2048", dict(B=128, D=2048, H=512, V=10000, T=50, tf=True, ado=False), torch.bfloat16),
+    ("c5_bf16", dict(B=128, D=2048, H=768, V=30522, T=20, tf=False, ado=False, gate=False, bert=True, start_token=101), torch.bfloat16),
+]
+
+
+@pytest.mark.parametrize("name,cfg,dt", FULL, ids=[f[0] for f in FULL])
+def test_fused_train_step_full_size(name, cfg, dt):
+    """`FusedTrainStep.step` (forward + fused loss + backward; what bench.py times) at the configuration's full size."""
+    from sat_b200.trainer import FusedTrainStep
+    L = 196
+    fp32 = dt == torch.float32
+    P = synth.make_params(cfg["V"], cfg["D"], cfg["H"], ado=cfg["ado"], seed=42, emb_scale=0.5)
+    a, cap = synth.make_inputs(cfg["B"], L, cfg["D"], cfg["T"], cfg["V"], seed=42, start_token=cfg.get("start_token", 0))
+    masks = synth.make_dropout_masks(cfg["B"], cfg["T"], cfg["H"]).cuda()
+    a, cap = a.cuda(), cap.cuda()
+    dec = _make_decoder(cfg, P, dt).train()
+    tr = FusedTrainStep(dec, lr=1e-4, alpha_c=1.0, distributed=False)
+    loss = tr.step(a.to(dt), cap, dropout_mask=masks, optimizer_step=False)
+    torch.cuda.synchronize()
+    tr.check_status()
+    alphas = tr.alphas
+    feed = None
+    if not cfg["tf"]:
+        # tokens OUR run fed to each step: start token, then the greedy choice from our logits (decoder.py:132-133)
+        logits = tr.logits()
+        ours = logits.argmax(2)
+        feed = torch.cat((torch.full((cfg["B"], 1), cfg.get("start_token", 0), device="cuda", dtype=torch.long), ours[:, :-1]), 1)
+    pr, ar, loss_r, gr = _oracle_step(cfg, P, a, cap, masks, feed)
+    rec = {"case": name, "dtype": "fp32" if fp32 else "bf16", "loss": loss[2].item(), "loss_oracle": loss_r}
+    errs = []
+    rtol_loss = 2e-5 if fp32 else 3e-2
+    if abs(loss[2].item() - loss_r) > rtol_loss * abs(loss_r):
+        errs.append(f"loss {loss[2].item()} vs {loss_r}")
+    rowsum = (alphas.sum(2) - 1).abs().max().item()
+    rec["alpha_rowsum_err"] = rowsum
+    if rowsum >= 1e-5:
+        errs.append(f"alpha row sum off by {rowsum}")
+    da = (alphas - ar).abs().max().item()
+    rec["alpha_max_abs_err"] = da
+    if da > (2e-6 if fp32 else 4e-3):
+        errs.append(f"alphas max abs err {da}")
+    if not cfg["tf"]:
+        # our greedy token must be an argmax of the oracle's logits up to the logit tolerance
+        gap = (pr.max(2).values - pr.gather(2, ours.unsqueeze(2)).squeeze(2))[:, :-1].max().item()
+        rec["argmax_gap"] = gap
+        if gap > (1e-4 if fp32 else 6e-2):
+            errs.append(f"greedy token is not an argmax of the oracle logits: gap {gap}")
+        dl = (logits - pr).abs().max().item()
+        rec["logit_max_abs_err"] = dl
+        if dl > (2e-4 if fp32 else 8e-2):
+            errs.append(f"logits max abs err {dl}")
+    rec["grad_rel_l2"] = {}
+    bar = 2e-3 if fp32 else 5e-2
+    for k in tr.train_keys:
+        if k == "attention.v.bias":
+            continue                  # true gradient is 0 (softmax shift invariance): rounding noise on both sides
+        rel = _rel_l2(tr.grad_views[k], gr[k])
+        rec["grad_rel_l2"][k] = rel
+        if not rel <= bar:
+            errs.append(f"grad {k}: rel L2 {rel:.4f} > {bar}")
+    _log(rec)
+    assert not errs, (name, errs)
+
+
+@pytest.mark.parametrize("name,cfg,dt", [FULL[0], FULL[1], FULL[2], FULL[3]], ids=[f[0] for f in FULL[:4]])
+def test_decoder_forward_full_size(name, cfg, dt):
+    """`Decoder.forward` (the drop-in surface: preds + alphas through autograd) at c1 / c2 size, incl. d img_features."""
+    L = 196
+    fp32 = dt == torch.float32
+    P = synth.make_params(cfg["V"], cfg["D"], cfg["H"], ado=cfg["ado"], seed=7, emb_scale=0.5)
+    a, cap = synth.make_inputs(cfg["B"], L, cfg["D"], cfg["T"], cfg["V"], seed=7)
+    masks = synth.make_dropout_masks(cfg["B"], cfg["T"], cfg["H"]).cuda()
+    a, cap = a.cuda(), cap.cuda()
+    dec = _make_decoder(cfg, P, dt).train()
+    feats = a.clone().requires_grad_(True)
+    preds, alphas = dec(feats, cap, dropout_masks=masks)
+    O.train_loss(preds, alphas, cap, 1.0).backward()
+    Pr = {k: v.cuda().clone().requires_grad_(True) for k, v in P.items()}
+    ar_in = a.clone().requires_grad_(True)
+    pr, ar = O.decoder_forward(Pr, ar_in, cap, tf=True, ado=cfg["ado"], attention=True, dropout_masks=masks)
+    O.train_loss(pr, ar, cap, 1.0).backward()
+    errs = []
+    rec = {"case": name + "_forward", "dtype": "fp32" if fp32 else "bf16"}
+    dl = (preds - pr).abs().max().item()
+    scale = pr.abs().max().item()
+    rec["logit_max_abs_err"], rec["logit_scale"] = dl, scale
+    if dl > (2e-4 if fp32 else 3e-2) * max(1.0, scale):
+        errs.append(f"logits max abs err {dl} (scale {scale})")
+    rowsum = (alphas.sum(2) - 1).abs().max().item()
+    rec["alpha_rowsum_err"] = rowsum
+    if rowsum >= 1e-5:
+        errs.append(f"alpha row sum off by {rowsum}")
+    bar = 2e-3 if fp32 else 5e-2
+    rel = _rel_l2(feats.grad, ar_in.grad)
+    rec["dfeat_rel_l2"] = rel
+    if not rel <= bar:
+        errs.append(f"d img_features: rel L2 {rel:.4f} > {bar}")
+    rec["grad_rel_l2"] = {}
+    unused = dec.unused_parameter_keys()
+    for k, p in dec.named_parameters():
+        if k in unused:
+            if p.grad is not None:
+                errs.append(f"{k} should have grad None")
+            continue
+        if k == "attention.v.bias":
+            continue
+        r = _rel_l2(p.grad, Pr[k].grad)
+        rec["grad_rel_l2"][k] = r
+        if not r <= bar:
+            errs.append(f"grad {k}: rel L2 {r:.4f} > {bar}")
+    _log(rec)
+    assert not errs, (name, errs)
+
+
+@pytest.mark.parametrize("beam", [5, 10])
+def test_c4_beam_tokens_bit_exact_on_sample(beam):
+    """c4: 128 VGG-shaped images per GPU, beam 5 / 10, fp32 mode; sentences of a 16-image sample must equal the oracle's
+    `caption` (decoder.py:160-269 restated) token for token; alphas within 1e-5."""
+    from sat_b200.decoder import Decoder
+    V, D, Hd, L, NI = 2531, 512, 512, 196, 128
+    P = synth.make_params(V, D, Hd, seed=21, emb_scale=0.5)
+    P["deep_output.bias"] = P["deep_output.bias"].clone()
+    P["deep_output.bias"][1] += 0.25            # random weights never emit <eos> (Q18): lengths of a few tokens, beams shrink
+    a, _ = synth.make_inputs(NI, L, D, 4, V, seed=21)
+    dec = Decoder(V, D, tf=False, ado=False, bert=False, attention=True, compute_dtype=torch.float32)
+    dec.load_state_dict(P)
+    dec = dec.cuda().eval()
+    res = dec.caption_batch(a.cuda(), beam)
+    Pc = {k: v.cuda() for k, v in P.items()}
+    sample = list(range(0, NI, 8))
+    n_done = 0
+    for i in sample:
+        with torch.no_grad():
+            sent, alpha, fallback = O.caption(Pc, a[i].cuda(), beam, ado=False, attention=True)
+        got_s, got_a = res[i]
+        assert got_s == sent, (i, got_s, sent)
+        if fallback:
+            torch.testing.assert_close(got_a.cpu(), alpha.cpu(), rtol=1e-4, atol=1e-6)
+        else:
+            n_done += 1
+            torch.testing.assert_close(torch.tensor(got_a), torch.tensor(alpha), rtol=1e-4, atol=1e-6)
+    _log({"case": f"c4_beam{beam}", "images": NI, "sample": len(sample), "completed_in_sample": n_done})
+    assert n_done > 0
