@@ -65,6 +65,10 @@ int sat_set_gemm_splitk(int max_split);
  * in the 126 MB L2 from one forward step to the next (measured -13% on the forward kernel at c2; the backward kernel is
  * fastest with everything evict_first). */
 int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes);
+/* tuning knob: the producers of the streaming attention kernels ask L2 (cp.async.bulk.prefetch.L2) for the slot they will load
+ * `slots` slots later (per CTA; 0 = off), forward / backward kernel separately: bytes in flight beyond what the shared-memory
+ * ring can hold. */
+int sat_set_attn_prefetch(int fwd_slots, int bwd_slots);
 
 /* Bench instrumentation: CUDA-event pairs around every attention-step (fwd = category 0, bwd = 1) and GEMM (2) launch,
  * recorded on the launching stream.  sat_profile_read fills ms[3] / counts[3] and resets. */

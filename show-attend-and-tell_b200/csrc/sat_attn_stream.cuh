@@ -24,6 +24,7 @@
 extern int g_attn_generic;     // debug knob (sat_set_attn_generic): 1 = always use the generic cluster kernels
 extern int g_attn_wa_hint_fwd, g_attn_wa_hint_bwd;   // L2 policy of the Wa rows, see Part
 extern long long g_attn_pin_bytes;   // bytes of a / Wa per launch loaded with the L2 evict_last hint
+extern int g_attn_pf_fwd, g_attn_pf_bwd;   // tuning knob (sat_set_attn_prefetch): L2 prefetch distance of the producers, in slots per CTA
 extern int g_attn_part;        // debug knob (sat_set_attn_partition): 0 = auto, 1 = whole items, 2 = equal slot counts
 
 namespace attn_s {
@@ -65,7 +66,7 @@ __device__ __forceinline__ float4 ldcg4(const float* p) { return __ldcg(reinterp
 // the first `pin` slots of every item are loaded with the L2 evict_last hint (kept for the next step's kernels, which
 // read the same a / Wa), the rest with evict_first -- the same fraction of every CTA's range whatever the partition
 // wa_hint: L2 policy of the Wa rows (0 = like the rest of the slot, 1 = evict_last, 2 = evict_normal)
-struct Part { long long tot; int align; int pin; int wa_hint; };
+struct Part { long long tot; int align; int pin; int wa_hint; int pf; };     // pf: L2 prefetch distance in slots (0 = off)
 __host__ __device__ __forceinline__ long long pstart(const Part& pt, int G, int i) { return (pt.tot / pt.align) * i / G * pt.align; }
 __device__ __forceinline__ int cta_of(const Part& pt, int G, long long slot) {
     int i = (int)(slot * G / pt.tot);
@@ -113,7 +114,7 @@ inline Smem make_smem(int slot_bytes, size_t red_bytes, size_t es_bytes, size_t 
 // one producer and one consumer, neither of which can run a whole phase ahead of the barrier it waits on (the parity wait
 // would otherwise pass on stale data).
 template <typename T, int D, int H, typename SideFn>
-__device__ __forceinline__ void produce(int pidx, bool static_inputs, const void* wa, const void* a, int L, int ngroups, long long q0, long long q1, int pin, int wa_hint, int spi,
+__device__ __forceinline__ void produce(int pidx, bool static_inputs, const void* wa, const void* a, int L, int ngroups, long long q0, long long q1, int pin, int wa_hint, int pf, int spi,
                                         uint8_t* ring, uint64_t* full, uint64_t* empty, int nslots, uint64_t* sfull,
                                         uint64_t* sempty, SideFn side) {
     using G = Geo<T, D, H>;
@@ -152,6 +153,23 @@ __device__ __forceinline__ void produce(int pidx, bool static_inputs, const void
     bool waited = !static_inputs;
     if (!static_inputs) pdl_wait();
     const int prefill = (int)((endc - basec) >> 3) + (int)((endn - basen) >> 3);
+    // L2 prefetch-ahead.  The ring (all the shared memory there is: ~16 slots = 160 KB per SM) bounds the bytes a CTA has in
+    // flight, and with it the per-SM stream rate at HBM latency (ncu r2: both streaming kernels pull ~4 TB/s from DRAM while
+    // their consumers wait for data 60 % of the time).  Requests that only have to reach L2 cost no shared memory: every
+    // producer asks L2 for the slot it will load `pf` slots from now, so the later cp.async.bulk finds its lines in L2
+    // (or already on their way) and the ring turns over at L2 latency instead of DRAM latency.
+    const int pfd = (pf / PWARPS) * PWARPS;          // keep the prefetched slot in this producer's own sequence
+    auto prefetch_slot = [&](long long q) {
+        const long long it = q / spi;
+        const int kk = (int)(q - it * spi);
+        const long long im = it / ngroups;
+        if (ngroups > 1 && it - im * ngroups != 0) return;          // beam groups re-read the image: prefetch it once
+        const int l0 = kk * LS, nloc = min(LS, L - l0);
+        l2_prefetch_bulk(reinterpret_cast<const T*>(wa) + ((size_t)im * L + l0) * H, (uint32_t)(nloc * H * sizeof(T)));
+        l2_prefetch_bulk(reinterpret_cast<const T*>(a) + ((size_t)im * L + l0) * D, (uint32_t)(nloc * D * sizeof(T)));
+    };
+    if (pfd > 0 && static_inputs)
+        for (long long q = q0 + pidx + prefill * PWARPS; q < q1 && q < q0 + pidx + pfd; q += PWARPS) prefetch_slot(q);
     int issued = 0;
     for (long long q = q0 + pidx; q < q1; q += PWARPS, ++issued) {
         if (pidx == 0 && (waited || issued >= prefill)) {
@@ -167,6 +185,7 @@ __device__ __forceinline__ void produce(int pidx, bool static_inputs, const void
         bulk_g2s_hint(dst, reinterpret_cast<const T*>(wa) + ((size_t)img * L + l0) * H, (uint32_t)(nloc * H * sizeof(T)), &full[rr],
                       wa_hint == 1 ? L2_EVICT_LAST : (wa_hint == 2 ? L2_EVICT_NORMAL : pol));
         bulk_g2s_hint(dst + LS * H * sizeof(T), reinterpret_cast<const T*>(a) + ((size_t)img * L + l0) * D, (uint32_t)(nloc * D * sizeof(T)), &full[rr], pol);
+        if (pfd > 0 && q + pfd < q1 && (waited || static_inputs)) prefetch_slot(q + pfd);
         rc += CWARPS;
         if (rc >= endc) { rc = basec; phc ^= 1; }
         { uint32_t t; t = rc; rc = rn; rn = t; t = phc; phc = phn; phn = t; t = basec; basec = basen; basen = t; t = endc; endc = endn; endn = t; }
@@ -497,7 +516,7 @@ fwd_stream_kernel(FwdParams p, Smem sl, Part pt, int ngroups) {
                     bulk_g2s(side + (size_t)sb * SIDE_F + (size_t)nb * (H + D), p.uf + row * p.ld_uf, (uint32_t)((H + D) * 4), bar);
                 }
             };
-            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, ngroups, q0, q1, pt.pin, pt.wa_hint, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
+            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, ngroups, q0, q1, pt.pin, pt.wa_hint, pt.pf, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
         }
     }
 }
@@ -821,7 +840,7 @@ bwd_stream_kernel(BwdParams p, Smem sl, Part pt) {
                 bulk_g2s(dst + D, p.ctx32 + b * p.ld_c32, (uint32_t)(D * 4), bar);
                 bulk_g2s(dst + 2 * D, p.uf + b * p.ld_uf, (uint32_t)(H * 4), bar);
             };
-            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, 1, q0, q1, pt.pin, pt.wa_hint, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
+            produce<T, D, H>(warp - CWARPS, p.static_inputs != 0, p.wa, p.a, L, 1, q0, q1, pt.pin, pt.wa_hint, pt.pf, spi, ring, full, empty, nslots, sfull, sempty, side_fn);
         }
     }
 }
@@ -894,6 +913,7 @@ inline Part pick_part(long long nitems, int spi, int slot_bytes, int ngroups, bo
     // beam groups of one image re-read the image inside the launch: count each image's bytes once
     const double total_bytes = (double)pt.tot * slot_bytes / ngroups;
     pt.wa_hint = bwd ? g_attn_wa_hint_bwd : g_attn_wa_hint_fwd;
+    pt.pf = bwd ? g_attn_pf_bwd : g_attn_pf_fwd;
     pt.pin = (double)g_attn_pin_bytes >= total_bytes ? spi : (int)(spi * ((double)g_attn_pin_bytes / total_bytes));
     bool whole = g_attn_part == 1 || (g_attn_part == 0 && nitems * 4 >= (long long)sms);
     // a capped grid that the items do not fill evenly would leave some CTAs a whole item more than others

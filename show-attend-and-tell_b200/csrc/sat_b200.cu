@@ -7,6 +7,7 @@ int g_force_simt = 0;
 int g_gemm_static_b = 1;     // in-loop GEMMs: weights loaded with evict_last and requested before the PDL wait
 int g_attn_generic = 0;
 int g_attn_part = 0;
+int g_attn_pf_fwd = 0, g_attn_pf_bwd = 0;   // L2 prefetch distance of the streaming attention producers (slots per CTA)
 long long g_attn_pin_bytes = 0;
 int g_attn_wa_hint_fwd = 1, g_attn_wa_hint_bwd = 0;
 int g_pdl = 1;
@@ -103,6 +104,9 @@ int sat_gemm_phase_stamps(int on, unsigned long long* out) {
 int sat_set_decoder_split(int on) { g_dec_split = on ? 1 : 0; g_split_chain = on == 2 ? 0 : 1; return SAT_OK; }
 int sat_set_decoder_split_sms(int attn_ctas, int gemm_sms) {
     g_split_attn_ctas = attn_ctas > 0 ? attn_ctas : 0; g_split_gemm_sms = gemm_sms > 0 ? gemm_sms : 0; return SAT_OK;
+}
+int sat_set_attn_prefetch(int fwd_slots, int bwd_slots) {
+    g_attn_pf_fwd = fwd_slots > 0 ? fwd_slots : 0; g_attn_pf_bwd = bwd_slots > 0 ? bwd_slots : 0; return SAT_OK;
 }
 int sat_set_attn_partition(int mode) { g_attn_part = (mode == 1 || mode == 2) ? mode : 0; return SAT_OK; }
 

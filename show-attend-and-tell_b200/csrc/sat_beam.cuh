@@ -293,6 +293,14 @@ __global__ void beam_init_state_kernel(int* live, int* done, int* n_active, int*
     if (i < NI * beam) { top_preds[i] = 0.0f; prev_word[i] = start; }     // decoder.py:166-171
 }
 
+// one pinned int per host thread for the early-exit poll
+static inline int beam_host_flag(int** out) {
+    static thread_local int* flag = nullptr;
+    if (!flag) SAT_CHECK_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&flag), sizeof(int), cudaHostAllocPortable));
+    *out = flag;
+    return SAT_OK;
+}
+
 template <typename T>
 int beam_search_t(const sat_beam_args& a) {
     constexpr bool PRECISE = IsF32<T>::value;
@@ -408,11 +416,15 @@ int beam_search_t(const sat_beam_args& a) {
         beam::topk_step_kernel<<<NI, beam::TOPK_THREADS, topk_smem, st>>>(sp);
         beam::gather_state_kernel<T><<<R, 128, 0, st>>>(w.X, xw, H + D, w.Hn, w.Cc, w.Cn, w.parent, w.live, w.done, NB, H);
         SAT_CHECK_CUDA(cudaGetLastError());
-        if ((step % 4) == 0 && step < S) {     // early exit once every image has finished (no effect on results)
-            int active = 1;
-            SAT_CHECK_CUDA(cudaMemcpyAsync(&active, w.n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
+        if ((step % 8) == 0 && step < S) {     // early exit once every image has finished (no effect on results)
+            // pinned flag: a pageable destination costs ~90 us per copy (staging) on top of the pipeline drain; every 8 steps
+            // keeps the drain + refill (~0.1 ms) under 3 % of a 51-step search while a batch of short captions still stops early
+            int* active = nullptr;
+            SAT_TRY(beam_host_flag(&active));
+            *active = 1;
+            SAT_CHECK_CUDA(cudaMemcpyAsync(active, w.n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
             SAT_CHECK_CUDA(cudaStreamSynchronize(st));
-            if (active <= 0) break;
+            if (*active <= 0) break;
         }
     }
     beam::FinalParams fp;

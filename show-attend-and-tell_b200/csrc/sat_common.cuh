@@ -221,6 +221,10 @@ __device__ __forceinline__ void tma_load_2d_hint(void* smem_dst, const CUtensorM
 }
 // pull one 128-byte line into L2 without waiting for it
 __device__ __forceinline__ void l2_prefetch(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+// ask L2 for `bytes` (multiple of 16) starting at p, asynchronously, without a destination (TMA engine, no shared memory)
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }

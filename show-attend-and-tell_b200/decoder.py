@@ -284,9 +284,9 @@ class Decoder(nn.Module):
         return out[:, :H].contiguous(), out[:, H:].contiguous()
 
     # ------------------------------------------------------------------------------------------
-    def caption_batch(self, img_features, beam_size, max_steps=50):
-        """Extension: beam search for NI images at once; img_features is (NI, L, D), one row per image.
-        Returns a list of (sentence, alpha) pairs with the reference's per-image return convention."""
+    def caption_batch_raw(self, img_features, beam_size, max_steps=50):
+        """Batched beam search, device-side outputs only (no host sync): dict of lens / status / live (NI,) int32, tokens
+        (NI, max_steps+2) int64, alphas (NI, max_steps+2, L) fp32, last_alpha (NI, beam, L) fp32."""
         self._check_inputs(img_features)
         L = _lib.lib()
         dev = img_features.device
@@ -305,34 +305,47 @@ class Decoder(nn.Module):
         a.a_stride_b, a.a_stride_l, a.a_stride_d = img_features.stride()
         keep = _fill_params(a, self)
         maxlen = max_steps + 2
-        out_len = torch.zeros(NI, device=dev, dtype=torch.int32)
-        out_status = torch.zeros(NI, device=dev, dtype=torch.int32)
-        out_live = torch.zeros(NI, device=dev, dtype=torch.int32)
-        out_tokens = torch.zeros(NI, maxlen, device=dev, dtype=torch.int64)
-        out_alphas = torch.zeros(NI, maxlen, Lloc, device=dev, dtype=torch.float32)
-        out_last = torch.zeros(NI, beam_size, Lloc, device=dev, dtype=torch.float32)
-        a.out_len, a.out_status, a.out_tokens = out_len.data_ptr(), out_status.data_ptr(), out_tokens.data_ptr()
-        a.out_alphas, a.out_last_alpha, a.out_live = out_alphas.data_ptr(), out_last.data_ptr(), out_live.data_ptr()
-        nbytes = C.c_int64(0)
-        _lib.check(L.sat_beam_workspace_bytes(C.byref(a), C.byref(nbytes)), "sat_beam_workspace_bytes")
-        ws = torch.empty(nbytes.value + 256, device=dev, dtype=torch.uint8)
-        a.workspace = ws.data_ptr() + ((-ws.data_ptr()) % 256)
-        a.workspace_bytes = nbytes.value
-        a.stream = torch.cuda.current_stream(dev).cuda_stream
-        with torch.no_grad(), torch.cuda.device(dev):
+        with torch.cuda.device(dev):
+            out_len = torch.zeros(NI, device=dev, dtype=torch.int32)
+            out_status = torch.zeros(NI, device=dev, dtype=torch.int32)
+            out_live = torch.zeros(NI, device=dev, dtype=torch.int32)
+            out_tokens = torch.zeros(NI, maxlen, device=dev, dtype=torch.int64)
+            out_alphas = torch.zeros(NI, maxlen, Lloc, device=dev, dtype=torch.float32)
+            out_last = torch.zeros(NI, beam_size, Lloc, device=dev, dtype=torch.float32)
+            a.out_len, a.out_status, a.out_tokens = out_len.data_ptr(), out_status.data_ptr(), out_tokens.data_ptr()
+            a.out_alphas, a.out_last_alpha, a.out_live = out_alphas.data_ptr(), out_last.data_ptr(), out_live.data_ptr()
+            nbytes = C.c_int64(0)
+            _lib.check(L.sat_beam_workspace_bytes(C.byref(a), C.byref(nbytes)), "sat_beam_workspace_bytes")
+            ws = torch.empty(nbytes.value + 256, device=dev, dtype=torch.uint8)
+            a.workspace = ws.data_ptr() + ((-ws.data_ptr()) % 256)
+            a.workspace_bytes = nbytes.value
             a.stream = torch.cuda.current_stream(dev).cuda_stream
-            _lib.check(L.sat_beam_search(C.byref(a)), "sat_beam_search")
-        lens, status, live = out_len.cpu().tolist(), out_status.cpu().tolist(), out_live.cpu().tolist()
-        toks, alph = out_tokens.cpu(), out_alphas.cpu()
+            with torch.no_grad():
+                _lib.check(L.sat_beam_search(C.byref(a)), "sat_beam_search")
+        del keep
+        return {"lens": out_len, "status": out_status, "live": out_live, "tokens": out_tokens, "alphas": out_alphas,
+                "last_alpha": out_last}
+
+    @staticmethod
+    def results_from_raw(raw):
+        """Padded device outputs -> the reference's per-image return values: (list[int], list[list[float]]) for a completed
+        caption, ([0], Tensor(live, L)) for the "No completed sentences found" fallback (decoder.py:256-258, Q18)."""
+        lens, status, live = raw["lens"].cpu().tolist(), raw["status"].cpu().tolist(), raw["live"].cpu().tolist()
+        toks = raw["tokens"].cpu()
+        alph = raw["alphas"].cpu() if "alphas" in raw else None
         results = []
-        for i in range(NI):
-            if status[i] != 0:                                   # decoder.py:256-258 (Q18)
-                results.append(([0], out_last[i, :live[i]].clone()))
+        for i in range(len(lens)):
+            if status[i] != 0:
+                results.append(([0], raw["last_alpha"][i, :live[i]].clone() if "last_alpha" in raw else None))
             else:
                 n = lens[i]
-                results.append((toks[i, :n].tolist(), alph[i, :n].tolist()))
-        del keep
+                results.append((toks[i, :n].tolist(), alph[i, :n].tolist() if alph is not None else None))
         return results
+
+    def caption_batch(self, img_features, beam_size, max_steps=50):
+        """Extension: beam search for NI images at once; img_features is (NI, L, D), one row per image.
+        Returns a list of (sentence, alpha) pairs with the reference's per-image return convention."""
+        return self.results_from_raw(self.caption_batch_raw(img_features, beam_size, max_steps))
 
     def caption(self, img_features, beam_size):
         """decoder.py:160-269.  `img_features` is one image expanded to (beam, L, D) as in

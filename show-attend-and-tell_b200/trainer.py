@@ -158,9 +158,10 @@ class FusedTrainStep:
             a.workspace = self._ws.data_ptr() + ((-self._ws.data_ptr()) % 256)
             a.workspace_bytes = nbytes.value
             self._a = a
+            if self._ws_key is not None:
+                self._graphs.clear()      # captured graphs point into the old workspace
+                self._seen.clear()
             self._ws_key = key
-            self._graphs.clear()          # captured graphs point into the old workspace
-            self._seen.clear()
         a = self._a
         a.alpha_c = float(self.alpha_c)
         a.img_features = img_features.data_ptr()
@@ -183,11 +184,12 @@ class FusedTrainStep:
         cur = tuple(p.data_ptr() for p in named.values())
         if cur != self._ptr_sig:
             self._check_param_storage(cur)
+            if self._ptr_sig is not None:     # a (non-flat) parameter moved: graphs captured its old address
+                self._graphs.clear()
+                self._seen.clear()
             self._ptr_sig = cur
             self._ptr_list = [(field, None if named.get(_lib.PARAM_KEYS[field]) is None else named[_lib.PARAM_KEYS[field]].data_ptr())
                               for field in _lib.PARAM_FIELDS]
-            self._graphs.clear()
-            self._seen.clear()
         return self._ptr_list
 
     def sync_grads(self):

@@ -95,3 +95,81 @@ def test_two_rank_gloo_flat_gradient_exchange(attention, ado):
         p.join(timeout=60)
     for rank, msg in res:
         assert msg == "ok", f"rank {rank}: {msg}"
+
+
+def _worker_round2(rank, world, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from sat_b200 import sharded
+        from sat_b200.decoder import Decoder
+        from sat_b200.trainer import FusedTrainStep
+        # 1. replicas built from DIFFERENT seeds leave FusedTrainStep.__init__ with rank 0's weights (parameters were
+        #    never broadcast, a seed skew drifted silently), frozen / unused tensors included
+        torch.manual_seed(100 + rank)
+        dec = Decoder(40, 64, tf=True, ado=True, bert=False, attention=True)
+        before = dec.lstm.weight_ih.detach().clone()
+        tr = FusedTrainStep(dec)
+        flat = [torch.zeros_like(tr.flat_param) for _ in range(world)]
+        dist.all_gather(flat, tr.flat_param)
+        assert all(torch.equal(f, flat[0]) for f in flat)
+        if rank != 0:
+            assert not torch.equal(before, dec.lstm.weight_ih)
+        unused = [torch.zeros_like(dec.deep_output.weight) for _ in range(world)]      # ado: deep_output is outside the flat buffer (Q7)
+        dist.all_gather(unused, dec.deep_output.weight.data)
+        assert all(torch.equal(u, unused[0]) for u in unused)
+        assert abs(tr.hyper[5].item() - 1.0 / world) < 1e-9                            # the mean's 1/world rides in the Adam kernel
+        # a mismatching layout is refused on every rank
+        dec2 = Decoder(40, 64, tf=True, ado=(rank == 0), bert=False, attention=True)
+        try:
+            FusedTrainStep(dec2)
+            raise AssertionError("layout mismatch not detected")
+        except RuntimeError as e:
+            assert "layout differs" in str(e)
+        # 2. sharded beam search: unequal shards, padded gather on rank 0, image order = rank order
+        lo, hi = sharded.shard_range(7, rank, world)
+        assert (lo, hi) == ((0, 4) if rank == 0 else (4, 7))
+        n, maxlen, Lloc, beam = hi - lo, 6, 5, 3
+        raw = {"lens": torch.arange(lo, hi, dtype=torch.int32) % 4 + 2,
+               "status": torch.tensor([1 if (i % 3 == 2) else 0 for i in range(lo, hi)], dtype=torch.int32),
+               "live": torch.full((n,), 2, dtype=torch.int32),
+               "tokens": (torch.arange(lo, hi).view(n, 1) * 10 + torch.arange(maxlen).view(1, maxlen)).to(torch.int64),
+               "alphas": torch.arange(lo, hi, dtype=torch.float32).view(n, 1, 1).expand(n, maxlen, Lloc).contiguous(),
+               "last_alpha": torch.arange(lo, hi, dtype=torch.float32).view(n, 1, 1).expand(n, beam, Lloc).contiguous() + 0.5}
+        got = sharded.gather_caption_results(raw, dst=0)
+        if rank == 0:
+            res = Decoder.results_from_raw(got)
+            assert len(res) == 7
+            for i, (sent, alpha) in enumerate(res):
+                if i % 3 == 2:                       # fallback (decoder.py:256-258): ([0], Tensor(live, L))
+                    assert sent == [0] and torch.is_tensor(alpha) and alpha.shape == (2, Lloc) and alpha[0, 0].item() == i + 0.5
+                else:
+                    assert sent == [i * 10 + j for j in range(i % 4 + 2)]
+                    assert len(alpha) == len(sent) and alpha[0][0] == float(i)
+            tok_only = sharded.gather_caption_results(raw, dst=0, with_alphas=False)
+            assert "alphas" not in tok_only and tok_only["tokens"].shape == (7, maxlen)
+        else:
+            assert got is None
+            assert sharded.gather_caption_results(raw, dst=0, with_alphas=False) is None
+        q.put((rank, "ok"))
+    except Exception as e:                            # pragma: no cover - reported to the parent
+        import traceback
+        q.put((rank, traceback.format_exc() or repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gloo_replica_sync_and_sharded_caption_gather():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_round2, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in res:
+        assert msg == "ok", f"rank {rank}: {msg}"

@@ -82,6 +82,7 @@ def test_fused_train_step_full_size(name, cfg, dt):
     a, cap = a.cuda(), cap.cuda()
     dec = _make_decoder(cfg, P, dt).train()
     tr = FusedTrainStep(dec, lr=1e-4, alpha_c=1.0, distributed=False)
+    a = a.to(dt).float()          # features are GIVEN in the compute dtype; kernels and oracle see the same values
     loss = tr.step(a.to(dt), cap, dropout_mask=masks, optimizer_step=False)
     torch.cuda.synchronize()
     tr.check_status()
@@ -139,6 +140,7 @@ def test_decoder_forward_full_size(name, cfg, dt):
     masks = synth.make_dropout_masks(cfg["B"], cfg["T"], cfg["H"]).cuda()
     a, cap = a.cuda(), cap.cuda()
     dec = _make_decoder(cfg, P, dt).train()
+    a = a.to(dt).float()          # features are GIVEN in the compute dtype; kernels and oracle see the same values
     feats = a.clone().requires_grad_(True)
     preds, alphas = dec(feats, cap, dropout_masks=masks)
     O.train_loss(preds, alphas, cap, 1.0).backward()

@@ -49,6 +49,10 @@ def test_img_features_gradient_vs_oracle(case, dt):
     O.train_loss(preds, alphas, cap.cuda()).backward()
     Pr = {k: v.clone().requires_grad_(True) for k, v in P.items()}
     ar_in = a.clone().requires_grad_(True)
+    if dt != torch.float32:
+        # the library casts fp32 features to the compute dtype once (Q20 hand-off); that input quantisation is part of the
+        # bf16 mode's definition, not kernel error: the oracle differentiates through the same rounded features
+        ar_in = a.to(dt).float().requires_grad_(True)
     pr, ar = O.decoder_forward(Pr, ar_in, cap, tf=cfg.get("tf", True), ado=cfg.get("ado", False),
                                attention=cfg.get("attention", True), gate=cfg.get("gate", True))
     O.train_loss(pr, ar, cap).backward()
@@ -178,7 +182,7 @@ def test_sequence_accuracy_ties_and_nan():
     row = torch.zeros(1, 1, V, device="cuda")
     row[0, 0, [10, 20, 30]] = torch.tensor([3.0, 2.0, 1.0], device="cuda")
     assert metrics.logit_rank(row, torch.tensor([[0]], device="cuda")).item() == 3        # after the three positives
-    assert metrics.logit_rank(row, torch.tensor([[40]], device="cuda")).item() == 3 + 38  # zeros with a lower id come first
+    assert metrics.logit_rank(row, torch.tensor([[40]], device="cuda")).item() == 3 + 37  # + the 37 zeros with a lower id
     # NaN target logit / NaN row: never correct
     nan = torch.full((1, 1, V), float("nan"), device="cuda")
     assert metrics.logit_rank(nan, torch.tensor([[5]], device="cuda")).item() == V
@@ -267,7 +271,8 @@ def test_graph_step_draws_fresh_dropout_masks():
     dec.load_state_dict(P)
     dec = dec.cuda().train()
     tr = FusedTrainStep(dec, lr=0.0, distributed=False, use_cuda_graph=True)       # lr 0: weights fixed, only the mask changes
-    vals = [tr.step(a.cuda(), cap.cuda())[0].item() for _ in range(6)]
+    ad, capd = a.cuda(), cap.cuda()                                # fixed device buffers: the graph is tied to their addresses
+    vals = [tr.step(ad, capd)[0].item() for _ in range(6)]
     assert tr.graph_replays == 4
     assert len({round(v, 6) for v in vals[2:]}) > 1, vals       # replays see different masks
 

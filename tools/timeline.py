@@ -45,7 +45,7 @@ def main():
     evs.sort(key=lambda e: e.time_range.start)
     # second step only (the first absorbs the profiler's start-up)
     names = [e.name for e in evs]
-    adam = [i for i, n in enumerate(names) if "adam" in n.lower()]
+    adam = [i for i, n in enumerate(names) if "adam_tick" in n.lower()]
     if len(adam) >= 2:
         evs = evs[adam[0] + 1:adam[1] + 1]
     t0 = evs[0].time_range.start
