@@ -27,8 +27,39 @@ Params = Dict[str, torch.Tensor]
 # ----------------------------------------------------------------------------
 # primitive layers
 # ----------------------------------------------------------------------------
-def _linear(P: Params, name: str, x: torch.Tensor) -> torch.Tensor:
+# Optional emulation of the CUDA path's STORAGE precision (bf16 mode): every tensor the kernels keep in bf16 -- GEMM
+# operands (activations and packed weights), Wa, P1 / P2 / comb of the advanced deep output -- is rounded to bf16 at
+# the same points, with a straight-through gradient; all arithmetic stays fp32.  The reference itself has no such mode
+# (it is fp32 only); this exists because a bf16 run cannot be compared tightly with fp32 THROUGH ReLUs: a pre-activation
+# within rounding noise of zero flips its mask and changes a whole gradient row.  With the rounding points aligned the masks
+# agree and the comparison measures the kernels, not the quantisation.  Used by tests only (`with O.emulate_storage(...)`).
+_STORAGE_DTYPE = None
+
+
+class emulate_storage:
+    def __init__(self, dtype):
+        self.dtype = dtype
+
+    def __enter__(self):
+        global _STORAGE_DTYPE
+        self.prev, _STORAGE_DTYPE = _STORAGE_DTYPE, self.dtype
+        return self
+
+    def __exit__(self, *exc):
+        global _STORAGE_DTYPE
+        _STORAGE_DTYPE = self.prev
+
+
+def _q(x: torch.Tensor) -> torch.Tensor:
+    if _STORAGE_DTYPE is None or _STORAGE_DTYPE == torch.float32:
+        return x
+    return x + (x.detach().to(_STORAGE_DTYPE).to(x.dtype) - x.detach())
+
+
+def _linear(P: Params, name: str, x: torch.Tensor, quant: bool = True) -> torch.Tensor:
     """nn.Linear: y = x W^T + b."""
+    if quant:
+        return _q(x) @ _q(P[name + ".weight"]).t() + P[name + ".bias"]
     return x @ P[name + ".weight"].t() + P[name + ".bias"]
 
 
@@ -36,9 +67,9 @@ def attention_forward(P: Params, a: torch.Tensor, h: torch.Tensor):
     """attention.py:14-21.  NOTE the naming swap: `attention.U` acts on
     the hidden state, `attention.W` on the image features."""
     U_h = _linear(P, "attention.U", h).unsqueeze(1)            # attention.py:15
-    W_s = _linear(P, "attention.W", a)                         # attention.py:16
+    W_s = _q(_linear(P, "attention.W", a))                     # attention.py:16
     att = torch.tanh(W_s + U_h)                                # attention.py:17
-    e = _linear(P, "attention.v", att).squeeze(2)              # attention.py:18
+    e = _linear(P, "attention.v", att, quant=False).squeeze(2)  # attention.py:18 (fp32 in the kernels)
     alpha = torch.softmax(e, dim=1)                            # attention.py:19
     context = (a * alpha.unsqueeze(2)).sum(1)                  # attention.py:20
     return context, alpha
@@ -54,7 +85,7 @@ def init_lstm_state(P: Params, a: torch.Tensor):
 
 def lstm_cell(P: Params, x: torch.Tensor, h: torch.Tensor, c: torch.Tensor):
     """nn.LSTMCell used at decoder.py:115 / :197; gate order i,f,g,o."""
-    g = x @ P["lstm.weight_ih"].t() + P["lstm.bias_ih"] + h @ P["lstm.weight_hh"].t() + P["lstm.bias_hh"]
+    g = _q(x) @ _q(P["lstm.weight_ih"]).t() + P["lstm.bias_ih"] + _q(h) @ _q(P["lstm.weight_hh"]).t() + P["lstm.bias_hh"]
     i, f, gg, o = g.chunk(4, dim=1)
     c2 = torch.sigmoid(f) * c + torch.sigmoid(i) * torch.tanh(gg)
     h2 = torch.sigmoid(o) * torch.tanh(c2)
@@ -63,9 +94,9 @@ def lstm_cell(P: Params, x: torch.Tensor, h: torch.Tensor, c: torch.Tensor):
 
 def advanced_deep_output(P: Params, h, context, emb):
     """decoder.py:149-158 (un-gated context, final ReLU on the logits: SURVEY Q8)."""
-    h_t = torch.relu(_linear(P, "f_h", h))
-    z_t = torch.relu(_linear(P, "f_z", context))
-    return torch.relu(_linear(P, "f_out", h_t + z_t + emb))
+    h_t = _q(torch.relu(_linear(P, "f_h", h)))
+    z_t = _q(torch.relu(_linear(P, "f_z", context)))
+    return torch.relu(_linear(P, "f_out", h_t + z_t + _q(emb)))
 
 
 def _step(P: Params, a, h, c, emb, *, attention: bool, gate: bool = True):

@@ -7,7 +7,9 @@ int g_force_simt = 0;
 int g_gemm_static_b = 1;     // in-loop GEMMs: weights loaded with evict_last and requested before the PDL wait
 int g_attn_generic = 0;
 int g_attn_part = 0;
-int g_attn_pf_fwd = 0, g_attn_pf_bwd = 0;   // L2 prefetch distance of the streaming attention producers (slots per CTA)
+int g_attn_pf_fwd = 0, g_attn_pf_bwd = 8;   // L2 prefetch distance of the streaming attention producers (slots per CTA).  Measured at c2
+                                            // (tools/ab_step.py, profiles/r2_ab_attention_knobs.txt): backward 8 slots ahead = -4.5 % per
+                                            // train step (bwd kernel 73 -> 66 us); any forward prefetch is slower (its Wa rows are L2-pinned)
 long long g_attn_pin_bytes = 0;
 int g_attn_wa_hint_fwd = 1, g_attn_wa_hint_bwd = 0;
 int g_pdl = 1;

