@@ -102,6 +102,21 @@ int sat_attn_step_fwd(int dtype, int NI, int NB, int L, int D, int H, const void
  * ctx_f32 (optional, streaming only) receives the fp32 un-gated context the streaming backward needs. */
 int sat_attn_scratch_bytes(int NI, int NB, int L, int D, int H, int64_t* bytes);
 
+/* No counterpart in the reference: added for callers that cannot allocate device memory
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  sat_attn_step_fwd with the scratch of
+ * the streaming kernels taken from a file-scope `static __device__` array of SAT_STATIC_SCRATCH_BYTES inside the library (every GPU
+ * that loads the library holds it until the process exits) instead of a caller-owned buffer; inputs and outputs are still the
+ * caller's.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).  Limits: only shapes the
+ * streaming kernels serve (D in {512, 2048}, H in {512, 768}, L <= 1024, NB > 1 only with D = 512) and only while
+ * sat_attn_scratch_bytes(NI, NB, L, D, H) <= SAT_STATIC_SCRATCH_BYTES (e.g. NI <= ~200 at D = 2048, ~1400 at D = 512, NB = 1);
+ * anything else returns an error that says so.  ALL calls on a device share the one array, which keeps the previous call's
+ * contents (nothing in it has to start at zero): calls that overlap on the GPU -- two streams, two host threads -- race; calls
+ * ordered on one stream are safe. */
+#define SAT_STATIC_SCRATCH_BYTES (4 * 1024 * 1024)
+int sat_attn_step_fwd_static(int dtype, int NI, int NB, int L, int D, int H, const void* a, const void* wa, const float* uf,
+                             int64_t ld_uf, const float* v, const float* bv, int gate, float* alpha, int64_t ld_alpha,
+                             void* ctx, int64_t ld_ctx, void* z, int64_t ld_z, float* ctx_f32, int64_t ld_c32, void* stream);
+
 /* K2 backward (autograd of the lines above inside loss.backward(), train.py:163).
  * The gradient wrt the hoisted projection Wa is produced in one of two ways: dpre_out != NULL -> this step's
  * dpre (B,L,H) is written once in the compute dtype (streaming kernel; the caller sums the steps afterwards);

@@ -205,6 +205,51 @@ int sat_attn_step_fwd(int dtype, int NI, int NB, int L, int D, int H, const void
     return SAT_ERR_ARG;
 }
 
+// ---- no-allocation variant of the attention step (requested by the run's operators; no counterpart in the reference) --------
+// The streaming attention kernels need a scratch buffer for the partial records of images the work partition cuts.  Callers that
+// cannot allocate (CUDA-graph capture, tight serving loops) get it from this file-scope array instead: SAT_STATIC_SCRATCH_BYTES
+// of device memory on every GPU that loads the library, held until the process exits.  In host code the array's NAME is only a
+// host-side stand-in, not a device address -- its device address is taken once per device with cudaGetSymbolAddress.
+static __device__ __align__(256) unsigned char g_static_attn_scratch[SAT_STATIC_SCRATCH_BYTES];
+
+static int static_attn_scratch(void** out) {
+    static void* ptr[64];
+    static SatPerDevice resolved;
+    int dev = 0;
+    SAT_CHECK_CUDA(cudaGetDevice(&dev));
+    SAT_REQUIRE(dev >= 0 && dev < 64, "device index %d out of range", dev);
+    SAT_TRY(resolved.once([&]() -> int {          // once per device, with that device current
+        void* p = nullptr;
+        SAT_CHECK_CUDA(cudaGetSymbolAddress(&p, g_static_attn_scratch));
+        SAT_REQUIRE(p != nullptr && ((uintptr_t)p & 255) == 0, "static scratch: bad device address %p", p);
+        ptr[dev] = p;
+        return SAT_OK;
+    }));
+    *out = ptr[dev];
+    return SAT_OK;
+}
+
+int sat_attn_step_fwd_static(int dtype, int NI, int NB, int L, int D, int H, const void* a, const void* wa, const float* uf,
+                             int64_t ld_uf, const float* v, const float* bv, int gate, float* alpha, int64_t ld_alpha,
+                             void* ctx, int64_t ld_ctx, void* z, int64_t ld_z, float* ctx_f32, int64_t ld_c32, void* stream) {
+    SAT_TRY(require_sm100());
+    SAT_REQUIRE(NI > 0 && NB > 0 && L > 0 && D > 0 && H > 0, "sat_attn_step_fwd_static: bad dims");
+    SAT_REQUIRE(attn_s::fwd_shape_ok(NB, L, D, H),
+                "sat_attn_step_fwd_static: shape (NB=%d, L=%d, D=%d, H=%d) is not served by the streaming kernels (D in {512, 2048}, "
+                "H in {512, 768}, L <= 1024, NB > 1 only with D = 512); it needs no scratch -- call sat_attn_step_fwd with scratch = NULL",
+                NB, L, D, H);
+    const int64_t need = attn_s::scratch_bytes(NI, NB, D, H);
+    SAT_REQUIRE(need <= (int64_t)SAT_STATIC_SCRATCH_BYTES,
+                "sat_attn_step_fwd_static: NI=%d NB=%d D=%d H=%d needs %lld bytes of scratch, the static buffer holds %lld "
+                "(SAT_STATIC_SCRATCH_BYTES); use sat_attn_step_fwd with a caller-owned buffer", NI, NB, D, H, (long long)need,
+                (long long)SAT_STATIC_SCRATCH_BYTES);
+    void* scratch = nullptr;
+    SAT_TRY(static_attn_scratch(&scratch));
+    // nothing in the scratch has to start at zero: every partial record is written by this launch before its combine kernel reads it
+    return sat_attn_step_fwd(dtype, NI, NB, L, D, H, a, wa, uf, ld_uf, v, bv, gate, alpha, ld_alpha, ctx, ld_ctx, z, ld_z, ctx_f32,
+                             ld_c32, scratch, (int64_t)SAT_STATIC_SCRATCH_BYTES, stream);
+}
+
 int sat_attn_step_bwd(int dtype, int B, int L, int D, int H, const void* a, const void* wa, const float* uf, int64_t ld_uf,
                       const float* v, const float* alpha, int64_t ld_alpha, const void* ctx, int64_t ld_ctx,
                       const float* dz, int64_t ld_dz, const float* dctx_extra, int64_t ld_dce, const float* galpha,
