@@ -27,6 +27,10 @@ const char* sat_last_error(void);
 int sat_version(void);
 /* debug knob: 1 = run bf16 GEMMs on the SIMT kernel (bring-up cross-check of the tcgen05 kernel) */
 int sat_set_force_simt(int on);
+/* fp32 compute mode: 1 (default) = GEMMs whose operands are both K-major (every forward GEMM, beam search included) run on the
+ * tensor cores as 3xTF32 -- each fp32 operand split into tf32 hi + lo, three tcgen05.mma.kind::tf32 per k-step into one fp32 TMEM
+ * accumulator: within a few fp32 ulps of an exact-fp32 dot product; 0 = the true-fp32 SIMT FMA kernel always */
+int sat_set_fp32_gemm_mode(int mode);
 /* debug knob: 1 = run the attention step on the generic cluster kernels even where the streaming kernels apply */
 int sat_set_attn_generic(int on);
 /* debug knob: work partition of the streaming attention kernels. 0 = auto, 1 = whole items per CTA, 2 = equal slot counts */

@@ -92,11 +92,13 @@ def lstm_cell(P: Params, x: torch.Tensor, h: torch.Tensor, c: torch.Tensor):
     return h2, c2
 
 
-def advanced_deep_output(P: Params, h, context, emb):
-    """decoder.py:149-158 (un-gated context, final ReLU on the logits: SURVEY Q8)."""
+def advanced_deep_output(P: Params, h, context, emb, out_mask=None):
+    """decoder.py:149-158 (un-gated context, final ReLU on the logits: SURVEY Q8).  `out_mask` (tests only): use this 0/1
+    mask in place of the final ReLU's own (logit > 0) -- the teacher-style check for the ReLU, see decoder_forward."""
     h_t = _q(torch.relu(_linear(P, "f_h", h)))
     z_t = _q(torch.relu(_linear(P, "f_z", context)))
-    return torch.relu(_linear(P, "f_out", h_t + z_t + _q(emb)))
+    pre = _linear(P, "f_out", h_t + z_t + _q(emb))
+    return torch.relu(pre) if out_mask is None else pre * out_mask
 
 
 def _step(P: Params, a, h, c, emb, *, attention: bool, gate: bool = True):
@@ -120,13 +122,18 @@ def _step(P: Params, a, h, c, emb, *, attention: bool, gate: bool = True):
 
 def decoder_forward(P: Params, a: torch.Tensor, captions: torch.Tensor, *, tf: bool, ado: bool,
                     attention: bool, gate: bool = True, start_token: int = 0,
-                    dropout_masks: Optional[torch.Tensor] = None, feed_tokens: Optional[torch.Tensor] = None):
+                    dropout_masks: Optional[torch.Tensor] = None, feed_tokens: Optional[torch.Tensor] = None,
+                    relu_masks: Optional[torch.Tensor] = None):
     """decoder.py:69-135.  `dropout_masks` (B,T,H) holds the *scaled* keep mask
     (0 or 1/(1-p)) applied to h before the output layer (decoder.py:121-125);
     None means eval mode (identity).  Tensors are created on `a.device`, so the same restatement runs on the GPU
     for the full-size parity tests.  `feed_tokens` (B,T), free-running mode only: feed these ids as step inputs
     instead of this function's own argmax (decoder.py:132) -- the teacher-style check of SURVEY 7.2: a bf16 run's
-    near-tie argmax may legitimately differ from the fp32 one, after which the two trajectories are incomparable."""
+    near-tie argmax may legitimately differ from the fp32 one, after which the two trajectories are incomparable.
+    `relu_masks` (B,T,V) bool, advanced deep output only: the same idea for the final ReLU on the V logits (decoder.py:158) --
+    the run under test says which logits it saw as positive.  A logit within bf16 noise of zero flips its mask; with V logits
+    per row a fraction f of flipped masks moves a gradient by ~sqrt(f) in relative L2 (0.3 % of flips -> 5 %), which says
+    nothing about the kernels."""
     B = a.shape[0]
     h, c = init_lstm_state(P, a)                                            # decoder.py:74
     T = captions.shape[1] - 1                                               # decoder.py:77
@@ -143,7 +150,8 @@ def decoder_forward(P: Params, a: torch.Tensor, captions: torch.Tensor, *, tf: b
         h, c, context, alpha = _step(P, a, h, c, emb, attention=attention, gate=gate)
         hd = h if dropout_masks is None else h * dropout_masks[:, t]
         if ado:
-            out = advanced_deep_output(P, hd, context, emb)                 # decoder.py:118-123
+            out = advanced_deep_output(P, hd, context, emb,                 # decoder.py:118-123
+                                       None if relu_masks is None else relu_masks[:, t].to(a.dtype))
         else:
             out = _linear(P, "deep_output", hd)                             # decoder.py:125
         preds[:, t] = out                                                   # decoder.py:127

@@ -7,6 +7,7 @@
 #include "sat_epilogue.cuh"
 #include "sat_gemm_simt.cuh"
 #include "sat_gemm_tc.cuh"
+#include "sat_gemm_tf32.cuh"
 #include "sat_attn_stream.cuh"
 #include "sat_misc.cuh"
 
@@ -28,6 +29,9 @@ int gemm(cudaStream_t s, const T* A, int64_t lda, bool a_k, const T* B, int64_t 
          const Epi& epi, int bn = 0, int sm_budget = 0, int b_static = 0) {
     SatProfScope prof(SAT_PROF_GEMM, s);
     if constexpr (IsF32<T>::value) {
+        // fp32 mode: forward-shaped GEMMs (both operands K-major) run on the tensor cores as 3xTF32 (fp32-accurate, see
+        // sat_gemm_tf32.cuh); transposed-operand (gradient) GEMMs and tiny ones stay on the true-fp32 SIMT kernel
+        if (tc32::applies(A, lda, a_k, B, ldb, b_k, M, N, K)) return tc32::launch<Epi>(s, A, lda, B, ldb, M, N, K, epi);
         return simt::launch<float, Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi);
     } else {
         if (g_force_simt) return simt::launch<bf16, Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi);

@@ -55,9 +55,11 @@ def test_img_features_gradient_vs_oracle(case, dt):
         ar_in = a.to(dt).float().requires_grad_(True)
     # bf16 through the ReLUs of the advanced deep output: compare with the oracle that rounds what the kernels store in bf16
     # at the same points (mask flips are quantisation, not kernel error; see tests/test_gpu_fullsize.py)
-    with O.emulate_storage(dt if (dt != torch.float32 and cfg.get("ado", False)) else None):
+    relu_bf16 = dt != torch.float32 and cfg.get("ado", False)
+    with O.emulate_storage(dt if relu_bf16 else None):
         pr, ar = O.decoder_forward(Pr, ar_in, cap, tf=cfg.get("tf", True), ado=cfg.get("ado", False),
-                                   attention=cfg.get("attention", True), gate=cfg.get("gate", True))
+                                   attention=cfg.get("attention", True), gate=cfg.get("gate", True),
+                                   relu_masks=(preds.detach().cpu() > 0) if relu_bf16 else None)
     O.train_loss(pr, ar, cap).backward()
     got, ref = feats.grad.cpu(), ar_in.grad
     assert got.shape == ref.shape and got.dtype == torch.float32
