@@ -245,6 +245,12 @@ int sat_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
  * host-side write of hyper[0] between steps. */
 int sat_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, const float* hyper,
                       int32_t* step_count, void* stream);
+/* Data-parallel gradient exchange in half the bytes (no upstream equivalent; the reference is single-device): sat_cast_f32_to_bf16
+ * rounds the flat fp32 gradient to bf16, the caller all-reduces that image over NVLink, and sat_adam_step_dev_bf16grad consumes
+ * the bf16 sums (same update as sat_adam_step_dev otherwise).  Every rank sees the same sums, so replicas stay identical. */
+int sat_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
+int sat_adam_step_dev_bf16grad(float* param, const void* grad_bf16, float* exp_avg, float* exp_avg_sq, int64_t n, const float* hyper,
+                               int32_t* step_count, void* stream);
 
 /* N1: utils.py:101-107 `calculate_caption_lengths(captions, skip_tokens)` (train.py:174-177) without the .item(): out[0] (device
  * int64) = number of ids in the (rows, cols) grid, row pitch `stride`, equal to none of skip0..2 (-1 = unused). */

@@ -349,14 +349,16 @@ int sat_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
  * hyper = [lr, beta1, beta2, eps, weight_decay, grad_scale]; *step_count is the number of updates done so far (the kernel uses
  * step_count + 1 for the bias corrections, a one-thread kernel increments it afterwards).  StepLR (train.py:72,100) then is a
  * host-side write of hyper[0] between steps. */
-__global__ void adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+}  // extern "C"  (the kernel below is a template)
+template <typename TG>
+__global__ void adam_dev_kernel(float* __restrict__ p, const TG* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                                 int64_t n, const float* __restrict__ hyper, const int32_t* __restrict__ step_count) {
     const float lr = hyper[0], b1 = hyper[1], b2 = hyper[2], eps = hyper[3], wd = hyper[4], gs = hyper[5];
     const float step = (float)(step_count[0] + 1);
     const float bc1 = 1.0f - powf(b1, step), bc2 = 1.0f - powf(b2, step);
     const float inv_sbc2 = 1.0f / sqrtf(bc2), slr = lr / bc1;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        float gr = g[i] * gs;
+        float gr = to_f32<TG>(g[i]) * gs;
         const float pv = p[i];
         if (wd != 0.0f) gr += wd * pv;
         const float mi = b1 * m[i] + (1.0f - b1) * gr;
@@ -366,16 +368,37 @@ __global__ void adam_dev_kernel(float* __restrict__ p, const float* __restrict__
     }
 }
 __global__ void adam_tick_kernel(int32_t* step_count) { step_count[0] += 1; }
+extern "C" {
 
-int sat_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, const float* hyper,
-                      int32_t* step_count, void* stream) {
+static int adam_step_dev_any(float* param, const void* grad, int grad_dtype, float* exp_avg, float* exp_avg_sq, int64_t n,
+                             const float* hyper, int32_t* step_count, void* stream) {
     SAT_TRY(require_sm100());
     SAT_REQUIRE(hyper && step_count, "sat_adam_step_dev: null hyper / step_count");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (n > 0) adam_dev_kernel<<<misc::grid_for(n), 256, 0, st>>>(param, grad, exp_avg, exp_avg_sq, n, hyper, step_count);
+    if (n > 0) {
+        if (grad_dtype == SAT_DTYPE_F32)
+            adam_dev_kernel<float><<<misc::grid_for(n), 256, 0, st>>>(param, reinterpret_cast<const float*>(grad), exp_avg, exp_avg_sq, n, hyper, step_count);
+        else
+            adam_dev_kernel<bf16><<<misc::grid_for(n), 256, 0, st>>>(param, reinterpret_cast<const bf16*>(grad), exp_avg, exp_avg_sq, n, hyper, step_count);
+    }
     adam_tick_kernel<<<1, 1, 0, st>>>(step_count);
     SAT_CHECK_CUDA(cudaGetLastError());
     return SAT_OK;
+}
+int sat_adam_step_dev(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, const float* hyper,
+                      int32_t* step_count, void* stream) {
+    return adam_step_dev_any(param, grad, SAT_DTYPE_F32, exp_avg, exp_avg_sq, n, hyper, step_count, stream);
+}
+/* ... with the gradient in bf16: what a data-parallel step all-reduced in half the bytes (sat_cast_f32_to_bf16) */
+int sat_adam_step_dev_bf16grad(float* param, const void* grad_bf16, float* exp_avg, float* exp_avg_sq, int64_t n, const float* hyper,
+                               int32_t* step_count, void* stream) {
+    return adam_step_dev_any(param, grad_bf16, SAT_DTYPE_BF16, exp_avg, exp_avg_sq, n, hyper, step_count, stream);
+}
+/* Gradient compression for the data-parallel exchange: dst (bf16) = src (fp32), n elements. */
+int sat_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream) {
+    SAT_TRY(require_sm100());
+    SAT_REQUIRE((src && dst) || n == 0, "sat_cast_f32_to_bf16: null pointer");
+    return misc::cast<float, bf16>(reinterpret_cast<cudaStream_t>(stream), reinterpret_cast<bf16*>(dst), src, n);
 }
 
 /* utils.py:101-107 / train.py:174-177: tokens of the (rows, cols) int64 grid (row pitch `stride`) that are none of the three

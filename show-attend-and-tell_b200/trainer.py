@@ -32,7 +32,7 @@ class FusedTrainStep:
     EARLY_KEYS = ("init_h.weight", "init_h.bias", "init_c.weight", "init_c.bias", "lstm.weight_ih", "lstm.weight_hh")
 
     def __init__(self, decoder, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, alpha_c=1.0, process_group=None,
-                 distributed=None, step_size=None, gamma=0.1, use_cuda_graph=False):
+                 distributed=None, step_size=None, gamma=0.1, use_cuda_graph=False, grad_exchange_dtype=torch.float32):
         self.dec = decoder
         self.base_lr, self.betas, self.eps, self.alpha_c = float(lr), betas, eps, alpha_c
         self.distributed = dist.is_initialized() if distributed is None else distributed
@@ -55,11 +55,18 @@ class FusedTrainStep:
         self.n_early = max([offsets[k] + ((named[k].numel() + 3) & ~3) for k in early], default=0)
         self.overlap_allreduce = True
         self._comm_stream = None
+        # grad_exchange_dtype = torch.bfloat16: the gradients cross NVLink in half the bytes (cast -> all-reduce -> Adam reads the
+        # bf16 sums); every rank still applies identical updates.  Only used when world > 1.
+        if grad_exchange_dtype not in (torch.float32, torch.bfloat16):
+            raise TypeError("grad_exchange_dtype must be float32 or bfloat16")
+        self.grad_exchange_dtype = grad_exchange_dtype
         # flat buffers; each parameter becomes a view into `flat_param` (state_dict keys/shapes unchanged)
         self.flat_param = torch.zeros(n, device=dev, dtype=torch.float32)
         self.flat_grad = torch.zeros(n, device=dev, dtype=torch.float32)
         self.exp_avg = torch.zeros(n, device=dev, dtype=torch.float32)
         self.exp_avg_sq = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.flat_grad16 = (torch.zeros(n, device=dev, dtype=torch.bfloat16)
+                            if (self.world > 1 and grad_exchange_dtype == torch.bfloat16) else None)
         self.grad_views = {}
         for k in self.train_keys:
             p, o = named[k], offsets[k]
@@ -192,13 +199,25 @@ class FusedTrainStep:
                               for field in _lib.PARAM_FIELDS]
         return self._ptr_list
 
+    def _exchange(self, lo, hi):
+        """All-reduce elements [lo, hi) of the flat gradient on the current stream, in the exchange dtype (async handle)."""
+        if self.flat_grad16 is None:
+            return dist.all_reduce(self.flat_grad[lo:hi], group=self.pg, async_op=True)
+        if self.flat_grad.is_cuda:
+            st = torch.cuda.current_stream(self.flat_grad.device).cuda_stream
+            _lib.check(_lib.lib().sat_cast_f32_to_bf16(self.flat_grad.data_ptr() + 4 * lo, self.flat_grad16.data_ptr() + 2 * lo,
+                                                       hi - lo, st), "sat_cast_f32_to_bf16")
+        else:                                         # host-logic tests on CPU (gloo)
+            self.flat_grad16[lo:hi].copy_(self.flat_grad[lo:hi])
+        return dist.all_reduce(self.flat_grad16[lo:hi], group=self.pg, async_op=True)
+
     def sync_grads(self):
         """The one exchange step of data-parallel training: sum the flat gradient buffer over the ranks (NCCL over
         NVLink on GPUs).  The 1/world of the mean is folded into the Adam kernel (grad_scale)."""
         if self.world <= 1:
             return
         if not (self.overlap_allreduce and self.flat_grad.is_cuda and 0 < self.n_early < self.n):
-            dist.all_reduce(self.flat_grad, group=self.pg)
+            self._exchange(0, self.n).wait()
             return
         # two buckets: the early one is reduced on a side stream as soon as the backward pass has written it (under the rest
         # of the backward tail), the rest on the current stream after the pass; Adam then waits for both
@@ -208,9 +227,14 @@ class FusedTrainStep:
         cs = self._comm_stream
         _lib.check(_lib.lib().sat_wait_early_grads(cs.cuda_stream), "sat_wait_early_grads")
         with torch.cuda.stream(cs):
-            early = dist.all_reduce(self.flat_grad[:self.n_early], group=self.pg, async_op=True)
-        dist.all_reduce(self.flat_grad[self.n_early:], group=self.pg)
+            early = self._exchange(0, self.n_early)
+        late = self._exchange(self.n_early, self.n)
+        late.wait()
         early.wait()                                   # the current stream waits for the early bucket
+
+    def reduced_grad(self):
+        """The buffer Adam consumes after sync_grads(): the fp32 flat gradient, or its all-reduced bf16 image."""
+        return self.flat_grad if self.flat_grad16 is None else self.flat_grad16
 
     def layout_signature(self):
         """(key, offset, numel) of every trainable tensor in the flat buffers; must be identical on all ranks."""
@@ -256,9 +280,10 @@ class FusedTrainStep:
         _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(self._grad_struct())), "sat_decoder_backward")
         self.sync_grads()
         if optimizer_step:
-            _lib.check(L.sat_adam_step_dev(self.flat_param.data_ptr(), self.flat_grad.data_ptr(), self.exp_avg.data_ptr(),
-                                           self.exp_avg_sq.data_ptr(), self.n, self.hyper.data_ptr(), self.step_dev.data_ptr(),
-                                           a.stream), "sat_adam_step_dev")
+            g = self.reduced_grad()
+            fn = L.sat_adam_step_dev if g.dtype == torch.float32 else L.sat_adam_step_dev_bf16grad
+            _lib.check(fn(self.flat_param.data_ptr(), g.data_ptr(), self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.n,
+                          self.hyper.data_ptr(), self.step_dev.data_ptr(), a.stream), "sat_adam_step_dev")
 
     def step(self, img_features, captions, dropout_mask=None, optimizer_step=True):
         """One training step; returns the device tensor [ce, alpha_reg, total, status] (no host sync)."""

@@ -127,6 +127,13 @@ def _worker_round2(rank, world, port, q):
             raise AssertionError("layout mismatch not detected")
         except RuntimeError as e:
             assert "layout differs" in str(e)
+        # 1b. bf16 gradient exchange: the sum arrives in the bf16 image Adam consumes; small integers are exact in bf16
+        torch.manual_seed(7)
+        tr16 = FusedTrainStep(Decoder(40, 64, tf=True, bert=False, attention=True), grad_exchange_dtype=torch.bfloat16)
+        tr16.flat_grad.copy_((torch.arange(tr16.n) % 61).float() + rank)
+        tr16.sync_grads()
+        want = world * (torch.arange(tr16.n) % 61).float() + sum(range(world))
+        assert tr16.reduced_grad().dtype == torch.bfloat16 and torch.equal(tr16.reduced_grad().float(), want)
         # 2. sharded beam search: unequal shards, padded gather on rank 0, image order = rank order
         lo, hi = sharded.shard_range(7, rank, world)
         assert (lo, hi) == ((0, 4) if rank == 0 else (4, 7))

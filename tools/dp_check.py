@@ -38,6 +38,21 @@ def main():
         others = [torch.empty_like(tr.flat_param) for _ in range(world)]
         dist.all_gather(others, tr.flat_param)
         assert all(torch.equal(o, others[0]) for o in others), f"overlap={overlap}: parameters differ between ranks"
+    # bf16 gradient exchange + CUDA-graph replay (what bench.py runs at N > 1): replicas stay bit-identical, and the parameters
+    # stay within the update size of the fp32 exchange
+    dec = Decoder(V, D, tf=True, attention=True, compute_dtype=torch.bfloat16)
+    dec.load_state_dict(P)
+    dec = dec.to(dev).eval()
+    tr = FusedTrainStep(dec, lr=1e-3, grad_exchange_dtype=torch.bfloat16, use_cuda_graph=True)
+    for _ in range(5):
+        loss16 = tr.step(a, cap)
+    torch.cuda.synchronize()
+    others = [torch.empty_like(tr.flat_param) for _ in range(world)]
+    dist.all_gather(others, tr.flat_param)
+    assert all(torch.equal(o, others[0]) for o in others), "bf16 exchange: parameters differ between ranks"
+    if rank == 0:
+        print(f"bf16 exchange + graph: {tr.graph_replays} graph replays, replicas identical, loss after 5 steps {loss16.tolist()}")
+    assert tr.graph_replays == 3
     p0, p1 = res[False][0], res[True][0]
     err = (p0 - p1).abs().max().item()
     upd = 3 * 1e-3                                                        # Adam moves an element by <= ~lr per step
