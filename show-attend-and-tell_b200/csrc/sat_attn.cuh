@@ -149,7 +149,7 @@ fwd_kernel(FwdParams p, SmemLayout sl) {
                 for (int nb = 0; nb < NBG; ++nb) {
                     const float* uu = uh_s + nb * H + c * VEC;
 #pragma unroll
-                    for (int i = 0; i < VEC; ++i) s[nb] = fmaf(vv[i], sat_tanh<PRECISE>(w[i] + uu[i]), s[nb]);
+                    for (int i = 0; i < VEC; ++i) s[nb] = fmaf(vv[i], attn_tanh<PRECISE>(w[i] + uu[i]), s[nb]);
                 }
             }
 #pragma unroll
@@ -495,7 +495,7 @@ bwd_kernel(BwdParams p, BwdSmem sl) {
             Vec16<T>::unpack(u, w);
 #pragma unroll
             for (int i = 0; i < VEC; ++i) {
-                const float th = sat_tanh<PRECISE>(w[i] + uh[i]);
+                const float th = attn_tanh<PRECISE>(w[i] + uh[i]);
                 dp[i] = de * vv[i] * (1.0f - th * th);
                 dU[i] += dp[i];
                 dV[i] = fmaf(de, th, dV[i]);

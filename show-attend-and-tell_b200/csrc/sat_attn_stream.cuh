@@ -367,8 +367,8 @@ fwd_stream_kernel(FwdParams p, Smem sl, Part pt, int ngroups) {
                             }
 #pragma unroll
                             for (int i = 0; i < VEC; ++i) {
-                                sc0[nb] = fmaf(vreg[j * VEC + i], sat_tanh<PRECISE>(f0[i] + u[i]), sc0[nb]);
-                                sc1[nb] = fmaf(vreg[j * VEC + i], sat_tanh<PRECISE>(f1[i] + u[i]), sc1[nb]);
+                                sc0[nb] = fmaf(vreg[j * VEC + i], attn_tanh<PRECISE>(f0[i] + u[i]), sc0[nb]);
+                                sc1[nb] = fmaf(vreg[j * VEC + i], attn_tanh<PRECISE>(f1[i] + u[i]), sc1[nb]);
                             }
                         }
                     }
@@ -762,8 +762,8 @@ bwd_stream_kernel(BwdParams p, Smem sl, Part pt) {
                         Vec16<T>::unpack(lds16(wa_s + (size_t)lq * H + c * VEC), w1);
 #pragma unroll
                         for (int i = 0; i < VEC; ++i) {
-                            const float t0 = sat_tanh<PRECISE>(w0[i] + uh[j * VEC + i]);
-                            const float t1 = sat_tanh<PRECISE>(w1[i] + uh[j * VEC + i]);
+                            const float t0 = attn_tanh<PRECISE>(w0[i] + uh[j * VEC + i]);
+                            const float t1 = attn_tanh<PRECISE>(w1[i] + uh[j * VEC + i]);
                             dp0[i] = de0 * vreg[j * VEC + i] * (1.0f - t0 * t0);
                             dp1[i] = de1 * vreg[j * VEC + i] * (1.0f - t1 * t1);
                             dU[j * VEC + i] += dp0[i] + dp1[i];

@@ -54,17 +54,34 @@ topk_step_kernel(StepParams p) {
     __syncthreads();
     float last_v = INFINITY;
     int last_i = -1;
+    if (cached) {
+        // Load phase: the cumulative scores of the image go to shared memory with independent, unrolled 16-byte loads.  (Reading
+        // global memory inside the first selection pass serialised ~25 dependent L2 round trips per thread: 23 us per step for
+        // 50 KB per image, r2 beam timeline.)  Rows are 32-byte aligned (ldl % 8 == 0); the tail of a row is done by scalars.
+        const int v4 = p.V >> 2;
+        for (int r = 0; r < rows; ++r) {
+            const float4* src = reinterpret_cast<const float4*>(lg + (size_t)r * p.ldl);
+            float* dst = s_cache + r * p.V;
+            const float tp = s_tp[r];
+#pragma unroll 4
+            for (int i = threadIdx.x; i < v4; i += TOPK_THREADS) {
+                const float4 x = __ldg(src + i);
+                dst[4 * i] = tp + x.x; dst[4 * i + 1] = tp + x.y; dst[4 * i + 2] = tp + x.z; dst[4 * i + 3] = tp + x.w;   // decoder.py:204
+            }
+            for (int i = 4 * v4 + threadIdx.x; i < p.V; i += TOPK_THREADS) dst[i] = tp + lg[(size_t)r * p.ldl + i];
+        }
+        __syncthreads();
+    }
     for (int k = 0; k < n; ++k) {
         float bv = -INFINITY;
         int bi = 0x7fffffff;
         for (int i = threadIdx.x; i < total; i += TOPK_THREADS) {
             float sc;
-            if (cached && k > 0) {
+            if (cached) {
                 sc = s_cache[i];
             } else {
                 const int r = i / p.V;
                 sc = s_tp[r] + lg[(size_t)r * p.ldl + (i - r * p.V)];   // decoder.py:204
-                if (cached) s_cache[i] = sc;
             }
             const bool after = (sc < last_v) || (sc == last_v && i > last_i);
             if (after && (sc > bv || (sc == bv && i < bi))) { bv = sc; bi = i; }
@@ -293,11 +310,22 @@ __global__ void beam_init_state_kernel(int* live, int* done, int* n_active, int*
     if (i < NI * beam) { top_preds[i] = 0.0f; prev_word[i] = start; }     // decoder.py:166-171
 }
 
-// one pinned int per host thread for the early-exit poll
-static inline int beam_host_flag(int** out) {
-    static thread_local int* flag = nullptr;
-    if (!flag) SAT_CHECK_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&flag), sizeof(int), cudaHostAllocPortable));
-    *out = flag;
+// two pinned flags + events per host thread and device for the pipelined early-exit poll
+struct BeamPoll { int* flag[2]; cudaEvent_t ev[2]; bool ok; };
+static inline int beam_poll_state(BeamPoll** out) {
+    static thread_local BeamPoll cache[64] = {};
+    int dev = 0;
+    SAT_CHECK_CUDA(cudaGetDevice(&dev));
+    SAT_REQUIRE(dev >= 0 && dev < 64, "device index %d out of range", dev);
+    BeamPoll& b = cache[dev];
+    if (!b.ok) {
+        for (int i = 0; i < 2; ++i) {
+            SAT_CHECK_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&b.flag[i]), sizeof(int), cudaHostAllocPortable));
+            SAT_CHECK_CUDA(cudaEventCreateWithFlags(&b.ev[i], cudaEventDisableTiming));
+        }
+        b.ok = true;
+    }
+    *out = &b;
     return SAT_OK;
 }
 
@@ -417,14 +445,20 @@ int beam_search_t(const sat_beam_args& a) {
         beam::gather_state_kernel<T><<<R, 128, 0, st>>>(w.X, xw, H + D, w.Hn, w.Cc, w.Cn, w.parent, w.live, w.done, NB, H);
         SAT_CHECK_CUDA(cudaGetLastError());
         if ((step % 8) == 0 && step < S) {     // early exit once every image has finished (no effect on results)
-            // pinned flag: a pageable destination costs ~90 us per copy (staging) on top of the pipeline drain; every 8 steps
-            // keeps the drain + refill (~0.1 ms) under 3 % of a 51-step search while a batch of short captions still stops early
-            int* active = nullptr;
-            SAT_TRY(beam_host_flag(&active));
-            *active = 1;
-            SAT_CHECK_CUDA(cudaMemcpyAsync(active, w.n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
-            SAT_CHECK_CUDA(cudaStreamSynchronize(st));
-            if (*active <= 0) break;
+            // PIPELINED poll: the flag copied after step s is only looked at after the launches of steps s+1 .. s+8 have been
+            // enqueued, so the host never drains the GPU (a blocking poll cost ~170 us of idle GPU each: the sync plus the time to
+            // enqueue the next steps' 56 launches).  Price: up to 8 extra steps on images that are all done already -- their
+            // kernels return at once (done[] / live[] guards).  Pinned flags: a pageable destination adds ~90 us of staging.
+            BeamPoll* bp = nullptr;
+            SAT_TRY(beam_poll_state(&bp));
+            const int cur = (step / 8) & 1;
+            if (step >= 16) {                  // the copy issued 8 steps ago
+                SAT_CHECK_CUDA(cudaEventSynchronize(bp->ev[cur ^ 1]));
+                if (*bp->flag[cur ^ 1] <= 0) break;
+            }
+            *bp->flag[cur] = 1;
+            SAT_CHECK_CUDA(cudaMemcpyAsync(bp->flag[cur], w.n_active, sizeof(int), cudaMemcpyDeviceToHost, st));
+            SAT_CHECK_CUDA(cudaEventRecord(bp->ev[cur], st));
         }
     }
     beam::FinalParams fp;

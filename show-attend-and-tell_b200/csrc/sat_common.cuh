@@ -144,6 +144,19 @@ template <bool PRECISE> __device__ __forceinline__ float sat_tanh(float x) {
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
+// tanh of the attention scores e_l = v . tanh(Wa_l + Uh) (attention.py:17-18).  fp32 mode: the score step of a 128-image beam-5
+// search evaluates 64 M tanh per decode step, and libm's tanhf (~25 instructions, two branches) made the fp32 attention kernel
+// compute-bound (93 us per step).  1 - 2 / (1 + e^{2x}) with ex2.approx + rcp.approx is 2 MUFU + 4 FMA-pipe instructions; its
+// ABSOLUTE error is <= ~3e-7 (saturates correctly to +-1), which is what matters here: the tanh feeds a dot product with |v| < 0.05,
+// so a score moves by ~1e-7 -- the size of libm-vs-libm differences -- while relative accuracy near 0 is irrelevant.  The LSTM cell
+// and the initial state keep tanhf.
+template <bool PRECISE> __device__ __forceinline__ float attn_tanh(float x) {
+    if (!PRECISE) return sat_tanh<false>(x);
+    float e, r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * 2.885390081777927f));      // e^{2x} = 2^{2x log2 e}
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+    return fmaf(-2.0f, r, 1.0f);
+}
 template <bool PRECISE> __device__ __forceinline__ float sat_sigmoid(float x) {
     if (PRECISE) return 1.0f / (1.0f + expf(-x));
     return 0.5f * sat_tanh<false>(0.5f * x) + 0.5f;

@@ -40,6 +40,32 @@ def _fill_params(struct, module: "Decoder", grads: bool = False, tensors=None):
     return keep
 
 
+_PINNED = {}
+
+
+def _to_host(tensors):
+    """Device tensors -> host tensors with ONE synchronisation: non-blocking copies into cached pinned buffers (six separate
+    `.cpu()` calls of pageable copies cost ~1 ms per beam-search call, r2 beam timeline).  The returned tensors are views of the
+    cache: consume them before the next call (results_from_raw converts them to lists / clones at once)."""
+    out, dev = {}, None
+    for k, t in tensors.items():
+        if not t.is_cuda:
+            out[k] = t
+            continue
+        dev = t.device
+        key = (k, tuple(t.shape), t.dtype)
+        buf = _PINNED.get(key)
+        if buf is None:
+            if len(_PINNED) > 64:
+                _PINNED.clear()
+            buf = _PINNED[key] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        buf.copy_(t, non_blocking=True)
+        out[k] = buf
+    if dev is not None:
+        torch.cuda.current_stream(dev).synchronize()
+    return out
+
+
 class _DecoderFn(torch.autograd.Function):
     """autograd bridge: forward = sat_decoder_forward, backward = sat_decoder_backward."""
 
@@ -330,11 +356,10 @@ class Decoder(nn.Module):
     def results_from_raw(raw):
         """Padded device outputs -> the reference's per-image return values: (list[int], list[list[float]]) for a completed
         caption, ([0], Tensor(live, L)) for the "No completed sentences found" fallback (decoder.py:256-258, Q18)."""
-        lens, status, live = raw["lens"].cpu().tolist(), raw["status"].cpu().tolist(), raw["live"].cpu().tolist()
-        toks = raw["tokens"].cpu()
-        alph = raw["alphas"].cpu() if "alphas" in raw else None
-        # one transfer for all fallback rows (the reference builds these tensors on the CPU, Q19)
-        last = raw["last_alpha"].cpu() if ("last_alpha" in raw and any(status)) else None
+        host = _to_host({k: raw[k] for k in ("lens", "status", "live", "tokens", "alphas", "last_alpha") if k in raw})
+        lens, status, live = host["lens"].tolist(), host["status"].tolist(), host["live"].tolist()
+        toks, alph = host["tokens"], host.get("alphas")
+        last = host.get("last_alpha") if any(status) else None     # fallback rows (the reference builds these on the CPU, Q19)
         results = []
         for i in range(len(lens)):
             if status[i] != 0:
