@@ -31,6 +31,10 @@ int sat_set_force_simt(int on);
  * tensor cores as 3xTF32 -- each fp32 operand split into tf32 hi + lo, three tcgen05.mma.kind::tf32 per k-step into one fp32 TMEM
  * accumulator: within a few fp32 ulps of an exact-fp32 dot product; 0 = the true-fp32 SIMT FMA kernel always */
 int sat_set_fp32_gemm_mode(int mode);
+/* tuning knob: 1 (default) = bf16 GEMMs with K-major operands whose grid fills the GPU at least twice over (the encoder projection
+ * K1) run on the 256 x 256 tile (two TMEM accumulators per CTA sharing one B stage: half the L2 traffic per flop of the 128 x 256
+ * tile); 0 = always the 128-row tile.  sat_gemm's bn_override = 512 forces the wide tile (tests). */
+int sat_set_gemm_wide_tile(int on);
 /* debug knob: 1 = run the attention step on the generic cluster kernels even where the streaming kernels apply */
 int sat_set_attn_generic(int on);
 /* debug knob: work partition of the streaming attention kernels. 0 = auto, 1 = whole items per CTA, 2 = equal slot counts */

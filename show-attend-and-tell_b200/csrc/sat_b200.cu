@@ -4,6 +4,7 @@
 #include "sat_beam.cuh"
 
 int g_force_simt = 0;
+int g_gemm_wide = 1;         // large K-major bf16 GEMMs on the 256 x 256 two-accumulator tile (sat_gemm_tc.cuh)
 int g_fp32_gemm_mode = 1;   // fp32 mode: 1 = 3xTF32 tcgen05 kernel for K-major x K-major GEMMs, 0 = SIMT FMA kernel always
 int g_gemm_static_b = 1;     // in-loop GEMMs: weights loaded with evict_last and requested before the PDL wait
 int g_attn_generic = 0;
@@ -80,6 +81,7 @@ extern "C" {
 const char* sat_last_error(void) { return g_err; }
 int sat_version(void) { return 200; }
 int sat_set_force_simt(int on) { g_force_simt = on ? 1 : 0; return SAT_OK; }
+int sat_set_gemm_wide_tile(int on) { g_gemm_wide = on ? 1 : 0; return SAT_OK; }
 int sat_set_fp32_gemm_mode(int mode) { g_fp32_gemm_mode = mode == 1 ? 1 : 0; return SAT_OK; }
 int sat_set_attn_generic(int on) { g_attn_generic = on ? 1 : 0; return SAT_OK; }
 int sat_set_attn_l2_policy(int wa_fwd, int wa_bwd, int64_t pin_bytes) {

@@ -18,6 +18,7 @@ constexpr int BM = 128, BK = 64, UMMA_K = 16;
 // tools/tma_bw.cu), which bounds a skinny GEMM's k-loop; so NPROD producer lanes take the k-blocks round-robin.
 constexpr int NPROD = SAT_GEMM_NPROD;
 }  // namespace tc
+extern int g_gemm_wide;         // sat_set_gemm_wide_tile: 1 (default) = large K-major GEMMs use the 256 x 256 two-accumulator tile
 extern int g_gemm_max_split;    // tuning knob (sat_set_gemm_splitk): largest split-K cluster size, 1 = never split
 // Debug instrumentation (sat_gemm_phase_stamps): when the flag is set, CTA (0,0,0) of a GEMM whose epilogue carries a
 // DBG_ID > 0 leaves %globaltimer stamps of its phases: 0 entry, 1 after the PDL wait, 2 first operand stage landed,
@@ -372,6 +373,121 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     }
 }
 
+// ---- wide tile: 256 x 256 per CTA (two 128-row accumulators sharing one B tile) --------------------------------------------
+// The 128 x 256 tile above pulls 48 KB from L2 per k-block for 0.26 us of MMAs = 185 GB/s per SM, 27 TB/s over 148 SMs -- more
+// than L2 delivers (~12 TB/s): ncu shows K1 (M = B L = 50 176, N = 512, K = 2048) at 47.7 % tensor-pipe activity = the L2 bound of
+// that tile shape (85 flop per operand byte).  Here one CTA keeps TWO M-tiles' accumulators in TMEM (2 x 256 = all 512 columns) and
+// issues both tiles' MMAs against the SAME B stage: 64 KB per k-block for twice the math (131 flop per byte, the intensity a
+// cta_group::2 pair would have) with nothing shared between SMs.  K-major operands only, BN = 256, no split-K; three 64 KB stages;
+// one producer thread (a k-block lasts 0.52 us, a TMA round ~0.3 us); the sixteen epilogue warps drain the two accumulators one
+// after the other through the coalesced staging path.
+struct Cfg2M {
+    static constexpr int BN = 256, MT = 2, STAGES = 3;
+    static constexpr int A_BYTES = MT * BM * BK * 2;     // 32 KB: 256 rows x 128 B, m-tile j starts at j * 16 KB
+    static constexpr int B_BYTES = BN * BK * 2;          // 32 KB
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 + 256;
+};
+
+template <typename Epi>
+__global__ void __launch_bounds__(THREADS, 1)
+gemm2m_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K, Epi epi) {
+    using C = Cfg2M;
+    constexpr int BN = C::BN;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + C::STAGES * C::A_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + C::STAGES;
+    uint64_t* tmem_full_bar = empty_bar + C::STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * (C::MT * BM), n0 = blockIdx.x * BN;
+    const int nk = (K + BK - 1) / BK;
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&mapA);
+        tma_prefetch_desc(&mapB);
+        for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(tmem_full_bar, 1);
+        mbar_fence_init();
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "n"(C::MT * BN) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kb = 0; kb < nk; ++kb) {
+                const int s = kb % C::STAGES;
+                mbar_wait(&empty_bar[s], ((kb / C::STAGES) & 1) ^ 1);
+                mbar_expect_tx(&full_bar[s], C::STAGE_BYTES);
+                tma_load_2d(sA + s * C::A_BYTES, &mapA, kb * BK, m0, &full_bar[s]);      // 256 rows: both M-tiles
+                tma_load_2d(sB + s * C::B_BYTES, &mapB, kb * BK, n0, &full_bar[s]);
+            }
+        }
+    } else if (warp == 1) {
+        if (elect_one()) {
+            constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            for (int kb = 0; kb < nk; ++kb) {
+                const int s = kb % C::STAGES;
+                mbar_wait(&full_bar[s], (kb / C::STAGES) & 1);
+                tc_fence_after();
+                const uint32_t a_addr = smem_u32(sA + s * C::A_BYTES), b_addr = smem_u32(sB + s * C::B_BYTES);
+#pragma unroll
+                for (int kk = 0; kk < BK / UMMA_K; ++kk) {
+                    const uint64_t bd = make_desc(b_addr + kk * (UMMA_K * 2), 16, 1024);
+#pragma unroll
+                    for (int j = 0; j < C::MT; ++j)
+                        umma_bf16(tmem_base + (uint32_t)(j * BN), make_desc(a_addr + j * (BM * BK * 2) + kk * (UMMA_K * 2), 16, 1024), bd, idesc,
+                                  (kb > 0 || kk > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);
+            }
+            umma_commit(tmem_full_bar);
+        }
+    } else if (warp < 2 + EPI_WARPS) {
+        const int q = warp & 3, grp = (warp - 2) >> 2;
+        mbar_wait(tmem_full_bar, 0);
+        tc_fence_after();
+        constexpr int XP = BN + 4, PW = 32, C4 = BN / 4;
+        static_assert(BM * XP * 4 <= C::STAGES * C::STAGE_BYTES, "staging buffer must fit in the stage ring");
+        float* xbuf = reinterpret_cast<float*>(smem);
+        const int row = q * 32 + lane;
+#pragma unroll 1
+        for (int j = 0; j < C::MT; ++j) {
+            if (j > 0) asm volatile("bar.sync 2, %0;" ::"n"(EPI_WARPS * 32) : "memory");      // everyone has read the previous tile
+#pragma unroll 1
+            for (int p = grp; p < BN / PW; p += EPI_GROUPS) {
+                float v[PW];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(j * BN + p * PW), v);
+                float4* dst = reinterpret_cast<float4*>(xbuf + (size_t)row * XP + p * PW);
+#pragma unroll
+                for (int c4 = 0; c4 < PW / 4; ++c4) dst[c4] = make_float4(v[4 * c4], v[4 * c4 + 1], v[4 * c4 + 2], v[4 * c4 + 3]);
+            }
+            asm volatile("bar.sync 2, %0;" ::"n"(EPI_WARPS * 32) : "memory");
+            for (int c = (warp - 2) * 32 + lane; c < BM * C4; c += EPI_WARPS * 32) {
+                const int r = c / C4, c4 = c - r * C4;
+                const float4 t = *reinterpret_cast<const float4*>(xbuf + (size_t)r * XP + c4 * 4);
+                const float acc[4] = {t.x, t.y, t.z, t.w};
+                const int n = n0 + c4 * 4;
+                if (n < N) epi.template apply<4>(m0 + j * BM + r, n, acc);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(C::MT * BN) : "memory");
+    }
+}
+
 // ---- host side ---------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -492,10 +608,35 @@ int launch_mn(cudaStream_t stream, const bf16* A, int64_t lda, const bf16* B, in
 }
 
 template <typename Epi>
+int launch_2m(cudaStream_t stream, const bf16* A, int64_t lda, const bf16* B, int64_t ldb, int M, int N, int K, const Epi& epi) {
+    CUtensorMap mA, mB;
+    SAT_TRY(make_map(&mA, A, K, M, lda, 64, Cfg2M::MT * BM));
+    SAT_TRY(make_map(&mB, B, K, N, ldb, 64, Cfg2M::BN));
+    auto kern = gemm2m_kernel<Epi>;
+    static SatPerDevice configured;
+    SAT_TRY(configured.once([&]() -> int {
+        SAT_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg2M::SMEM_BYTES));
+        return SAT_OK;
+    }));
+    cudaLaunchConfig_t cfg;
+    cudaLaunchAttribute attr[1];
+    pdl_config(&cfg, attr, dim3(sat_cdiv(N, Cfg2M::BN), sat_cdiv(M, Cfg2M::MT * BM)), dim3(THREADS), Cfg2M::SMEM_BYTES, stream);
+    SAT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, M, N, K, epi));
+    return SAT_OK;
+}
+
+template <typename Epi>
 int launch(cudaStream_t stream, const bf16* A, int64_t lda, bool a_kmajor, const bf16* B, int64_t ldb, bool b_kmajor,
            int M, int N, int K, const Epi& epi, int bn_override = 0, int split_override = 0, int sm_budget = 0, int b_static = 0) {
     if (M <= 0 || N <= 0) return SAT_OK;
     SAT_REQUIRE(K > 0, "tcgen05 GEMM needs K > 0");
+    if constexpr (EpiCoalesce<Epi>::value) {
+        // wide tile where the grid still fills the machine at least twice over (K1 at c2: 196 x 2 CTAs); bn_override = 512 forces it
+        if (a_kmajor && b_kmajor && !sm_budget && (bn_override == 512 || (g_gemm_wide && !bn_override && N >= 256 && K >= 256 &&
+            (long long)sat_cdiv(M, Cfg2M::MT * BM) * sat_cdiv(N, Cfg2M::BN) >= 2 * 148)))
+            return launch_2m<Epi>(stream, A, lda, B, ldb, M, N, K, epi);
+    }
+    SAT_REQUIRE(bn_override != 512, "the 256 x 256 tile needs K-major operands and a coalescing epilogue");
     int bn = 0, split = 1;
     pick_tile(M, N, K, !b_kmajor, &bn, &split, sm_budget);
     if (bn_override) { bn = bn_override; split = split_override > 0 ? split_override : 1; }

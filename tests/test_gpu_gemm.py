@@ -65,6 +65,13 @@ def test_gemm_bf16_tile_widths(bn):
         _run(torch.bfloat16, 300, 520, 448, False, False, bn=bn)
 
 
+@pytest.mark.parametrize("M,N,K", [(700, 520, 448), (256, 256, 64), (1000, 2531, 512), (4096, 512, 2048), (130, 300, 1000)])
+def test_gemm_bf16_wide_tile(M, N, K):
+    """256 x 256 tile (two TMEM accumulators per CTA sharing one B stage), forced with bn = 512: ragged M / N / K, bias, tanh."""
+    _run(torch.bfloat16, M, N, K, True, True, bn=512)
+    _run(torch.bfloat16, M, N, K, True, True, bn=512, act=1, bias=False, seed=3)
+
+
 def test_gemm_bf16_long_k_and_act():
     _run(torch.bfloat16, 512, 2048, 50176 // 8, False, False, bias=False)
     _run(torch.bfloat16, 64, 1024, 2048, True, True, act=1)

@@ -1,6 +1,6 @@
 """A/B timing of the fused c2 train step under library tuning knobs (device-resident, CUDA events, median of repeats).
   python tools/ab_step.py "pf=0,0" "pf=32,32" "pf=64,64;part=2" ...
-Knobs per variant (';'-separated): pf=F,B (sat_set_attn_prefetch), part=M (sat_set_attn_partition), graph=0|1 (CUDA-graph replay),
+Knobs per variant (';'-separated): pf=F,B (sat_set_attn_prefetch), part=M (sat_set_attn_partition), graph=0|1 (CUDA-graph replay), wide=0|1 (sat_set_gemm_wide_tile),
 ado=0|1.  Prints one line per variant: ms/step (median of 5 x 20 steps), attention fwd / bwd event-bracket averages."""
 import ctypes
 import os
@@ -27,9 +27,10 @@ def main():
     trainers = {}
     for v in variants:
         kn = dict(kv.split("=") for kv in v.split(";") if kv)
-        pf = [int(x) for x in kn.get("pf", "0,0").split(",")]
+        pf = [int(x) for x in kn.get("pf", "0,8").split(",")]
         L.sat_set_attn_prefetch(pf[0], pf[1])
         L.sat_set_attn_partition(int(kn.get("part", 0)))
+        L.sat_set_gemm_wide_tile(int(kn.get("wide", 1)))
         graph, ado = int(kn.get("graph", 0)), int(kn.get("ado", 0))
         key = (graph, ado)
         if key not in trainers:
