@@ -23,6 +23,10 @@ extern "C" {
 /* device-side status bits of a sequence-driver call (sat_decoder_args.loss[3]) */
 #define SAT_STATUS_BAD_TOKEN 1   /* a caption id outside [0, V): nn.Embedding / CrossEntropyLoss raise IndexError upstream */
 
+/* Threading: the compute entry points may be called from several host threads (thread-local error string, per-thread / per-device
+ * side streams and events, per-device kernel attributes).  The sat_set_* knobs below are DEBUG / TUNING switches stored in plain
+ * process-wide ints: set them before the first compute call or from one thread while no call is in flight -- they are not part of
+ * the re-entrancy guarantee, and the defaults are the product configuration. */
 const char* sat_last_error(void);
 int sat_version(void);
 /* debug knob: 1 = run bf16 GEMMs on the SIMT kernel (bring-up cross-check of the tcgen05 kernel) */
