@@ -505,6 +505,7 @@ def run_ours(args, rank, world, local_rank):
         beam = {"skipped": "SAT_BENCH_SKIP_SIDE"} if skip_side else beam_block(dev, rank, world, barrier, max_over_ranks)
     except Exception as e:                                   # noqa: BLE001
         beam = {"error": f"{type(e).__name__}: {e}"}
+    trainer.close()                                        # graphs with captured NCCL work must be gone before the process group is
     if rank != 0:
         return
     cpu = None
@@ -566,10 +567,17 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
         run_ours(args, rank, world, local_rank)
-    finally:
-        if world > 1:
-            import torch.distributed as dist
-            dist.destroy_process_group()
+    except BaseException:
+        # a rank that dies while its peers sit in a collective would hang the job (and destroy_process_group() hangs while CUDA
+        # graphs with captured NCCL work are alive in the failed frame): report and leave at once
+        import traceback
+        traceback.print_exc()
+        sys.stderr.flush()
+        os._exit(1)
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":

@@ -427,9 +427,8 @@ int decoder_forward_t(const sat_decoder_args& a) {
         const float* logits = a.preds ? a.preds : w.logits_tmp;
         // with need_grad the same pass also leaves d loss / d logits for a unit upstream gradient (what the fused train step
         // feeds back); sat_decoder_backward recomputes it only when it is handed a dloss scalar
-        misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, w.rowloss,
-                                                        a.need_grad ? w.dlog : (T*)nullptr, w.Vp, nullptr, 1.0f / (float)(B * (Tn - 1)),
-                                                        a.ado, w.flags);
+        misc::ce_rows<T>(st, B * Tn, logits, w.ldl, V, Tn, a.captions, a.cap_stride, w.rowloss,
+                         a.need_grad ? w.dlog : (T*)nullptr, w.Vp, nullptr, 1.0f / (float)(B * (Tn - 1)), a.ado, w.flags);
         misc::loss_partial_kernel<<<misc::LOSS_PARTS, 256, 0, st>>>(w.rowloss, B * Tn, a.alphas, B, Tn, L, w.loss_part);
         misc::loss_finalize_kernel<<<1, 256, 0, st>>>(w.loss_part, misc::LOSS_PARTS, B * (Tn - 1), a.alphas != nullptr, B, L, a.alpha_c, a.loss,
                                                       w.flags);
@@ -463,8 +462,7 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     if (a.fused_loss) {
         const float scale = 1.0f / (float)(B * (Tn - 1));
         if (g.dloss)     // otherwise the forward's unit-gradient dlogits are still in the workspace
-            misc::ce_rows_kernel<T><<<B * Tn, 256, 0, st>>>(logits, w.ldl, V, Tn, a.captions, a.cap_stride, nullptr, w.dlog, Vp, g.dloss, scale,
-                                                            a.ado, nullptr);
+            misc::ce_rows<T>(st, B * Tn, logits, w.ldl, V, Tn, a.captions, a.cap_stride, nullptr, w.dlog, Vp, g.dloss, scale, a.ado, nullptr);
         if (a.attention) {
             misc::alpha_reg_grad_kernel<<<sat_cdiv(B * L, 128), 128, 0, st>>>(a.alphas, w.galpha, B, Tn, L, a.alpha_c, g.dloss);
             galpha = w.galpha;

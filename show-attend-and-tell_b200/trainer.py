@@ -341,6 +341,14 @@ class FusedTrainStep:
         graph.replay()              # capture records, it does not execute
         self.graph_replays += 1
 
+    def close(self):
+        """Drop the captured CUDA graphs.  Call before `dist.destroy_process_group()`: a live graph that captured NCCL all-reduces
+        keeps the communicator busy and the destroy call hangs (seen with tools/dp_check.py on 2 GPUs)."""
+        self._graphs.clear()
+        self._seen.clear()
+        if self.flat_param.is_cuda:
+            torch.cuda.synchronize(self.flat_param.device)
+
     def check_status(self, loss_host=None):
         """Raise what the reference raises eagerly: IndexError for a caption id outside [0, V) (nn.Embedding /
         CrossEntropyLoss).  The kernels only set a flag (loss[3]); call this wherever the loss is read back anyway

@@ -60,6 +60,10 @@ def main():
         print(f"ranks={world} n_early={tr.n_early} of {tr.n} floats; max |param(one call) - param(two buckets)| = {err:.3e} "
               f"(three Adam steps of lr 1e-3); losses {res[False][1].tolist()} / {res[True][1].tolist()}")
     assert err <= 0.02 * upd, err
+    # a live CUDA graph that captured NCCL work keeps the communicator busy: destroy_process_group() then hangs.  Drop the graphs first.
+    tr.close()
+    del tr
+    torch.cuda.synchronize()
     dist.destroy_process_group()
     if rank == 0:
         print("dp_check OK")
