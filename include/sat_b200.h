@@ -205,6 +205,9 @@ int sat_decoder_logits(const sat_decoder_args* args, const float** logits, int64
  * lstm.weight_ih / weight_hh, which are final ~160 us before the call's last kernel; a caller can all-reduce that bucket under the
  * rest of the backward pass.  No-op before the first backward. */
 int sat_wait_early_grads(void* stream);
+/* ... and until every gradient except attention.W.* / attention.v.* is written (they come last, from the main chain of the
+ * backward tail): a caller can all-reduce and apply all the others while the encoder projection's gradient GEMM is still running. */
+int sat_wait_side_grads(void* stream);
 int sat_decoder_forward(const sat_decoder_args* args);
 int sat_decoder_backward(const sat_decoder_args* args, const sat_decoder_grads* grads);
 
@@ -257,6 +260,11 @@ int sat_adam_step_dev(float* param, const float* grad, float* exp_avg, float* ex
  * rounds the flat fp32 gradient to bf16, the caller all-reduces that image over NVLink, and sat_adam_step_dev_bf16grad consumes
  * the bf16 sums (same update as sat_adam_step_dev otherwise).  Every rank sees the same sums, so replicas stay identical. */
 int sat_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
+/* One slice [0, n) of the same update (gradient fp32 or bf16: grad_dtype = SAT_DTYPE_*), the step counter incremented only when
+ * tick != 0 (n = 0: tick only): parameters whose gradients are final early are updated on another stream under the rest of the
+ * backward pass, one tick at the end. */
+int sat_adam_step_dev_part(float* param, const void* grad, int grad_dtype, float* exp_avg, float* exp_avg_sq, int64_t n,
+                           const float* hyper, int32_t* step_count, int tick, void* stream);
 int sat_adam_step_dev_bf16grad(float* param, const void* grad_bf16, float* exp_avg, float* exp_avg_sq, int64_t n, const float* hyper,
                                int32_t* step_count, void* stream);
 

@@ -143,6 +143,15 @@ int sat_wait_early_grads(void* stream) {
     return SAT_OK;
 }
 
+/* ... and until it has written every gradient except attention.W.* / attention.v.* (the end of the backward tail's side chain). */
+int sat_wait_side_grads(void* stream) {
+    SAT_TRY(require_sm100());
+    SideStream* ss = nullptr;
+    SAT_TRY(side_stream(&ss));
+    SAT_CHECK_CUDA(cudaStreamWaitEvent(reinterpret_cast<cudaStream_t>(stream), ss->side, 0));
+    return SAT_OK;
+}
+
 /* utils.py:44-80 (sequence_accuracy) in one pass: rank[r] = #{v : logits[r, v] > logits[r, targets[r]]} for `rows` rows of V
  * logits with row pitch ld.  The target is among the top k exactly when rank < k (a tie counts for the target). */
 int sat_logit_rank(const float* logits, int64_t ld, int64_t rows, int V, const int64_t* targets, int32_t* rank, void* stream) {
@@ -396,6 +405,26 @@ int sat_adam_step_dev_bf16grad(float* param, const void* grad_bf16, float* exp_a
                                int32_t* step_count, void* stream) {
     return adam_step_dev_any(param, grad_bf16, SAT_DTYPE_BF16, exp_avg, exp_avg_sq, n, hyper, step_count, stream);
 }
+/* One slice of the update: the same arithmetic on elements [0, n) of the given pointers, gradient fp32 or bf16 (grad_dtype =
+ * SAT_DTYPE_*); the step counter is incremented only when tick != 0 (n may be 0: tick only).  Lets a caller update the parameters
+ * whose gradients are final early on another stream under the rest of the backward pass, and tick once at the end. */
+int sat_adam_step_dev_part(float* param, const void* grad, int grad_dtype, float* exp_avg, float* exp_avg_sq, int64_t n,
+                           const float* hyper, int32_t* step_count, int tick, void* stream) {
+    SAT_TRY(require_sm100());
+    SAT_REQUIRE(hyper && step_count, "sat_adam_step_dev_part: null hyper / step_count");
+    SAT_REQUIRE(grad_dtype == SAT_DTYPE_F32 || grad_dtype == SAT_DTYPE_BF16, "sat_adam_step_dev_part: bad grad dtype %d", grad_dtype);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (n > 0) {
+        if (grad_dtype == SAT_DTYPE_F32)
+            adam_dev_kernel<float><<<misc::grid_for(n), 256, 0, st>>>(param, reinterpret_cast<const float*>(grad), exp_avg, exp_avg_sq, n, hyper, step_count);
+        else
+            adam_dev_kernel<bf16><<<misc::grid_for(n), 256, 0, st>>>(param, reinterpret_cast<const bf16*>(grad), exp_avg, exp_avg_sq, n, hyper, step_count);
+    }
+    if (tick) adam_tick_kernel<<<1, 1, 0, st>>>(step_count);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
+}
+
 /* Gradient compression for the data-parallel exchange: dst (bf16) = src (fp32), n elements. */
 int sat_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream) {
     SAT_TRY(require_sm100());

@@ -50,7 +50,7 @@ static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 // created once per host thread and device; the caller's stream forks into it before the loop and joins after it.
 // ---------------------------------------------------------------------------------------------------
 extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap;
-struct SideStream { cudaStream_t s; cudaEvent_t fork, join, attn_done[2], early; bool ok; };
+struct SideStream { cudaStream_t s; cudaEvent_t fork, join, attn_done[2], early, side; bool ok; };
 static inline int side_stream(SideStream** out) {
     static thread_local SideStream cache[32] = {};
     int dev = 0;
@@ -64,6 +64,7 @@ static inline int side_stream(SideStream** out) {
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.attn_done[0], cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.attn_done[1], cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.early, cudaEventDisableTiming));
+        SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.side, cudaEventDisableTiming));
         ss.ok = true;
     }
     *out = &ss;
@@ -716,6 +717,9 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         SAT_TRY(gemm<T>(sb, w.dlog, Vp, false, out_in, H, false, V, H, BT, e));          // dW = dlog^T X
     }
     if (g_out_b) SAT_TRY(misc::colsum<T>(sb, w.dlog, Vp, BT, V, g_out_b, csb, w.csum_floats));
+    // every gradient except the encoder projection's (attention.W.*, attention.v.*: main chain) is final here: data-parallel
+    // callers all-reduce them, and the optimizer updates them, under the rest of the main chain (sat_wait_side_grads)
+    SAT_CHECK_CUDA(cudaEventRecord(tl->side, sb));
     if (g_tail_overlap) {
         SAT_CHECK_CUDA(cudaEventRecord(tl->join, sb));
         SAT_CHECK_CUDA(cudaStreamWaitEvent(st, tl->join, 0));

@@ -504,9 +504,34 @@ inline EncodeTiledFn get_encode_fn() {
     return fn;
 }
 
+inline int make_map_uncached(CUtensorMap* map, const void* ptr, uint64_t inner, uint64_t outer, int64_t ld,
+                             uint32_t box_inner, uint32_t box_outer);
+// Tensor maps are a pure function of (pointer, shape, pitch, box, element type): a small per-thread direct-mapped cache saves the
+// driver call for the ~90 GEMMs of an eagerly launched train step, whose operands live at fixed workspace addresses (under CUDA-graph
+// replay the maps are baked into the captured kernel parameters and nothing is encoded at all).
+struct MapKey { const void* ptr; uint64_t inner, outer; int64_t ld; uint32_t bi, bo, esz; };
+struct MapSlot { MapKey k; CUtensorMap m; bool ok; };
+inline MapSlot* map_slot(const MapKey& k) {
+    static thread_local MapSlot cache[256] = {};
+    uint64_t h = ((uint64_t)(uintptr_t)k.ptr >> 7) * 0x9E3779B97F4A7C15ull ^ (k.inner * 131 + k.outer) * 0xC2B2AE3D27D4EB4Full ^ ((uint64_t)k.bo << 20 | k.bi << 4 | k.esz);
+    return &cache[(h >> 32) & 255];
+}
+inline bool map_key_eq(const MapKey& a, const MapKey& b) {
+    return a.ptr == b.ptr && a.inner == b.inner && a.outer == b.outer && a.ld == b.ld && a.bi == b.bi && a.bo == b.bo && a.esz == b.esz;
+}
+
 // 2-D bf16 tensor map: `inner` contiguous elements per row, `outer` rows, row pitch ld elements.
 inline int make_map(CUtensorMap* map, const void* ptr, uint64_t inner, uint64_t outer, int64_t ld,
                     uint32_t box_inner, uint32_t box_outer) {
+    const MapKey key{ptr, inner, outer, ld, box_inner, box_outer, 2u};
+    MapSlot* slot = map_slot(key);
+    if (slot->ok && map_key_eq(slot->k, key)) { *map = slot->m; return SAT_OK; }
+    SAT_TRY(make_map_uncached(map, ptr, inner, outer, ld, box_inner, box_outer));
+    slot->k = key; slot->m = *map; slot->ok = true;
+    return SAT_OK;
+}
+inline int make_map_uncached(CUtensorMap* map, const void* ptr, uint64_t inner, uint64_t outer, int64_t ld,
+                             uint32_t box_inner, uint32_t box_outer) {
     EncodeTiledFn fn = get_encode_fn();
     if (!fn) { sat_set_error("cuTensorMapEncodeTiled entry point not found"); return SAT_ERR_CUDA; }
     if (((uintptr_t)ptr & 15) || (ld % 8)) {

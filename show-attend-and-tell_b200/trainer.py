@@ -30,6 +30,8 @@ from . import _lib
 class FusedTrainStep:
     # gradients that are final ~160 us before sat_decoder_backward's last kernel (sat_wait_early_grads): 62 % of the bytes at c2
     EARLY_KEYS = ("init_h.weight", "init_h.bias", "init_c.weight", "init_c.bias", "lstm.weight_ih", "lstm.weight_hh")
+    # gradients the MAIN chain of the backward tail writes last (sum over t -> dW_att GEMM -> column sums)
+    LAST_KEYS = ("attention.W.weight", "attention.W.bias", "attention.v.weight", "attention.v.bias")
 
     def __init__(self, decoder, lr=1e-4, betas=(0.9, 0.999), eps=1e-8, alpha_c=1.0, process_group=None,
                  distributed=None, step_size=None, gamma=0.1, use_cuda_graph=False, grad_exchange_dtype=torch.float32):
@@ -41,8 +43,11 @@ class FusedTrainStep:
         unused = decoder.unused_parameter_keys()
         keys = [n for n, p in decoder.named_parameters() if p.requires_grad and n not in unused]
         # the gradients sat_decoder_backward finishes early go first in the flat buffer: one contiguous all-reduce bucket
+        # ... then everything the side chain of the backward tail produces, and last the encoder projection's gradients, which
+        # the main chain finishes at the very end (sat_wait_side_grads): three contiguous buckets
         early = [k for k in keys if k in self.EARLY_KEYS]
-        self.train_keys = early + [k for k in keys if k not in self.EARLY_KEYS]
+        last = [k for k in keys if k in self.LAST_KEYS]
+        self.train_keys = early + [k for k in keys if k not in self.EARLY_KEYS and k not in self.LAST_KEYS] + last
         named = dict(decoder.named_parameters())
         dev = next(decoder.parameters()).device
         self.device = dev
@@ -53,6 +58,7 @@ class FusedTrainStep:
         n = off
         self.offsets = offsets
         self.n_early = max([offsets[k] + ((named[k].numel() + 3) & ~3) for k in early], default=0)
+        self.n_side = min([offsets[k] for k in last], default=n)          # [n_early, n_side): side-chain gradients; [n_side, n): last
         self.overlap_allreduce = True
         self._comm_stream = None
         # grad_exchange_dtype = torch.bfloat16: the gradients cross NVLink in half the bytes (cast -> all-reduce -> Adam reads the
@@ -219,18 +225,47 @@ class FusedTrainStep:
         if not (self.overlap_allreduce and self.flat_grad.is_cuda and 0 < self.n_early < self.n):
             self._exchange(0, self.n).wait()
             return
-        # two buckets: the early one is reduced on a side stream as soon as the backward pass has written it (under the rest
-        # of the backward tail), the rest on the current stream after the pass; Adam then waits for both
+        self._finish_step(False)
+
+    def _finish_step(self, optimizer_step):
+        """Exchange + update, bucket by bucket as sat_decoder_backward finishes them.  On the comm stream: the early bucket
+        (initial-state and LSTM weights, final ~160 us before the pass ends) and the side-chain bucket (everything but the
+        encoder projection) are all-reduced as soon as their events fire and their parameters are updated right away -- under
+        the main chain's `sum_t dpre` pass and `dW_att` GEMM; on the caller's stream: the last bucket (attention.W / v, 8 % of the
+        bytes at c2) after the pass, its update, the join and ONE tick of the step counter.  With world == 1 only the updates
+        move (Adam's 62 us at c2 is otherwise serialised behind the pass)."""
+        L = _lib.lib()
         dev = self.flat_grad.device
         if self._comm_stream is None:
             self._comm_stream = torch.cuda.Stream(dev)
-        cs = self._comm_stream
-        _lib.check(_lib.lib().sat_wait_early_grads(cs.cuda_stream), "sat_wait_early_grads")
+        cs, cur = self._comm_stream, torch.cuda.current_stream(dev)
+        nE, nS, n = self.n_early, self.n_side, self.n
+        dist_on = self.world > 1
+
+        def adam(lo, hi, stream, tick=0):
+            g = self.reduced_grad()
+            _lib.check(L.sat_adam_step_dev_part(self.flat_param.data_ptr() + 4 * lo, g.data_ptr() + g.element_size() * lo,
+                                                _lib.dtype_code(g.dtype), self.exp_avg.data_ptr() + 4 * lo,
+                                                self.exp_avg_sq.data_ptr() + 4 * lo, hi - lo, self.hyper.data_ptr(),
+                                                self.step_dev.data_ptr(), tick, stream.cuda_stream), "sat_adam_step_dev_part")
+
+        _lib.check(L.sat_wait_early_grads(cs.cuda_stream), "sat_wait_early_grads")
         with torch.cuda.stream(cs):
-            early = self._exchange(0, self.n_early)
-        late = self._exchange(self.n_early, self.n)
-        late.wait()
-        early.wait()                                   # the current stream waits for the early bucket
+            if dist_on and nE > 0:
+                self._exchange(0, nE).wait()
+        _lib.check(L.sat_wait_side_grads(cs.cuda_stream), "sat_wait_side_grads")
+        with torch.cuda.stream(cs):
+            if dist_on and nS > nE:
+                self._exchange(nE, nS).wait()
+            if optimizer_step and nS > 0:
+                adam(0, nS, cs)
+        if dist_on and n > nS:
+            self._exchange(nS, n).wait()
+        if optimizer_step and n > nS:
+            adam(nS, n, cur)
+        cur.wait_stream(cs)
+        if optimizer_step:
+            adam(0, 0, cur, tick=1)
 
     def reduced_grad(self):
         """The buffer Adam consumes after sync_grads(): the fp32 flat gradient, or its all-reduced bf16 image."""
@@ -278,6 +313,9 @@ class FusedTrainStep:
         a = self._args(img_features, captions, dropout_mask)
         _lib.check(L.sat_decoder_forward(C.byref(a)), "sat_decoder_forward")
         _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(self._grad_struct())), "sat_decoder_backward")
+        if self.overlap_allreduce and self.flat_grad.is_cuda and 0 < self.n_early < self.n:
+            self._finish_step(optimizer_step)
+            return
         self.sync_grads()
         if optimizer_step:
             g = self.reduced_grad()
@@ -316,7 +354,8 @@ class FusedTrainStep:
         tied to the addresses of the feature and caption buffers: feed a training loop from a fixed set of device buffers
         (double buffering = two graphs)."""
         key = (img_features.data_ptr(), captions.data_ptr(), tuple(img_features.shape), tuple(img_features.stride()),
-               img_features.dtype, tuple(captions.shape), captions.stride(0), bool(self.dec.training))
+               img_features.dtype, tuple(captions.shape), captions.stride(0), bool(self.dec.training), float(self.alpha_c),
+               float(self.dec.dropout.p))          # scalars that are baked into the captured kernel parameters
         g = self._graphs.get(key)
         if g is not None:
             g[0].replay()

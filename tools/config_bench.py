@@ -54,7 +54,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--configs", default="c2,c3-D512,c3-D2048,c5")
     ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=6, help=">= 6: each of the two batch buffers needs three steps before its CUDA graph exists")
+    ap.add_argument("--ado", type=int, default=0, help="1 = advanced deep output (the flag set train_models.py passes)")
+    ap.add_argument("--graph", type=int, default=1, help="1 = replay the step as one CUDA graph (what bench.py does)")
     args = ap.parse_args()
     from sat_b200.decoder import Decoder
     from sat_b200.trainer import FusedTrainStep
@@ -67,10 +69,10 @@ def main():
         torch.manual_seed(42)
         if c["bert"]:
             stub_bert()
-        dec = Decoder(c["V"], c["D"], tf=c["tf"], ado=False, bert=c["bert"], attention=True, compute_dtype=torch.bfloat16,
+        dec = Decoder(c["V"], c["D"], tf=c["tf"], ado=bool(args.ado), bert=c["bert"], attention=True, compute_dtype=torch.bfloat16,
                       gate=c["gate"]).to(dev).train()
         H, V, B, T, D = dec.embedding_size, dec.vocabulary_size, c["B"], c["T"], c["D"]
-        tr = FusedTrainStep(dec, lr=1e-4, alpha_c=1.0, distributed=False)
+        tr = FusedTrainStep(dec, lr=1e-4, alpha_c=1.0, distributed=False, use_cuda_graph=bool(args.graph))
         batches = []
         for i in range(2):
             g = torch.Generator().manual_seed(42 + i)
@@ -93,7 +95,8 @@ def main():
         floor_ms = attn_bytes / (peak * 1e9) * 1e3
         lv = [float(x) for x in loss.tolist()]
         print(json.dumps({"config": name, "shape": {"B": B, "L": L, "D": D, "H": H, "V": V, "T": T, "tf": c["tf"], "gate": c["gate"],
-                                                    "frozen_embedding": c["bert"]},
+                                                    "frozen_embedding": c["bert"], "ado": bool(args.ado)},
+                          "launch": "cuda graph" if tr.graph_replays else "eager",
                           "dtype": "bf16", "ms_per_step": ms, "captions_per_s": B / (ms / 1e3),
                           "attention_algorithmic_bytes": attn_bytes, "hbm_floor_ms": floor_ms, "step_frac_of_hbm_floor": floor_ms / ms,
                           "peak_gbs": peak, "peak_source": peak_src, "loss": lv[2], "finite": all(map(lambda x: x == x and abs(x) < 1e30, lv)),
