@@ -60,6 +60,11 @@ class FusedTrainStep:
         self.n_early = max([offsets[k] + ((named[k].numel() + 3) & ~3) for k in early], default=0)
         self.n_side = min([offsets[k] for k in last], default=n)          # [n_early, n_side): side-chain gradients; [n_side, n): last
         self.overlap_allreduce = True
+        # buckets = 2 (default): early bucket under the backward tail, the rest after the pass, one Adam launch.  buckets = 3: the
+        # side-chain bucket is exchanged AND updated under the main chain as well (_finish_step).  Measured on 8 x B200 at c2
+        # (profiles/r2_bench_c2_n8*.json): 3.78 ms per step with 2 buckets, 3.82 ms with 3 -- the extra NCCL kernels and the early
+        # Adam compete with the HBM-bound `sum_t dpre` pass they run beside; on one GPU the two are equal (3.62 ms).
+        self.buckets = 2
         self._comm_stream = None
         # grad_exchange_dtype = torch.bfloat16: the gradients cross NVLink in half the bytes (cast -> all-reduce -> Adam reads the
         # bf16 sums); every rank still applies identical updates.  Only used when world > 1.
@@ -225,7 +230,21 @@ class FusedTrainStep:
         if not (self.overlap_allreduce and self.flat_grad.is_cuda and 0 < self.n_early < self.n):
             self._exchange(0, self.n).wait()
             return
-        self._finish_step(False)
+        if self.buckets == 3:
+            self._finish_step(False)
+            return
+        # two buckets: the early one is reduced on a side stream as soon as the backward pass has written it (under the rest
+        # of the backward tail), the rest on the current stream after the pass; Adam then waits for both
+        dev = self.flat_grad.device
+        if self._comm_stream is None:
+            self._comm_stream = torch.cuda.Stream(dev)
+        cs = self._comm_stream
+        _lib.check(_lib.lib().sat_wait_early_grads(cs.cuda_stream), "sat_wait_early_grads")
+        with torch.cuda.stream(cs):
+            early = self._exchange(0, self.n_early)
+        late = self._exchange(self.n_early, self.n)
+        late.wait()
+        early.wait()                                   # the current stream waits for the early bucket
 
     def _finish_step(self, optimizer_step):
         """Exchange + update, bucket by bucket as sat_decoder_backward finishes them.  On the comm stream: the early bucket
@@ -313,7 +332,7 @@ class FusedTrainStep:
         a = self._args(img_features, captions, dropout_mask)
         _lib.check(L.sat_decoder_forward(C.byref(a)), "sat_decoder_forward")
         _lib.check(L.sat_decoder_backward(C.byref(a), C.byref(self._grad_struct())), "sat_decoder_backward")
-        if self.overlap_allreduce and self.flat_grad.is_cuda and 0 < self.n_early < self.n:
+        if self.buckets == 3 and self.overlap_allreduce and self.flat_grad.is_cuda and 0 < self.n_early < self.n:
             self._finish_step(optimizer_step)
             return
         self.sync_grads()
@@ -355,7 +374,7 @@ class FusedTrainStep:
         (double buffering = two graphs)."""
         key = (img_features.data_ptr(), captions.data_ptr(), tuple(img_features.shape), tuple(img_features.stride()),
                img_features.dtype, tuple(captions.shape), captions.stride(0), bool(self.dec.training), float(self.alpha_c),
-               float(self.dec.dropout.p))          # scalars that are baked into the captured kernel parameters
+               float(self.dec.dropout.p), int(self.buckets))          # scalars / launch order that are baked into the captured kernel parameters
         g = self._graphs.get(key)
         if g is not None:
             g[0].replay()

@@ -282,6 +282,29 @@ def test_graph_step_draws_fresh_dropout_masks():
     assert len({round(v, 6) for v in vals[2:]}) > 1, vals       # replays see different masks
 
 
+def test_three_bucket_update_equals_default():
+    """FusedTrainStep.buckets = 3 (side-chain gradients applied on the comm stream under the main chain of the backward tail, one
+    tick at the end) gives the same parameters as the default single Adam launch."""
+    from sat_b200.decoder import Decoder
+    from sat_b200.trainer import FusedTrainStep
+    V, D, B, L, T = 400, 512, 40, 196, 4
+    P = synth.make_params(V, D, 512, seed=19, emb_scale=0.5)
+    a, cap = synth.make_inputs(B, L, D, T, V, seed=19)
+    ad, capd = a.cuda().to(torch.bfloat16), cap.cuda()
+    out = {}
+    for nb in (2, 3):
+        dec = Decoder(V, D, tf=True, attention=True, compute_dtype=torch.bfloat16)
+        dec.load_state_dict(P, strict=True)
+        tr = FusedTrainStep(dec.cuda().eval(), lr=1e-3, distributed=False)
+        tr.buckets = nb
+        for _ in range(3):
+            tr.step(ad, capd)
+        torch.cuda.synchronize()
+        out[nb] = (tr.flat_param.clone(), int(tr.step_dev.item()))
+    assert out[2][1] == out[3][1] == 3
+    assert (out[2][0] - out[3][0]).abs().max().item() <= 2e-4      # embedding scatter-add atomics may reorder; Adam itself is elementwise
+
+
 def test_param_storage_guard():
     from sat_b200.decoder import Decoder
     from sat_b200.trainer import FusedTrainStep
