@@ -277,6 +277,12 @@ class Decoder(nn.Module):
     def forward(self, img_features, captions, *, dropout_masks=None):
         captions = self._check_inputs(img_features, captions, "forward")
         B, T = img_features.shape[0], captions.shape[1] - 1
+        if B == 0 or T <= 0:
+            # decoder.py:92-93 allocate zero tensors and the `for t in range(max_timespan)` loop (decoder.py:96) never runs: captions
+            # holding only <start>, or an empty batch, give empty preds / alphas that no parameter reaches
+            T = max(T, 0)
+            return (torch.zeros(B, T, self.vocabulary_size, device=img_features.device),
+                    torch.zeros(B, T, img_features.shape[1], device=img_features.device))
         mask = self._dropout_mask(B, T, img_features.device, dropout_masks)
         params = tuple(p for _, p in self.named_parameters())
         need_grad = torch.is_grad_enabled() and (img_features.requires_grad or any(p.requires_grad for p in params))
