@@ -49,11 +49,13 @@ int sat_set_pdl(int on);
 /* tuning knob: 1 (default) = the per-step GEMMs of the decoder loop load their weight operand with the L2 evict_last hint (it
  * survives the attention kernel's 257 MB stream until the next step) and request its first tiles before the PDL wait */
 int sat_set_gemm_static_weights(int on);
-/* tuning knob: 1 (default) = sat_decoder_backward runs the work after the BPTT loop as two independent chains on two streams
+/* tuning knob: 1 = sat_decoder_backward runs the work after the BPTT loop as two independent chains on two streams
  * (sum over t + dW_att on the caller's stream, the small weight-gradient GEMMs / column sums on an internal side stream that
  * is joined back before the call returns), and sat_decoder_forward runs the initial-state / embedding work on that side
- * stream beside the encoder-projection GEMM; 0 = one chain; 2 = like 1 with a register-thin, shared-memory-staged sum over t
- * that GEMM CTAs of the side chain can run beside (experimental: measured slower) */
+ * stream beside the encoder-projection GEMM; 3 (default) = like 1, and the side chain itself forks: embedding, [U; f_beta] and
+ * output-layer gradients on a second internal stream beside the initial-state and LSTM weight gradients (3.61 -> 3.56 ms per
+ * c2 step); 0 = one chain; 2 = like 1 with a register-thin, shared-memory-staged sum over t that GEMM CTAs of the side chain
+ * can run beside (experimental: measured slower) */
 int sat_set_tail_overlap(int on);
 /* tuning knob: 1 (default) = with attention on, the LSTM cell backward of step t-1 runs in the epilogue of step t's dh GEMM;
  * 0 = the pointwise kernel is launched every step */

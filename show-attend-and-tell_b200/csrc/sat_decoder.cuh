@@ -50,7 +50,7 @@ static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 // created once per host thread and device; the caller's stream forks into it before the loop and joins after it.
 // ---------------------------------------------------------------------------------------------------
 extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap;
-struct SideStream { cudaStream_t s; cudaEvent_t fork, join, attn_done[2], early, side; bool ok; };
+struct SideStream { cudaStream_t s, s2; cudaEvent_t fork, join, join2, attn_done[2], early, side; bool ok; };
 static inline int side_stream(SideStream** out) {
     static thread_local SideStream cache[32] = {};
     int dev = 0;
@@ -59,8 +59,10 @@ static inline int side_stream(SideStream** out) {
     SideStream& ss = cache[dev];
     if (!ss.ok) {
         SAT_CHECK_CUDA(cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking));
+        SAT_CHECK_CUDA(cudaStreamCreateWithFlags(&ss.s2, cudaStreamNonBlocking));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming));
+        SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.join2, cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.attn_done[0], cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.attn_done[1], cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.early, cudaEventDisableTiming));
@@ -132,6 +134,8 @@ struct DecWs {
     float* gscratch;
     float* csum;
     float* csum2;
+    float* csum3;
+    float* gscratch2;
     float* dcomb;    // ado (T,B,H) fp32
     T *dP1, *dP2;    // ado (T,B,H)
     float* dctx_all; // ado (T,B,D) fp32
@@ -190,6 +194,8 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
         if (w.csum_floats < (int64_t)4 * 148 * H) w.csum_floats = (int64_t)4 * 148 * H;      // sum_over_t_colsum: one row per block
         TK(csum, w.csum_floats, float);
         TK(csum2, w.csum_floats, float);      // column-sum scratch of the side chain of the backward tail
+        TK(csum3, w.csum_floats, float);      // ... and of its second branch
+        TK(gscratch2, (H + D) * H, float);
         TK(dcomb, a.ado ? B * Tn * H : 0, float); TK(dP1, a.ado ? B * Tn * H : 0, T); TK(dP2, a.ado ? B * Tn * H : 0, T);
         TK(dctx_all, a.ado ? B * Tn * D : 0, float);
     }
@@ -622,9 +628,17 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     SAT_TRY(side_stream(&tl));
     cudaStream_t sb = g_tail_overlap ? tl->s : st;
     float* csb = g_tail_overlap ? w.csum2 : w.csum;
+    // g_tail_overlap == 3: the side chain itself forks.  Its launches are small and mutually independent (each GEMM covers 64-80
+    // of the 148 SMs), so embedding / [U; f_beta] / output-layer gradients run on a second side stream beside the initial-state
+    // and gate-weight gradients, with their own scratch (gscratch2 / csum3).
+    const bool three = g_tail_overlap == 3;
+    cudaStream_t sc = three ? tl->s2 : sb;
+    float* csc = three ? w.csum3 : csb;
+    float* gsc = three ? w.gscratch2 : w.gscratch;
     if (g_tail_overlap) {
         SAT_CHECK_CUDA(cudaEventRecord(tl->fork, st));
         SAT_CHECK_CUDA(cudaStreamWaitEvent(sb, tl->fork, 0));
+        if (three) SAT_CHECK_CUDA(cudaStreamWaitEvent(sc, tl->fork, 0));
     }
     if (a.attention) {      // main chain
         // encoder projection: dW (H x D) = (sum_t dpre)^T a ; db_W = colsum ; dv, db_v
@@ -694,29 +708,33 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
     }
     // embedding: dE = dG W_gx (+ dcomb for ado), scatter-add by token (skipped when frozen / NULL: Q23)
     if (g.embedding) {
-        SAT_CHECK_CUDA(cudaMemsetAsync(g.embedding, 0, (size_t)V * H * 4, sb));
+        SAT_CHECK_CUDA(cudaMemsetAsync(g.embedding, 0, (size_t)V * H * 4, sc));
         auto e = lin<T>(BT, H, nullptr, SAT_ACT_NONE, nullptr, 0, w.dE, H, a.ado ? w.dcomb : nullptr, H);
-        SAT_TRY(gemm<T>(sb, w.dG, 4 * H, true, w.w_gx, H, false, BT, H, 4 * H, e));
-        if (a.tf) misc::scatter_add_bt_kernel<T><<<BT, 128, 0, sb>>>(g.embedding, H, w.dE, a.captions, a.cap_stride, B, V);
-        else misc::scatter_add_rows_kernel<T><<<BT, 128, 0, sb>>>(g.embedding, H, w.dE, w.tok_in, V);
+        SAT_TRY(gemm<T>(sc, w.dG, 4 * H, true, w.w_gx, H, false, BT, H, 4 * H, e));
+        if (a.tf) misc::scatter_add_bt_kernel<T><<<BT, 128, 0, sc>>>(g.embedding, H, w.dE, a.captions, a.cap_stride, B, V);
+        else misc::scatter_add_rows_kernel<T><<<BT, 128, 0, sc>>>(g.embedding, H, w.dE, w.tok_in, V);
         SAT_CHECK_CUDA(cudaGetLastError());
     }
     if (a.attention) {
         // [U ; f_beta] grads: dW_uf ((H+D) x H) = dUF^T Hprev  (Hprev = ZH[:, D:], steps 0..T-1)
-        auto e = lin<T>(H + D, H, nullptr, SAT_ACT_NONE, w.gscratch, H, nullptr, 0);
-        SAT_TRY(gemm<T>(sb, w.dUF, H + D, false, w.ZH + D, zw, false, H + D, H, BT, e));
-        if (g.att_U_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_w, w.gscratch, (size_t)H * H * 4, cudaMemcpyDeviceToDevice, sb));
-        if (g.f_beta_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_w, w.gscratch + (size_t)H * H, (size_t)D * H * 4, cudaMemcpyDeviceToDevice, sb));
-        SAT_TRY(misc::colsum<T>(sb, w.dUF, H + D, BT, H + D, w.gscratch, csb, w.csum_floats));
-        if (g.att_U_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_b, w.gscratch, (size_t)H * 4, cudaMemcpyDeviceToDevice, sb));
-        if (g.f_beta_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_b, w.gscratch + H, (size_t)D * 4, cudaMemcpyDeviceToDevice, sb));
+        auto e = lin<T>(H + D, H, nullptr, SAT_ACT_NONE, gsc, H, nullptr, 0);
+        SAT_TRY(gemm<T>(sc, w.dUF, H + D, false, w.ZH + D, zw, false, H + D, H, BT, e));
+        if (g.att_U_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_w, gsc, (size_t)H * H * 4, cudaMemcpyDeviceToDevice, sc));
+        if (g.f_beta_w) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_w, gsc + (size_t)H * H, (size_t)D * H * 4, cudaMemcpyDeviceToDevice, sc));
+        SAT_TRY(misc::colsum<T>(sc, w.dUF, H + D, BT, H + D, gsc, csc, w.csum_floats));
+        if (g.att_U_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.att_U_b, gsc, (size_t)H * 4, cudaMemcpyDeviceToDevice, sc));
+        if (g.f_beta_b) SAT_CHECK_CUDA(cudaMemcpyAsync(g.f_beta_b, gsc + H, (size_t)D * 4, cudaMemcpyDeviceToDevice, sc));
     }
     // output layer weights (deferred from before the loop)
     if (g_out_w) {
         auto e = lin<T>(V, H, nullptr, SAT_ACT_NONE, g_out_w, H, nullptr, 0);
-        SAT_TRY(gemm<T>(sb, w.dlog, Vp, false, out_in, H, false, V, H, BT, e));          // dW = dlog^T X
+        SAT_TRY(gemm<T>(sc, w.dlog, Vp, false, out_in, H, false, V, H, BT, e));          // dW = dlog^T X
     }
-    if (g_out_b) SAT_TRY(misc::colsum<T>(sb, w.dlog, Vp, BT, V, g_out_b, csb, w.csum_floats));
+    if (g_out_b) SAT_TRY(misc::colsum<T>(sc, w.dlog, Vp, BT, V, g_out_b, csc, w.csum_floats));
+    if (three) {
+        SAT_CHECK_CUDA(cudaEventRecord(tl->join2, sc));
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(sb, tl->join2, 0));
+    }
     // every gradient except the encoder projection's (attention.W.*, attention.v.*: main chain) is final here: data-parallel
     // callers all-reduce them, and the optimizer updates them, under the rest of the main chain (sat_wait_side_grads)
     SAT_CHECK_CUDA(cudaEventRecord(tl->side, sb));
