@@ -460,7 +460,10 @@ def run_ours(args, rank, world, local_rank):
     s = 2  # bf16
     Lc, D, H = CFG["L"], CFG["D"], CFG["H"]
     bytes_fwd = B * Lc * (H + D) * s
-    bytes_bwd = B * (Lc * (H + D) * s + Lc * H * s)      # a, Wa read once + this step's dpre written once
+    # a, Wa read once + this step's score gradients de (B x L fp32) written once: sum_t dpre is rebuilt after the loop in one
+    # pass over Wa (misc::dpre_sum, library default sat_set_dpre_recompute(1)); round 1 wrote a (B, L, H) dpre slab per step
+    bytes_bwd = B * (Lc * (H + D) * s + Lc * 4)
+    bytes_dpre_sum = 2 * B * Lc * H * s                  # the rebuild: Wa read, sum_t dpre written (once per train step)
     peak, peak_src = read_peaks()
     kern = {}
     for name, idx, nbytes in (("attn_step_fwd", 0, bytes_fwd), ("attn_step_bwd", 1, bytes_bwd)):
@@ -479,8 +482,8 @@ def run_ours(args, rank, world, local_rank):
     roofline = {"bound": "hbm", "kernel": dom, "achieved": kern[dom]["achieved_gbs"], "peak": peak, "unit": "GB/s",
                 "frac": kern[dom]["achieved_gbs"] / peak, "traffic": traffic, "peak_source": peak_src,
                 "share_of_step": kern[dom]["ms_per_step"] / ms_step, "kernels": kern,
-                "step_hbm_floor_ms": T * (bytes_fwd + bytes_bwd + B * Lc * H * s) / peak / 1e6,
-                "step_frac_of_hbm_floor": T * (bytes_fwd + bytes_bwd + B * Lc * H * s) / peak / 1e6 / ms_step}
+                "step_hbm_floor_ms": (T * (bytes_fwd + bytes_bwd) + bytes_dpre_sum) / peak / 1e6,
+                "step_frac_of_hbm_floor": (T * (bytes_fwd + bytes_bwd) + bytes_dpre_sum) / peak / 1e6 / ms_step}
 
     launches, exposed = count_my_launches(lambda: trainer.step(*dev_batches[0]))
     trainer.use_cuda_graph = graph_was

@@ -57,6 +57,12 @@ int sat_set_gemm_static_weights(int on);
  * c2 step); 0 = one chain; 2 = like 1 with a register-thin, shared-memory-staged sum over t that GEMM CTAs of the side chain
  * can run beside (experimental: measured slower) */
 int sat_set_tail_overlap(int on);
+/* tuning knob: 1 (default) = with the streaming attention kernels, a backward decode step stores only its score gradients
+ * de_t (B x L floats) and the sum over t of the pre-activation gradients (the input of the encoder-projection weight gradient) is
+ * rebuilt after the loop in one pass over Wa; 0 = every step writes its (B, L, H) slab and one pass sums the T slabs (round-1
+ * scheme: 2 x T x B x L x H x sizeof(T) more HBM traffic, T x B x L x H x sizeof(T) more workspace).  Read by
+ * sat_decoder_workspace_bytes: set it before sizing the workspace. */
+int sat_set_dpre_recompute(int on);
 /* tuning knob: 1 (default) = with attention on, the LSTM cell backward of step t-1 runs in the epilogue of step t's dh GEMM;
  * 0 = the pointwise kernel is launched every step */
 int sat_set_fused_cell_backward(int on);

@@ -72,7 +72,7 @@ class BeamArgs(C.Structure):
 
 _LIB = None
 
-EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_set_fp32_gemm_mode", "sat_set_gemm_wide_tile", "sat_set_attn_generic", "sat_set_attn_partition", "sat_set_pdl", "sat_set_gemm_static_weights", "sat_set_tail_overlap", "sat_set_fused_cell_backward", "sat_gemm_phase_stamps", "sat_set_decoder_split", "sat_set_decoder_split_sms", "sat_set_gemm_splitk", "sat_set_attn_l2_policy", "sat_set_attn_prefetch", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_fwd_static", "sat_attn_step_bwd", "sat_attn_scratch_bytes",
+EXPORTS = ["sat_last_error", "sat_version", "sat_set_force_simt", "sat_set_fp32_gemm_mode", "sat_set_gemm_wide_tile", "sat_set_attn_generic", "sat_set_attn_partition", "sat_set_pdl", "sat_set_gemm_static_weights", "sat_set_tail_overlap", "sat_set_dpre_recompute", "sat_set_fused_cell_backward", "sat_gemm_phase_stamps", "sat_set_decoder_split", "sat_set_decoder_split_sms", "sat_set_gemm_splitk", "sat_set_attn_l2_policy", "sat_set_attn_prefetch", "sat_gemm", "sat_attn_step_fwd", "sat_attn_step_fwd_static", "sat_attn_step_bwd", "sat_attn_scratch_bytes",
            "sat_decoder_workspace_bytes", "sat_decoder_logits", "sat_wait_early_grads", "sat_wait_side_grads", "sat_logit_rank", "sat_decoder_forward", "sat_decoder_backward", "sat_beam_workspace_bytes",
            "sat_beam_search", "sat_adam_step", "sat_adam_step_dev", "sat_adam_step_dev_bf16grad", "sat_cast_f32_to_bf16", "sat_adam_step_dev_part", "sat_count_tokens", "sat_argmax_rows", "sat_gather_items",
            "sat_profile", "sat_profile_read"]

@@ -322,6 +322,8 @@ struct BwdParams {
     float* dbv_acc;         // (B)   fp32
     float* da_acc;          // (B, L, D) fp32 or null
     void* dpre_out;         // T (B, L, H): this step's dpre written once (streaming kernel); null -> accumulate into dwa_acc
+    float* de_out;          // streaming kernel: (B, L) fp32 score gradients de of this step (or null).  With de_out set dpre_out may
+                            // be null: the caller rebuilds sum_t dpre from de / uf / wa afterwards (misc::dpre_sum)
     const float* ctx32;     // streaming kernel: fp32 (B, ld_c32) un-gated context saved by the forward kernel
     int64_t ld_c32;
     float* s_part;          // streaming kernel scratch (see FwdParams)

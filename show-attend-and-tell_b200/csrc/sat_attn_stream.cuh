@@ -723,6 +723,8 @@ bwd_stream_kernel(BwdParams p, Smem sl, Part pt) {
             for (int i = 0; i < HPL * VEC; ++i) { dU[i] = 0.0f; dV[i] = 0.0f; }
             float desum = 0.0f;
             T* dpre_g = reinterpret_cast<T*>(p.dpre_out) + (size_t)b * L * H;
+            const bool keep_dpre = p.dpre_out != nullptr;
+            float* de_g = p.de_out ? p.de_out + (size_t)b * L : nullptr;
             const long long seg_end_local = ge - q0;
 
             for (; ql < seg_end_local; ql += CWARPS) {
@@ -754,6 +756,7 @@ bwd_stream_kernel(BwdParams p, Smem sl, Part pt) {
                     const float de0 = alpha_s[l] * (s0 - S);                       // softmax backward
                     const float de1 = two ? alpha_s[l + 1] * (s1 - S) : 0.0f;
                     desum += de0 + de1;
+                    if (de_g && lane == 0) { de_g[l] = de0; if (two) de_g[l + 1] = de1; }
 #pragma unroll
                     for (int j = 0; j < HPL; ++j) {
                         const int c = lane + 32 * j;
@@ -769,8 +772,10 @@ bwd_stream_kernel(BwdParams p, Smem sl, Part pt) {
                             dU[j * VEC + i] += dp0[i] + dp1[i];
                             dV[j * VEC + i] = fmaf(de0, t0, fmaf(de1, t1, dV[j * VEC + i]));
                         }
-                        __stcs(reinterpret_cast<uint4*>(dpre_g + (size_t)l * H + c * VEC), Vec16<T>::pack(dp0));     // written once, read at
-                        if (two) __stcs(reinterpret_cast<uint4*>(dpre_g + (size_t)(l + 1) * H + c * VEC), Vec16<T>::pack(dp1));   // the end of BPTT
+                        if (keep_dpre) {
+                            __stcs(reinterpret_cast<uint4*>(dpre_g + (size_t)l * H + c * VEC), Vec16<T>::pack(dp0));     // written once, read at
+                            if (two) __stcs(reinterpret_cast<uint4*>(dpre_g + (size_t)(l + 1) * H + c * VEC), Vec16<T>::pack(dp1));   // the end of BPTT
+                        }
                     }
                 }
                 __syncwarp();
@@ -982,13 +987,13 @@ int launch_fwd(const FwdParams& p, cudaStream_t stream) {
 
 template <typename T>
 inline bool bwd_eligible(const BwdParams& p) {
-    if (!p.dpre_out || p.da_acc || !p.ctx32 || !p.s_part || !shape_ok(p.L, p.D, p.H)) return false;
+    if ((!p.dpre_out && !p.de_out) || p.da_acc || !p.ctx32 || !p.s_part || !shape_ok(p.L, p.D, p.H)) return false;
     if (!p.dz_is_dctx && !p.s_dctx) return false;
     const size_t oa = sizeof(T) == 2 ? 8 : 16;
     return aligned(p.a, 16) && aligned(p.wa, 16) && aligned(p.uf, 16) && (p.ld_uf % 4 == 0) && aligned(p.v, 16) &&
            aligned(p.dz, 16) && (p.ld_dz % 4 == 0) && (!p.dctx_extra || (aligned(p.dctx_extra, 16) && p.ld_dce % 4 == 0)) &&
            aligned(p.ctx32, 16) && (p.ld_c32 % 4 == 0) && aligned(p.duf, oa) && (p.ld_duf % 4 == 0) && aligned(p.dpre_out, 16) &&
-           aligned(p.s_part, 16);
+           aligned(p.de_out, 4) && aligned(p.s_part, 16);
 }
 
 template <typename T, int D, int H, bool PRECISE>
@@ -1045,8 +1050,8 @@ int attn_step_fwd(const attn::FwdParams& p, cudaStream_t stream) {
 }
 template <typename T, bool PRECISE>
 int attn_step_bwd(const attn::BwdParams& p, cudaStream_t stream) {
-    if (p.dpre_out) {
-        SAT_REQUIRE(attn_s::bwd_eligible<T>(p), "attention bwd: dpre_out given but the streaming kernel does not support this shape/alignment/scratch");
+    if (p.dpre_out || p.de_out) {
+        SAT_REQUIRE(attn_s::bwd_eligible<T>(p), "attention bwd: dpre_out / de_out given but the streaming kernel does not support this shape/alignment/scratch");
         return attn_s::launch_bwd<T, PRECISE>(p, stream);
     }
     SAT_REQUIRE(p.dwa_acc != nullptr, "attention bwd: dwa_acc is NULL");

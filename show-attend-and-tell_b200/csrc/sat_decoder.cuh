@@ -49,7 +49,7 @@ static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 // space; a half is only a row range [b0, b0 + nb) of every time-major slice.  The side stream and its two events are
 // created once per host thread and device; the caller's stream forks into it before the loop and joins after it.
 // ---------------------------------------------------------------------------------------------------
-extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap;
+extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap, g_dpre_recompute;
 struct SideStream { cudaStream_t s, s2; cudaEvent_t fork, join, join2, attn_done[2], early, side; bool ok; };
 static inline int side_stream(SideStream** out) {
     static thread_local SideStream cache[32] = {};
@@ -120,7 +120,8 @@ struct DecWs {
     T* dUF;          // (T,B,H+D)
     float *dh_carry, *dc_carry;
     float* dwa_acc;  // (B,L,H)      generic attention backward: fp32 accumulator over time
-    T* dpre_all;     // (T,B,L,H)    streaming attention backward: each step's dpre written once
+    T* dpre_all;     // (T,B,L,H)    streaming attention backward: each step's dpre written once (g_dpre_recompute == 0)
+    float* de_all;   // (T,B,L)      streaming attention backward: each step's score gradients (g_dpre_recompute == 1)
     float* Ctx32;    // (T,B,D)      fp32 un-gated context saved by the streaming forward kernel for its backward
     uint8_t* attn_scratch;   // streaming attention kernels: arrival counters + partial records
     uint8_t* attn_scratch2;
@@ -182,7 +183,11 @@ int64_t carve(const sat_decoder_args& a, DecWs<T>& w, uint8_t* base) {
         TK(dabar, a.need_dfeat ? B * D : 0, float);
         TK(dUF, B * Tn * (H + D), T); TK(dh_carry, B * H, float); TK(dc_carry, B * H, float);
         TK(dwa_acc, (a.attention && !w.attn_stream) ? B * L * H : 0, float); TK(dwa_t, a.attention ? B * L * H : 0, T);
-        TK(dpre_all, w.attn_stream ? Tn * B * L * H : 0, T);
+        // streaming attention: the T slabs of dpre (g_dpre_recompute == 0), or only the score gradients de_t they are rebuilt from
+        TK(dpre_all, (w.attn_stream && !g_dpre_recompute) ? Tn * B * L * H : 0, T);
+        TK(de_all, (w.attn_stream && g_dpre_recompute) ? Tn * B * L : 0, float);
+        if (!(w.attn_stream && g_dpre_recompute)) w.de_all = nullptr;      // (a zero-byte take still hands out an address)
+        else w.dpre_all = nullptr;
         TK(dv_acc, B * H, float); TK(dbv_acc, B, float);
         TK(dE, B * Tn * H, T); TK(dpre0, B * 2 * H, T); TK(galpha, B * Tn * L, float);
         int64_t gs = 4 * H * (D + H);
@@ -562,7 +567,8 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
             // kernels leave that term to dfeat_kernel after the loop (dctx_t stays in dZH[t])
             p.da_acc = (g.img_features && !w.attn_stream) ? g.img_features + (size_t)b0 * L * D : nullptr;
             if (w.attn_stream) {
-                p.dpre_out = w.dpre_all + ((size_t)t * B + b0) * L * H;
+                if (w.de_all) p.de_out = w.de_all + ((size_t)t * B + b0) * L;          // sum_t dpre is rebuilt after the loop
+                else p.dpre_out = w.dpre_all + ((size_t)t * B + b0) * L * H;
                 p.ctx32 = w.Ctx32 + r * D; p.ld_c32 = D;
                 p.s_part = reinterpret_cast<float*>(scratch);
                 p.dz_is_dctx = 1;            // EpiDzGate above already turned dz into dctx and wrote d f_beta
@@ -644,7 +650,11 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         // encoder projection: dW (H x D) = (sum_t dpre)^T a ; db_W = colsum ; dv, db_v
         bool att_W_b_done = false;
         if (w.attn_stream) {
-            if (g.att_W_b) {     // one pass: sum over t + the bias gradient's column sums
+            if (w.de_all) {      // one pass over Wa: sum_t dpre_t rebuilt from de_t / Uh_t (+ the bias gradient's column sums)
+                SAT_TRY((misc::dpre_sum<T, PRECISE>(st, w.dwa_t, w.wa, w.UF, H + D, w.de_all, a.att_v_w, B, L, H, Tn, g.att_W_b,
+                                                    w.csum, w.csum_floats)));
+                att_W_b_done = true;
+            } else if (g.att_W_b) {     // one pass: sum over t + the bias gradient's column sums
                 SAT_TRY(misc::sum_over_t_colsum<T>(st, w.dwa_t, w.dpre_all, (int64_t)B * L, H, Tn, g.att_W_b, w.csum, w.csum_floats, g_tail_overlap == 2));
                 att_W_b_done = true;
             } else {

@@ -428,6 +428,126 @@ int sum_over_t_colsum(cudaStream_t s, T* out, const T* src, int64_t rows, int H,
     return SAT_OK;
 }
 
+// ---- sum over time of the attention pre-activation gradient, RECOMPUTED instead of stored -------------------------------------
+// Backward of attention.py:16-18 for the encoder projection W:  dWa[b,l,:] = sum_t dpre_t[b,l,:]  with
+//   dpre_t[b,l,h] = de_t[b,l] * v[h] * (1 - tanh^2(Wa[b,l,h] + Uh_t[b,h])).
+// The streaming backward kernel has every dpre_t in registers, but writing it out costs B*L*H*sizeof(T) per decode step and the
+// sum over t reads all of it back (2 x 1.03 GB at c2).  Everything dpre_t depends on besides Wa is tiny -- the score gradients
+// de_t (B*L floats per step) and the saved Uh_t rows (B*H floats per step) -- so the backward steps store only de_t and this kernel
+// rebuilds the sum in ONE pass over Wa: per (b, l) row it holds Wa in registers and loops over t with Uh_t / de_t in shared memory.
+// One MUFU tanh per (t, b, l, h): 514 M at c2, i.e. ~115 us of the SFU pipe instead of ~2 GB of HBM traffic; the sum is kept in
+// fp32 and rounded to T once (the stored slabs were rounded per step).
+// Block = (H/4, 2) threads: threadIdx.x owns 4 adjacent columns, threadIdx.y every second row of the item's DS_LC rows.  Items
+// (image, row chunk) are dealt to a persistent grid in contiguous ranges, so a block reloads the Uh table only when the image changes
+// and keeps its column sums (the bias gradient) in registers: part[block][H], added up by colsum_final_kernel.
+constexpr int DS_LC = 14;            // rows per item (196 = 14 x 14)
+constexpr int DS_NLR = DS_LC / 2;    // rows per thread
+template <typename T, bool PRECISE>
+__global__ void __launch_bounds__(384)
+dpre_sum_kernel(T* __restrict__ out, const T* __restrict__ wa, const float* __restrict__ uf, int64_t ld_uf,
+                const float* __restrict__ de, const float* __restrict__ v, int B, int L, int H, int Tn, int TC,
+                int64_t items, int chunks, float* __restrict__ part) {
+    extern __shared__ __align__(16) float ds_sm[];
+    float* uh_s = ds_sm;                               // [TC][H]
+    float* de_s = ds_sm + (size_t)TC * H;              // [TC][DS_LC]
+    const int tx = threadIdx.x, ty = threadIdx.y, h = tx * 4;
+    const int nthr = blockDim.x * blockDim.y, tid = ty * blockDim.x + tx;
+    const int64_t i0 = items * blockIdx.x / gridDim.x, i1 = items * (blockIdx.x + 1) / gridDim.x;
+    const float4 v4 = *reinterpret_cast<const float4*>(v + h);
+    const float vv[4] = {v4.x, v4.y, v4.z, v4.w};
+    float cs[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+    int64_t b_loaded = -1;
+    for (int64_t it = i0; it < i1; ++it) {
+        const int64_t b = it / chunks;
+        const int l0 = (int)(it - b * chunks) * DS_LC;
+        float w[DS_NLR][4], acc[DS_NLR][4];
+#pragma unroll
+        for (int i = 0; i < DS_NLR; ++i) {
+            const int l = l0 + ty + 2 * i;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) { acc[i][k] = 0.0f; w[i][k] = 0.0f; }
+            if (l < L) load4<T>(wa + ((size_t)b * L + l) * H + h, w[i]);
+        }
+        for (int t0 = 0; t0 < Tn; t0 += TC) {
+            const int tn = min(TC, Tn - t0);
+            const bool reload = (b != b_loaded) || (TC < Tn);
+            __syncthreads();                                         // the previous item / chunk is done with the tables
+            if (reload)
+                for (int i = tid; i < tn * (H / 4); i += nthr) {
+                    const int t = i / (H / 4), c = i - t * (H / 4);
+                    *reinterpret_cast<float4*>(uh_s + (size_t)t * H + c * 4) =
+                        *reinterpret_cast<const float4*>(uf + ((size_t)(t0 + t) * B + b) * ld_uf + c * 4);
+                }
+            for (int i = tid; i < tn * DS_LC; i += nthr) {
+                const int t = i / DS_LC, r = i - t * DS_LC;
+                de_s[i] = (l0 + r < L) ? de[((size_t)(t0 + t) * B + b) * L + l0 + r] : 0.0f;
+            }
+            __syncthreads();
+            for (int t = 0; t < tn; ++t) {
+                const float4 u4 = *reinterpret_cast<const float4*>(uh_s + (size_t)t * H + h);
+                const float u[4] = {u4.x, u4.y, u4.z, u4.w};
+#pragma unroll
+                for (int i = 0; i < DS_NLR; ++i) {
+                    const float d = de_s[t * DS_LC + ty + 2 * i];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float th = attn_tanh<PRECISE>(w[i][k] + u[k]);
+                        acc[i][k] = fmaf(d, fmaf(-th, th, 1.0f), acc[i][k]);
+                    }
+                }
+            }
+        }
+        b_loaded = b;
+#pragma unroll
+        for (int i = 0; i < DS_NLR; ++i) {
+            const int l = l0 + ty + 2 * i;
+            if (l < L) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { acc[i][k] *= vv[k]; cs[k] += acc[i][k]; }
+                store4<T>(out + ((size_t)b * L + l) * H + h, acc[i]);
+            }
+        }
+    }
+    if (part) {                                                      // the two row-parities of a block: through shared memory
+        __syncthreads();
+        if (ty == 1) *reinterpret_cast<float4*>(ds_sm + h) = make_float4(cs[0], cs[1], cs[2], cs[3]);
+        __syncthreads();
+        if (ty == 0) {
+            const float4 o = *reinterpret_cast<const float4*>(ds_sm + h);
+            *reinterpret_cast<float4*>(part + (size_t)blockIdx.x * H + h) = make_float4(cs[0] + o.x, cs[1] + o.y, cs[2] + o.z, cs[3] + o.w);
+        }
+    }
+}
+// out (B, L, H) T = sum_t dpre_t rebuilt from wa (B, L, H), uf (T, B, ld_uf: first H columns = U h_t + b_U), de (T, B, L) and v (H);
+// colsum_out[H] (may be NULL) = its column sums over (b, l), fp32.  scratch: blocks x H floats.
+template <typename T, bool PRECISE>
+int dpre_sum(cudaStream_t s, T* out, const T* wa, const float* uf, int64_t ld_uf, const float* de, const float* v, int B, int L,
+             int H, int Tn, float* colsum_out, float* scratch, int64_t scratch_floats) {
+    SAT_REQUIRE(H % 4 == 0 && H / 4 <= 192 && ld_uf % 4 == 0, "dpre_sum: H (%d) must be a multiple of 4, at most 768", H);
+    const int chunks = sat_cdiv(L, DS_LC);
+    const int64_t items = (int64_t)B * chunks;
+    int TC = Tn;
+    const int tc_max = (int)((96 * 1024) / ((size_t)(H + DS_LC) * 4));
+    if (TC > tc_max) TC = tc_max;
+    const size_t smem = (size_t)TC * (H + DS_LC) * 4;
+    int64_t blocks = items < 3 * 148 ? items : 3 * 148;
+    if (colsum_out && blocks * H > scratch_floats) blocks = scratch_floats / H;
+    SAT_REQUIRE(blocks >= 1, "dpre_sum: scratch too small");
+    static SatPerDevice configured;
+    SAT_TRY(configured.once([&]() -> int {
+        SAT_CHECK_CUDA(cudaFuncSetAttribute(dpre_sum_kernel<T, PRECISE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024 + 1024));
+        return SAT_OK;
+    }));
+    dpre_sum_kernel<T, PRECISE><<<(int)blocks, dim3(H / 4, 2), smem, s>>>(out, wa, uf, ld_uf, de, v, B, L, H, Tn, TC, items, chunks,
+                                                                           colsum_out ? scratch : nullptr);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    if (colsum_out) {
+        colsum_final_kernel<<<sat_cdiv(H, 32), 256, 0, s>>>(scratch, (int)blocks, H, colsum_out, 0);
+        SAT_CHECK_CUDA(cudaGetLastError());
+    }
+    return SAT_OK;
+}
+
 // abar[b,d] = mean_l a[b,l,d]   (decoder.py:139 / :104).  One pass over `a` (205 MB at c2): 16-byte loads, the L loop split
 // over blockIdx.z so that enough loads are in flight, partial sums combined with a second tiny pass when split.
 template <typename T>

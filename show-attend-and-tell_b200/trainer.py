@@ -176,6 +176,7 @@ class FusedTrainStep:
             a.workspace = self._ws.data_ptr() + ((-self._ws.data_ptr()) % 256)
             a.workspace_bytes = nbytes.value
             self._a = a
+            self._a_ptrs = None           # a fresh struct: the parameter pointers have to be written again
             if self._ws_key is not None:
                 self._graphs.clear()      # captured graphs point into the old workspace
                 self._seen.clear()

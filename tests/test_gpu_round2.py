@@ -305,6 +305,37 @@ def test_three_bucket_update_equals_default():
     assert (out[2][0] - out[3][0]).abs().max().item() <= 2e-4      # embedding scatter-add atomics may reorder; Adam itself is elementwise
 
 
+def test_trainer_follows_changing_batch_shapes():
+    """train.py:127-140 pads every batch to ITS longest caption and the last batch of an epoch is short: T and B change from step
+    to step.  A trainer that has seen (B, T) before must give the same update as a fresh one on the same step."""
+    from sat_b200.decoder import Decoder
+    from sat_b200.trainer import FusedTrainStep
+    V, D, L = 300, 512, 49
+    P = synth.make_params(V, D, 512, seed=23, emb_scale=0.5)
+    shapes = [(24, 5), (24, 3), (7, 6), (24, 5)]
+    batches = [synth.make_inputs(B, L, D, T, V, seed=50 + i) for i, (B, T) in enumerate(shapes)]
+
+    def fresh():
+        dec = Decoder(V, D, tf=True, attention=True, compute_dtype=torch.float32)
+        dec.load_state_dict(P, strict=True)
+        return FusedTrainStep(dec.cuda().eval(), lr=1e-3, distributed=False)
+
+    tr = fresh()
+    for i, (a, cap) in enumerate(batches):
+        state = (tr.flat_param.clone(), tr.exp_avg.clone(), tr.exp_avg_sq.clone())
+        loss = tr.step(a.cuda(), cap.cuda()).clone()
+        one = fresh()                                   # the same step on a trainer that has never seen another shape
+        one.flat_param.copy_(state[0])
+        one.exp_avg.copy_(state[1])
+        one.exp_avg_sq.copy_(state[2])
+        one.step_dev.fill_(i)
+        loss1 = one.step(a.cuda(), cap.cuda())
+        torch.cuda.synchronize()
+        tr.check_status()
+        torch.testing.assert_close(loss[:3], loss1[:3], rtol=1e-6, atol=1e-6)
+        torch.testing.assert_close(tr.flat_param, one.flat_param, rtol=0, atol=1e-5)      # embedding scatter-add atomics reorder
+
+
 def test_param_storage_guard():
     from sat_b200.decoder import Decoder
     from sat_b200.trainer import FusedTrainStep

@@ -91,7 +91,9 @@ def main():
         torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / args.steps
         s = 2
-        attn_bytes = B * T * (2 * L * (H + D) * s + L * H * s + L * H * s)
+        # per decode step: a + Wa read by the forward and by the backward kernel, the backward's score gradients written; once per
+        # train step: the rebuild of sum_t dpre (Wa read, the sum written) -- the same accounting as bench.py's step_hbm_floor_ms
+        attn_bytes = B * T * (2 * L * (H + D) * s + L * 4) + 2 * B * L * H * s
         floor_ms = attn_bytes / (peak * 1e9) * 1e3
         lv = [float(x) for x in loss.tolist()]
         print(json.dumps({"config": name, "shape": {"B": B, "L": L, "D": D, "H": H, "V": V, "T": T, "tf": c["tf"], "gate": c["gate"],
