@@ -55,7 +55,9 @@ int sat_set_gemm_static_weights(int on);
  * stream beside the encoder-projection GEMM; 3 (default) = like 1, and the side chain itself forks: embedding, [U; f_beta] and
  * output-layer gradients on a second internal stream beside the initial-state and LSTM weight gradients (3.61 -> 3.56 ms per
  * c2 step); 0 = one chain; 2 = like 1 with a register-thin, shared-memory-staged sum over t that GEMM CTAs of the side chain
- * can run beside (experimental: measured slower) */
+ * can run beside (experimental: measured slower).  10 + mode (default: 13) = the main chain (sum over t, dW_att)
+ * runs on an internal stream of the highest priority, so its CTAs are dispatched ahead of the side chains' pending ones (3.471 ->
+ * 3.455 ms per c2 step under CUDA-graph replay; launch by launch it is 0.006 ms slower). */
 int sat_set_tail_overlap(int on);
 /* tuning knob: 1 (default) = with the streaming attention kernels, a backward decode step stores only its score gradients
  * de_t (B x L floats) and the sum over t of the pre-activation gradients (the input of the encoder-projection weight gradient) is

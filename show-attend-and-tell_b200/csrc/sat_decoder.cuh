@@ -49,8 +49,8 @@ static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 // space; a half is only a row range [b0, b0 + nb) of every time-major slice.  The side stream and its two events are
 // created once per host thread and device; the caller's stream forks into it before the loop and joins after it.
 // ---------------------------------------------------------------------------------------------------
-extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap, g_dpre_recompute;
-struct SideStream { cudaStream_t s, s2; cudaEvent_t fork, join, join2, attn_done[2], early, side; bool ok; };
+extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap, g_dpre_recompute, g_tail_hp;
+struct SideStream { cudaStream_t s, s2, hp; cudaEvent_t fork, join, join2, joinhp, attn_done[2], early, side; bool ok; };
 static inline int side_stream(SideStream** out) {
     static thread_local SideStream cache[32] = {};
     int dev = 0;
@@ -60,6 +60,13 @@ static inline int side_stream(SideStream** out) {
     if (!ss.ok) {
         SAT_CHECK_CUDA(cudaStreamCreateWithFlags(&ss.s, cudaStreamNonBlocking));
         SAT_CHECK_CUDA(cudaStreamCreateWithFlags(&ss.s2, cudaStreamNonBlocking));
+        {   // the critical chain of the backward tail may run on a stream of the highest priority (g_tail_hp): its CTAs are
+            // dispatched ahead of the side chains' pending ones whenever an SM frees up
+            int least = 0, greatest = 0;
+            SAT_CHECK_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+            SAT_CHECK_CUDA(cudaStreamCreateWithPriority(&ss.hp, cudaStreamNonBlocking, greatest));
+        }
+        SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.joinhp, cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.fork, cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.join, cudaEventDisableTiming));
         SAT_CHECK_CUDA(cudaEventCreateWithFlags(&ss.join2, cudaEventDisableTiming));
@@ -646,6 +653,12 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         SAT_CHECK_CUDA(cudaStreamWaitEvent(sb, tl->fork, 0));
         if (three) SAT_CHECK_CUDA(cudaStreamWaitEvent(sc, tl->fork, 0));
     }
+    cudaStream_t caller = st;
+    const bool main_hp = g_tail_hp && g_tail_overlap && a.attention;
+    if (main_hp) {          // the main chain moves to the high-priority stream (forked from the same event as the side chains)
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(tl->hp, tl->fork, 0));
+        st = tl->hp;
+    }
     if (a.attention) {      // main chain
         // encoder projection: dW (H x D) = (sum_t dpre)^T a ; db_W = colsum ; dv, db_v
         bool att_W_b_done = false;
@@ -681,6 +694,11 @@ int decoder_backward_t(const sat_decoder_args& a, const sat_decoder_grads& g) {
         }
     }
 
+    if (main_hp) {
+        SAT_CHECK_CUDA(cudaEventRecord(tl->joinhp, st));
+        st = caller;
+        SAT_CHECK_CUDA(cudaStreamWaitEvent(st, tl->joinhp, 0));
+    }
     // ---- side chain: initial state (decoder.py:137-147) ------------------------------------------------------------
     misc::dinit_kernel<T><<<sat_cdiv(B * H, 256), 256, 0, sb>>>(w.dpre0, w.dh_carry, w.dc_carry, w.hc0, B, H);
     SAT_CHECK_CUDA(cudaGetLastError());

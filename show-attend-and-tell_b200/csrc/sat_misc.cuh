@@ -436,7 +436,8 @@ int sum_over_t_colsum(cudaStream_t s, T* out, const T* src, int64_t rows, int H,
 // de_t (B*L floats per step) and the saved Uh_t rows (B*H floats per step) -- so the backward steps store only de_t and this kernel
 // rebuilds the sum in ONE pass over Wa: per (b, l) row it holds Wa in registers and loops over t with Uh_t / de_t in shared memory.
 // One MUFU tanh per (t, b, l, h): 514 M at c2, i.e. ~115 us of the SFU pipe instead of ~2 GB of HBM traffic; the sum is kept in
-// fp32 and rounded to T once (the stored slabs were rounded per step).
+// fp32 and rounded to T once (the stored slabs were rounded per step).  Measured at c2: 162 us alone (ncu: the SFU pipe is the busiest
+// unit at 68 %, mio_throttle the top stall); a variant with the next item's rows prefetched by cp.async was slower (170 us) and was dropped.
 // Block = (H/4, 2) threads: threadIdx.x owns 4 adjacent columns, threadIdx.y every second row of the item's DS_LC rows.  Items
 // (image, row chunk) are dealt to a persistent grid in contiguous ranges, so a block reloads the Uh table only when the image changes
 // and keeps its column sums (the bias gradient) in registers: part[block][H], added up by colsum_final_kernel.

@@ -1,7 +1,7 @@
 """A/B timing of the fused c2 train step under library tuning knobs (device-resident, CUDA events, median of repeats).
   python tools/ab_step.py "pf=0,0" "pf=32,32" "pf=64,64;part=2" ...
 Knobs per variant (';'-separated): pf=F,B (sat_set_attn_prefetch), part=M (sat_set_attn_partition), graph=0|1 (CUDA-graph replay), wide=0|1 (sat_set_gemm_wide_tile),
-ado=0|1, tail=0..3 (sat_set_tail_overlap), dpre=0|1 (sat_set_dpre_recompute).  Prints one line per variant: ms/step (median of 5 x 20 steps), attention fwd / bwd event-bracket averages."""
+ado=0|1, tail=0..3 (sat_set_tail_overlap), dpre=0|1 (sat_set_dpre_recompute), buckets=2|3 (FusedTrainStep.buckets).  Prints one line per variant: ms/step (median of 5 x 20 steps), attention fwd / bwd event-bracket averages."""
 import ctypes
 import os
 import statistics
@@ -41,6 +41,7 @@ def main():
             trainers[key] = FusedTrainStep(dec.to(dev).train(), lr=1e-4, use_cuda_graph=bool(graph))
         tr = trainers[key]
         L.sat_set_dpre_recompute(int(kn.get("dpre", 1)))
+        tr.buckets = int(kn.get("buckets", 2))
         tr._graphs.clear(); tr._seen.clear()          # knobs are baked into captured graphs
         tr._ws_key = None                              # ... and into the workspace layout
         for i in range(8):
