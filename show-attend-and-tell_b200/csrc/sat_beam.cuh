@@ -253,11 +253,19 @@ struct BeamWs {
     bool attn_stream;
     float* top_preds;
     int64_t* prev_word;
+    T* emb_t;
+    float* emb_gate;
+    bool emb_table;
     int *live, *done, *n_active, *parent, *cand_word, *cand_parent, *slot_cand, *comp_step, *comp_cand, *ncomp, *last_step, *last_n;
     float* comp_score;
     int64_t total;
 };
 
+extern int g_beam_emb_table;
+// the table costs one V x 4H x H GEMM per call and V * 4H * 4 bytes; it pays from a few decode steps on while the vocabulary is small
+static inline bool beam_emb_table(const sat_beam_args& a) {
+    return g_beam_emb_table && a.embedding != nullptr && (int64_t)a.V * 4 * a.H * 4 <= ((int64_t)96 << 20) && a.max_steps >= 8;
+}
 static inline int beam_check_args(const sat_beam_args* a) {
     SAT_REQUIRE(a != nullptr, "null args");
     SAT_REQUIRE(a->struct_bytes == (int32_t)sizeof(sat_beam_args), "sat_beam_args size mismatch: got %d, library expects %zu",
@@ -283,6 +291,10 @@ int64_t beam_carve(const sat_beam_args& a, BeamWs<T>& w, uint8_t* base) {
 #define TK(field, count, type) w.field = reinterpret_cast<type*>(take((int64_t)(count) * (int64_t)sizeof(type)))
     TK(w_att, H * D, T); TK(w_uf, (H + D) * H, T); TK(w_gall, 4 * H * (2 * H + D), T); TK(w_init, 2 * H * D, T); TK(w_out, V * H, T);
     TK(w_fh, a.ado ? H * H : 0, T); TK(w_fz, a.ado ? H * D : 0, T);
+    // embedding share of the gate pre-activations for EVERY token, once per call: emb_gate = Emb W_ih[:, :H]^T + b_ih + b_hh
+    // (V x 4H fp32).  The step's gate GEMM then contracts over [z | h] only and its epilogue adds row prev_word[r].
+    w.emb_table = beam_emb_table(a);
+    TK(emb_t, w.emb_table ? V * H : 0, T); TK(emb_gate, w.emb_table ? V * 4 * H : 0, float);
     TK(b_uf, H + D, float); TK(b_g, 4 * H, float); TK(b_init, 2 * H, float);
     const bool a_alias = (a.a_dtype == a.dtype) && a.a_stride_d == 1 && a.a_stride_l == D && a.a_stride_b == L * D && al16(a.img_features);
     TK(a_c, a_alias ? 0 : NI * L * D, T);
@@ -363,7 +375,12 @@ int beam_search_t(const sat_beam_args& a) {
     } else {
         SAT_TRY(pl.weight(w.w_out, H, a.deep_w, H, V, H, 0, 0));
     }
+    if (w.emb_table) SAT_TRY(pl.weight(w.emb_t, H, a.embedding, H, V, H, 0, 0));
     SAT_TRY(pl.flush(st));
+    if (w.emb_table) {
+        auto e = lin<T>(V, 4 * H, w.b_g, SAT_ACT_NONE, w.emb_gate, 4 * H, nullptr, 0);
+        SAT_TRY(gemm<T>(st, w.emb_t, H, true, w.w_gall, xw, true, V, 4 * H, H, e));
+    }
     // ---- per-image precompute ----
     if (reinterpret_cast<const void*>(w.a_c) != a.img_features) {
         if (a.a_dtype == SAT_DTYPE_F32)
@@ -397,7 +414,8 @@ int beam_search_t(const sat_beam_args& a) {
         }));
     }
     for (int step = 1; step <= S; ++step) {
-        SAT_TRY(misc::gather_rows<T>(st, w.X, xw, a.embedding, H, w.prev_word, 1, R, V));                  // decoder.py:183
+        if (!w.emb_table || a.ado)      // (the advanced deep output reads the embedding itself, decoder.py:154)
+            SAT_TRY(misc::gather_rows<T>(st, w.X, xw, a.embedding, H, w.prev_word, 1, R, V));              // decoder.py:183
         if (a.attention) {
             auto e = lin<T>(R, H + D, w.b_uf, SAT_ACT_NONE, w.UF, H + D, nullptr, 0);
             SAT_TRY(gemm<T>(st, w.X + H + D, xw, true, w.w_uf, H, true, R, H + D, H, e));
@@ -417,7 +435,12 @@ int beam_search_t(const sat_beam_args& a) {
         memset(&e, 0, sizeof(e));
         e.bias = w.b_g; e.c_prev = w.Cc; e.ld_cp = H; e.c_out = w.Cn; e.ld_co = H; e.h_next = w.Hn; e.ld_hn = H;
         e.M = R; e.H = H;
-        SAT_TRY(gemm<T>(st, w.X, xw, true, w.w_gall, xw, true, R, 4 * H, (int)xw, e));                     // decoder.py:196-197
+        if (w.emb_table) {              // gates = emb_gate[prev_word] + [z | h] [W_ih[:, H:] | W_hh]^T
+            e.bias = nullptr; e.xg = w.emb_gate; e.ld_xg = 4 * H; e.xg_rows = w.prev_word;
+            SAT_TRY(gemm<T>(st, w.X + H, xw, true, w.w_gall + H, xw, true, R, 4 * H, D + H, e));           // decoder.py:196-197
+        } else {
+            SAT_TRY(gemm<T>(st, w.X, xw, true, w.w_gall, xw, true, R, 4 * H, (int)xw, e));                 // decoder.py:196-197
+        }
         if (!a.ado) {
             auto eo = lin<T>(R, V, out_b, SAT_ACT_NONE, w.logits, Vp, nullptr, 0);
             SAT_TRY(gemm<T>(st, w.Hn, H, true, w.w_out, H, true, R, V, H, eo));                            // decoder.py:203

@@ -222,6 +222,7 @@ template <typename T, bool PRECISE>
 struct EpiLstm {
     const float* xg;         // fp32 [M, ld_xg] pre-activation addend (interleaved) or null
     int64_t ld_xg;
+    const int64_t* xg_rows;  // null: row m of xg belongs to GEMM row m; else row xg_rows[m] (beam search: a table indexed by token id)
     const float* bias;       // fp32 [4H] interleaved or null
     const float* c_prev;     // fp32 [M, ld_cp]
     int64_t ld_cp;
@@ -251,7 +252,7 @@ struct EpiLstm {
     // attention kernel streamed 257 MB through L2: request them while the MMAs run instead of after the accumulator is ready
     __device__ __forceinline__ void prefetch(int m, int n, int nc) const {
         if (m >= M) return;
-        if (xg) for (int c = 0; c < nc; c += 32) l2_prefetch(xg + (int64_t)m * ld_xg + n + c);
+        if (xg && !xg_rows) for (int c = 0; c < nc; c += 32) l2_prefetch(xg + (int64_t)m * ld_xg + n + c);
         l2_prefetch(c_prev + (int64_t)m * ld_cp + (n >> 2));
         if (mask) l2_prefetch(mask + (int64_t)m * ld_mask + (n >> 2));
     }
@@ -259,6 +260,7 @@ struct EpiLstm {
     template <int NV>
     __device__ __forceinline__ void apply(int m, int n0, const float* acc) const {
         if (m >= M) return;
+        const int64_t xrow = (xg && xg_rows) ? xg_rows[m] : (int64_t)m;
         if constexpr (NV >= 16) {
             // the tensor-core GEMM hands one thread NV consecutive columns of ONE row = NV/4 consecutive units: work on
             // groups of 4 units so that every global access is a 16-byte (fp32) or 8-byte (bf16) vector
@@ -273,7 +275,7 @@ struct EpiLstm {
                 for (int u = 0; u < 4; ++u) {
                     const int n = n0 + 4 * (u0 + u);
                     float p[4] = {acc[4 * (u0 + u)], acc[4 * (u0 + u) + 1], acc[4 * (u0 + u) + 2], acc[4 * (u0 + u) + 3]};
-                    if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + (int64_t)m * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+                    if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + xrow * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
                     if (bias) { float4 x = *reinterpret_cast<const float4*>(bias + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
                     cell(p, cp[u], c[u], h[u]);
                     if (gates) store4<T>(gates + (int64_t)m * ld_g + n, p);
@@ -295,7 +297,7 @@ struct EpiLstm {
                 const int j = n >> 2;
                 if (j >= H) return;
                 float p[4] = {acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]};
-                if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + (int64_t)m * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+                if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + xrow * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
                 if (bias) { float4 x = *reinterpret_cast<const float4*>(bias + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
                 float c, h;
                 cell(p, c_prev[(int64_t)m * ld_cp + j], c, h);

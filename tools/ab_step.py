@@ -1,7 +1,7 @@
 """A/B timing of the fused c2 train step under library tuning knobs (device-resident, CUDA events, median of repeats).
   python tools/ab_step.py "pf=0,0" "pf=32,32" "pf=64,64;part=2" ...
 Knobs per variant (';'-separated): pf=F,B (sat_set_attn_prefetch), part=M (sat_set_attn_partition), graph=0|1 (CUDA-graph replay), wide=0|1 (sat_set_gemm_wide_tile),
-ado=0|1, tail=0..3 (sat_set_tail_overlap), dpre=0|1 (sat_set_dpre_recompute), buckets=2|3 (FusedTrainStep.buckets).  Prints one line per variant: ms/step (median of 5 x 20 steps), attention fwd / bwd event-bracket averages."""
+ado=0|1, tail=0..3 (sat_set_tail_overlap), dpre=0|1 (sat_set_dpre_recompute), buckets=2|3 (FusedTrainStep.buckets), l2=F,B[,PIN_MB] (sat_set_attn_l2_policy: Wa hint fwd, bwd, pinned feature megabytes).  Prints one line per variant: ms/step (median of 5 x 20 steps), attention fwd / bwd event-bracket averages."""
 import ctypes
 import os
 import statistics
@@ -31,6 +31,8 @@ def main():
         L.sat_set_attn_prefetch(pf[0], pf[1])
         L.sat_set_attn_partition(int(kn.get("part", 0)))
         L.sat_set_gemm_wide_tile(int(kn.get("wide", 1)))
+        l2 = [int(x) for x in kn.get("l2", "1,0,0").split(",")] + [0]
+        L.sat_set_attn_l2_policy(l2[0], l2[1], ctypes.c_int64(l2[2] * 1000000))
         if "tail" in kn:
             L.sat_set_tail_overlap(int(kn["tail"]))
         graph, ado = int(kn.get("graph", 0)), int(kn.get("ado", 0))

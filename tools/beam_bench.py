@@ -34,6 +34,9 @@ def main():
     from sat_b200 import synth
     from sat_b200.decoder import Decoder
     dev = torch.device("cuda", 0)
+    if "SAT_ATTN_PART" in os.environ:                       # 0 = automatic, 1 = whole items per CTA, 2 = equal slot counts + combine
+        from sat_b200 import _lib
+        _lib.lib().sat_set_attn_partition(int(os.environ["SAT_ATTN_PART"]))
     P = synth.make_params(args.V, args.D, args.H, seed=42)
     g = torch.Generator().manual_seed(7)
     a32 = torch.relu(torch.randn(args.images, args.L, args.D, generator=g))
