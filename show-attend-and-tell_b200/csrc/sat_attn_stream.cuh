@@ -313,6 +313,18 @@ fwd_stream_kernel(FwdParams p, Smem sl, Part pt, int ngroups) {
             const int nb_valid = min(NBG, p.NB - grp * NBG);
             const float* uf_s = side + (size_t)(seg & 1) * SIDE_F;     // this item's uf rows, fetched by the producer
             mbar_wait(&sfull[seg & 1], (seg >> 1) & 1);
+            // fp32 mode with beam rows: tanh(Wa + Uh) from separate exponentials (see tanh_from_exp2x).  The consumers turn the
+            // item's Uh rows into e^{2 Uh} in place, once, before anyone reads them.
+            constexpr bool EXPU = PRECISE && NBG > 1;
+            if constexpr (EXPU) {
+                float* us = side + (size_t)(seg & 1) * SIDE_F;
+                for (int i = tid; i < NBG * H; i += CTHREADS) {
+                    const int nb = i / H, hh = i - nb * H;
+                    us[nb * (H + D) + hh] = exp2x_clamped(us[nb * (H + D) + hh]);
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // these generic writes precede the producer's next bulk copy
+                consumer_bar();
+            }
             float uh[HPL * VEC];
             if (NBG == 1) {
 #pragma unroll
@@ -352,6 +364,10 @@ fwd_stream_kernel(FwdParams p, Smem sl, Part pt, int ngroups) {
                         float f0[VEC], f1[VEC];
                         Vec16<T>::unpack(lds16(wa_s + (size_t)lp * H + c * VEC), f0);
                         Vec16<T>::unpack(lds16(wa_s + (size_t)lq * H + c * VEC), f1);
+                        if constexpr (EXPU) {
+#pragma unroll
+                            for (int i = 0; i < VEC; ++i) { f0[i] = exp2x_clamped(f0[i]); f1[i] = exp2x_clamped(f1[i]); }
+                        }
 #pragma unroll
                         for (int nb = 0; nb < NBG; ++nb) {
                             float u[VEC];
@@ -367,8 +383,13 @@ fwd_stream_kernel(FwdParams p, Smem sl, Part pt, int ngroups) {
                             }
 #pragma unroll
                             for (int i = 0; i < VEC; ++i) {
-                                sc0[nb] = fmaf(vreg[j * VEC + i], attn_tanh<PRECISE>(f0[i] + u[i]), sc0[nb]);
-                                sc1[nb] = fmaf(vreg[j * VEC + i], attn_tanh<PRECISE>(f1[i] + u[i]), sc1[nb]);
+                                if constexpr (EXPU) {                       // f0 / f1 hold e^{2 Wa}, u holds e^{2 Uh}
+                                    sc0[nb] = fmaf(vreg[j * VEC + i], tanh_from_exp2x(f0[i] * u[i]), sc0[nb]);
+                                    sc1[nb] = fmaf(vreg[j * VEC + i], tanh_from_exp2x(f1[i] * u[i]), sc1[nb]);
+                                } else {
+                                    sc0[nb] = fmaf(vreg[j * VEC + i], attn_tanh<PRECISE>(f0[i] + u[i]), sc0[nb]);
+                                    sc1[nb] = fmaf(vreg[j * VEC + i], attn_tanh<PRECISE>(f1[i] + u[i]), sc1[nb]);
+                                }
                             }
                         }
                     }

@@ -253,6 +253,8 @@ struct BeamWs {
     bool attn_stream;
     float* top_preds;
     int64_t* prev_word;
+    T *w_uf_hi, *w_uf_lo, *w_gall_hi, *w_gall_lo, *w_out_hi, *w_out_lo;      // fp32 mode: operands pre-split for the 3xTF32 GEMM
+    bool presplit;
     T* emb_t;
     float* emb_gate;
     bool emb_table;
@@ -261,7 +263,7 @@ struct BeamWs {
     int64_t total;
 };
 
-extern int g_beam_emb_table;
+extern int g_beam_emb_table, g_beam_presplit;
 // the table costs one V x 4H x H GEMM per call and V * 4H * 4 bytes; it pays from a few decode steps on while the vocabulary is small
 static inline bool beam_emb_table(const sat_beam_args& a) {
     return g_beam_emb_table && a.embedding != nullptr && (int64_t)a.V * 4 * a.H * 4 <= ((int64_t)96 << 20) && a.max_steps >= 8;
@@ -295,6 +297,11 @@ int64_t beam_carve(const sat_beam_args& a, BeamWs<T>& w, uint8_t* base) {
     // (V x 4H fp32).  The step's gate GEMM then contracts over [z | h] only and its epilogue adds row prev_word[r].
     w.emb_table = beam_emb_table(a);
     TK(emb_t, w.emb_table ? V * H : 0, T); TK(emb_gate, w.emb_table ? V * 4 * H : 0, float);
+    // fp32 mode: the weights of the three per-step GEMMs pre-split into tf32 hi / lo parts once per call (tc32::split_operand)
+    w.presplit = IsF32<T>::value && g_beam_presplit && a.max_steps >= 8;
+    TK(w_uf_hi, w.presplit && a.attention ? (H + D) * H : 0, T); TK(w_uf_lo, w.presplit && a.attention ? (H + D) * H : 0, T);
+    TK(w_gall_hi, w.presplit ? 4 * H * (2 * H + D) : 0, T); TK(w_gall_lo, w.presplit ? 4 * H * (2 * H + D) : 0, T);
+    TK(w_out_hi, w.presplit ? V * H : 0, T); TK(w_out_lo, w.presplit ? V * H : 0, T);
     TK(b_uf, H + D, float); TK(b_g, 4 * H, float); TK(b_init, 2 * H, float);
     const bool a_alias = (a.a_dtype == a.dtype) && a.a_stride_d == 1 && a.a_stride_l == D && a.a_stride_b == L * D && al16(a.img_features);
     TK(a_c, a_alias ? 0 : NI * L * D, T);
@@ -377,6 +384,17 @@ int beam_search_t(const sat_beam_args& a) {
     }
     if (w.emb_table) SAT_TRY(pl.weight(w.emb_t, H, a.embedding, H, V, H, 0, 0));
     SAT_TRY(pl.flush(st));
+    if constexpr (IsF32<T>::value) {
+        if (w.presplit) {
+            if (a.attention) SAT_TRY(tc32::split_operand(st, w.w_uf_hi, w.w_uf_lo, w.w_uf, (int64_t)(H + D) * H));
+            SAT_TRY(tc32::split_operand(st, w.w_gall_hi, w.w_gall_lo, w.w_gall, (int64_t)4 * H * xw));
+            SAT_TRY(tc32::split_operand(st, w.w_out_hi, w.w_out_lo, w.w_out, (int64_t)V * H));
+        }
+    }
+    const T* uf_hi = w.presplit ? w.w_uf_hi : nullptr;
+    const T* uf_lo = w.presplit ? w.w_uf_lo : nullptr;
+    const T* out_hi = w.presplit ? w.w_out_hi : nullptr;
+    const T* out_lo = w.presplit ? w.w_out_lo : nullptr;
     if (w.emb_table) {
         auto e = lin<T>(V, 4 * H, w.b_g, SAT_ACT_NONE, w.emb_gate, 4 * H, nullptr, 0);
         SAT_TRY(gemm<T>(st, w.emb_t, H, true, w.w_gall, xw, true, V, 4 * H, H, e));
@@ -418,7 +436,7 @@ int beam_search_t(const sat_beam_args& a) {
             SAT_TRY(misc::gather_rows<T>(st, w.X, xw, a.embedding, H, w.prev_word, 1, R, V));              // decoder.py:183
         if (a.attention) {
             auto e = lin<T>(R, H + D, w.b_uf, SAT_ACT_NONE, w.UF, H + D, nullptr, 0);
-            SAT_TRY(gemm<T>(st, w.X + H + D, xw, true, w.w_uf, H, true, R, H + D, H, e));
+            SAT_TRY(gemm<T>(st, w.X + H + D, xw, true, w.w_uf, H, true, R, H + D, H, e, 0, 0, 0, uf_hi, uf_lo));
             attn::FwdParams p;
             memset(&p, 0, sizeof(p));
             p.a = w.a_c; p.wa = w.wa; p.uf = w.UF; p.ld_uf = H + D; p.v = a.att_v_w; p.bv = a.att_v_b;
@@ -437,13 +455,15 @@ int beam_search_t(const sat_beam_args& a) {
         e.M = R; e.H = H;
         if (w.emb_table) {              // gates = emb_gate[prev_word] + [z | h] [W_ih[:, H:] | W_hh]^T
             e.bias = nullptr; e.xg = w.emb_gate; e.ld_xg = 4 * H; e.xg_rows = w.prev_word;
-            SAT_TRY(gemm<T>(st, w.X + H, xw, true, w.w_gall + H, xw, true, R, 4 * H, D + H, e));           // decoder.py:196-197
+            SAT_TRY(gemm<T>(st, w.X + H, xw, true, w.w_gall + H, xw, true, R, 4 * H, D + H, e, 0, 0, 0,
+                            w.presplit ? w.w_gall_hi + H : nullptr, w.presplit ? w.w_gall_lo + H : nullptr));      // decoder.py:196-197
         } else {
-            SAT_TRY(gemm<T>(st, w.X, xw, true, w.w_gall, xw, true, R, 4 * H, (int)xw, e));                 // decoder.py:196-197
+            SAT_TRY(gemm<T>(st, w.X, xw, true, w.w_gall, xw, true, R, 4 * H, (int)xw, e, 0, 0, 0,
+                            w.presplit ? w.w_gall_hi : nullptr, w.presplit ? w.w_gall_lo : nullptr));              // decoder.py:196-197
         }
         if (!a.ado) {
             auto eo = lin<T>(R, V, out_b, SAT_ACT_NONE, w.logits, Vp, nullptr, 0);
-            SAT_TRY(gemm<T>(st, w.Hn, H, true, w.w_out, H, true, R, V, H, eo));                            // decoder.py:203
+            SAT_TRY(gemm<T>(st, w.Hn, H, true, w.w_out, H, true, R, V, H, eo, 0, 0, 0, out_hi, out_lo));   // decoder.py:203
         } else {
             auto e1 = lin<T>(R, H, a.f_h_b, SAT_ACT_RELU, nullptr, 0, w.P1, H);
             SAT_TRY(gemm<T>(st, w.Hn, H, true, w.w_fh, H, true, R, H, H, e1));
@@ -454,7 +474,7 @@ int beam_search_t(const sat_beam_args& a) {
             beam_add3_kernel<T><<<R, 128, 0, st>>>(w.Comb, w.P1, w.P2, w.X, xw, H);
             SAT_CHECK_CUDA(cudaGetLastError());
             auto e3 = lin<T>(R, V, out_b, SAT_ACT_RELU, w.logits, Vp, nullptr, 0);
-            SAT_TRY(gemm<T>(st, w.Comb, H, true, w.w_out, H, true, R, V, H, e3));                          // decoder.py:199-201
+            SAT_TRY(gemm<T>(st, w.Comb, H, true, w.w_out, H, true, R, V, H, e3, 0, 0, 0, out_hi, out_lo)); // decoder.py:199-201
         }
         beam::StepParams sp;
         sp.logits = w.logits; sp.ldl = Vp; sp.top_preds = w.top_preds; sp.prev_word = w.prev_word; sp.live = w.live; sp.done = w.done;

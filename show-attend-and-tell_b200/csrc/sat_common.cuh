@@ -157,6 +157,21 @@ template <bool PRECISE> __device__ __forceinline__ float attn_tanh(float x) {
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
     return fmaf(-2.0f, r, 1.0f);
 }
+// tanh(w + u) from e^{2w} and e^{2u} kept separately: when one w meets several u (the beam rows of an image) the exponential of
+// w is taken once and each pair costs one reciprocal -- 1 + 1/NB SFU operations per element instead of 2.  The exponents are
+// clamped to +-40 so that neither factor is 0 or inf (their product may be: tanh then saturates correctly, never NaN); the clamp
+// only matters for |w| > 40 with u of the opposite sign within ~10 of it, far outside what a tanh pre-activation sees.
+__device__ __forceinline__ float exp2x_clamped(float x) {
+    float e;
+    const float a = fminf(fmaxf(x * 2.885390081777927f, -115.4f), 115.4f);
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(a));
+    return e;
+}
+__device__ __forceinline__ float tanh_from_exp2x(float e) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+    return fmaf(-2.0f, r, 1.0f);
+}
 template <bool PRECISE> __device__ __forceinline__ float sat_sigmoid(float x) {
     if (PRECISE) return 1.0f / (1.0f + expf(-x));
     return 0.5f * sat_tanh<false>(0.5f * x) + 0.5f;

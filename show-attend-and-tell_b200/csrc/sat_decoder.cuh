@@ -26,12 +26,16 @@ template <typename T> struct IsF32 { static constexpr bool value = std::is_same<
 
 template <typename T, typename Epi>
 int gemm(cudaStream_t s, const T* A, int64_t lda, bool a_k, const T* B, int64_t ldb, bool b_k, int M, int N, int K,
-         const Epi& epi, int bn = 0, int sm_budget = 0, int b_static = 0) {
+         const Epi& epi, int bn = 0, int sm_budget = 0, int b_static = 0, const T* B_hi = nullptr, const T* B_lo = nullptr) {
     SatProfScope prof(SAT_PROF_GEMM, s);
     if constexpr (IsF32<T>::value) {
         // fp32 mode: forward-shaped GEMMs (both operands K-major) run on the tensor cores as 3xTF32 (fp32-accurate, see
         // sat_gemm_tf32.cuh); transposed-operand (gradient) GEMMs and tiny ones stay on the true-fp32 SIMT kernel
-        if (tc32::applies(A, lda, a_k, B, ldb, b_k, M, N, K)) return tc32::launch<Epi>(s, A, lda, B, ldb, M, N, K, epi);
+        // (B_hi, B_lo): the same operand pre-split by tc32::split_operand (fp32 mode only; the SIMT fallback reads the original B)
+        if (tc32::applies(A, lda, a_k, B, ldb, b_k, M, N, K)) {
+            if (B_hi && B_lo && ((((uintptr_t)B_hi | (uintptr_t)B_lo) & 15) == 0)) return tc32::launch<Epi>(s, A, lda, B_hi, ldb, M, N, K, epi, B_lo);
+            return tc32::launch<Epi>(s, A, lda, B, ldb, M, N, K, epi);
+        }
         return simt::launch<float, Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi);
     } else {
         if (g_force_simt) return simt::launch<bf16, Epi>(s, A, lda, a_k, B, ldb, b_k, M, N, K, epi);

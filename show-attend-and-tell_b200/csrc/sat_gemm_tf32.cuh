@@ -57,9 +57,14 @@ __device__ __forceinline__ float tf32_rna(float x) {
     return __uint_as_float(r);
 }
 
-template <int BN, typename Epi>
+// BSPLIT: the B operand (weights that serve many launches, e.g. the 51 decode steps of a beam search) arrives already split --
+// mapB = tf32(B), mapBl = B - tf32(B), made once by split_operand() -- so the work warps split only the A tile.  A k-block of the
+// unsplit kernel moves ~192 KB through shared memory (split: 32 KB read + 64 KB written; MMAs: 3 x (A + B) read), which is what
+// bounds it at ~1 us; the pre-split B takes a quarter of that away.
+template <int BN, typename Epi, bool BSPLIT>
 __global__ void __launch_bounds__(THREADS, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, int M, int N, int K, Epi epi) {
+gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, const __grid_constant__ CUtensorMap mapBl,
+            int M, int N, int K, Epi epi) {
     using C = Cfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -76,6 +81,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&mapA);
         tma_prefetch_desc(&mapB);
+        if constexpr (BSPLIT) tma_prefetch_desc(&mapBl);
         for (int s = 0; s < C::STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&split_bar[s], WORK_WARPS); mbar_init(&empty_bar[s], 1); }
         mbar_init(tmem_full_bar, 1);
         mbar_fence_init();
@@ -98,9 +104,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
                 const uint32_t ph = (kb / C::STAGES) & 1;
                 mbar_wait(&empty_bar[s], ph ^ 1);
                 uint8_t* st = smem + s * C::STAGE_BYTES;
-                mbar_expect_tx(&full_bar[s], A_BYTES + C::B_BYTES);
+                mbar_expect_tx(&full_bar[s], A_BYTES + (BSPLIT ? 2 : 1) * C::B_BYTES);
                 tma_load_2d(st, &mapA, kb * BK, m0, &full_bar[s]);                            // raw A -> "A hi"
-                tma_load_2d(st + 2 * A_BYTES, &mapB, kb * BK, n0, &full_bar[s]);              // raw B -> "B hi"
+                tma_load_2d(st + 2 * A_BYTES, &mapB, kb * BK, n0, &full_bar[s]);              // raw B (or its hi part) -> "B hi"
+                if constexpr (BSPLIT) tma_load_2d(st + 2 * A_BYTES + C::B_BYTES, &mapBl, kb * BK, n0, &full_bar[s]);      // -> "B lo"
             }
         }
     } else if (warp == 1) {
@@ -132,7 +139,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     } else {
         const int wt = threadIdx.x - 64;                 // 0 .. 511
         // ---- split the landed tiles: hi in place, lo to the twin buffer ----
-        constexpr int A_CH = A_BYTES / 16, B_CH = C::B_BYTES / 16;
+        constexpr int A_CH = A_BYTES / 16, B_CH = C::B_BYTES / 16, SPLIT_CH = BSPLIT ? A_CH : A_CH + B_CH;
         for (int kb = 0; kb < nk; ++kb) {
             const int s = kb % C::STAGES;
             const uint32_t ph = (kb / C::STAGES) & 1;
@@ -142,7 +149,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
             float4* bhi = alo + A_CH;
             float4* blo = bhi + B_CH;
 #pragma unroll 2
-            for (int c = wt; c < A_CH + B_CH; c += WORK_WARPS * 32) {
+            for (int c = wt; c < SPLIT_CH; c += WORK_WARPS * 32) {
                 float4* hp = c < A_CH ? ahi + c : bhi + (c - A_CH);
                 float4* lp = c < A_CH ? alo + c : blo + (c - A_CH);
                 const float4 x = *hp;
@@ -222,9 +229,9 @@ inline bool applies(const float* A, int64_t lda, bool a_k, const float* B, int64
            (((uintptr_t)A | (uintptr_t)B) & 15) == 0;
 }
 
-template <int BN, typename Epi>
-int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB, int M, int N, int K, const Epi& epi) {
-    auto kern = gemm_kernel<BN, Epi>;
+template <int BN, typename Epi, bool BSPLIT>
+int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB, const CUtensorMap& mBl, int M, int N, int K, const Epi& epi) {
+    auto kern = gemm_kernel<BN, Epi, BSPLIT>;
     constexpr int smem = Cfg<BN>::SMEM_BYTES;
     static SatPerDevice configured;
     SAT_TRY(configured.once([&]() -> int {
@@ -234,12 +241,14 @@ int launch_bn(cudaStream_t stream, const CUtensorMap& mA, const CUtensorMap& mB,
     cudaLaunchConfig_t cfg;
     cudaLaunchAttribute attr[1];
     pdl_config(&cfg, attr, dim3(sat_cdiv(N, BN), sat_cdiv(M, BM)), dim3(THREADS), smem, stream);
-    SAT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, M, N, K, epi));
+    SAT_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, mA, mB, mBl, M, N, K, epi));
     return SAT_OK;
 }
 
+// B_lo != NULL: B holds tf32(B) and B_lo the remainder (same layout), see split_operand()
 template <typename Epi>
-int launch(cudaStream_t stream, const float* A, int64_t lda, const float* B, int64_t ldb, int M, int N, int K, const Epi& epi) {
+int launch(cudaStream_t stream, const float* A, int64_t lda, const float* B, int64_t ldb, int M, int N, int K, const Epi& epi,
+           const float* B_lo = nullptr) {
     if (M <= 0 || N <= 0) return SAT_OK;
     // widest tile that keeps the grid in the fewest waves; a k-block costs ~0.41 us of MMAs at BN = 128 (12 x 128x128x8 tf32),
     // half / a quarter of that at 64 / 32 with a ~0.16 us floor (TMA + split), plus ~6 us of launch, prologue and drain
@@ -263,8 +272,37 @@ int launch(cudaStream_t stream, const float* A, int64_t lda, const float* B, int
     CUtensorMap mA, mB;
     SAT_TRY(make_map_f32(&mA, A, (uint64_t)K, (uint64_t)M, lda, BM));
     SAT_TRY(make_map_f32(&mB, B, (uint64_t)K, (uint64_t)N, ldb, (uint32_t)bn));
-    if (bn == 128) return launch_bn<128, Epi>(stream, mA, mB, M, N, K, epi);
-    if (bn == 64) return launch_bn<64, Epi>(stream, mA, mB, M, N, K, epi);
-    return launch_bn<32, Epi>(stream, mA, mB, M, N, K, epi);
+    if (B_lo) {
+        CUtensorMap mBl;
+        SAT_TRY(make_map_f32(&mBl, B_lo, (uint64_t)K, (uint64_t)N, ldb, (uint32_t)bn));
+        if (bn == 128) return launch_bn<128, Epi, true>(stream, mA, mB, mBl, M, N, K, epi);
+        if (bn == 64) return launch_bn<64, Epi, true>(stream, mA, mB, mBl, M, N, K, epi);
+        return launch_bn<32, Epi, true>(stream, mA, mB, mBl, M, N, K, epi);
+    }
+    if (bn == 128) return launch_bn<128, Epi, false>(stream, mA, mB, mB, M, N, K, epi);
+    if (bn == 64) return launch_bn<64, Epi, false>(stream, mA, mB, mB, M, N, K, epi);
+    return launch_bn<32, Epi, false>(stream, mA, mB, mB, M, N, K, epi);
+}
+
+// hi = tf32(src) (round to nearest, ties away), lo = src - hi: the operand split of 3xTF32, done once for an operand many launches share
+__global__ void split_operand_kernel(float* __restrict__ hi, float* __restrict__ lo, const float* __restrict__ src, int64_t n4) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+        const float4 x = reinterpret_cast<const float4*>(src)[i];
+        float4 h, l;
+        h.x = tf32_rna(x.x); h.y = tf32_rna(x.y); h.z = tf32_rna(x.z); h.w = tf32_rna(x.w);
+        l.x = x.x - h.x; l.y = x.y - h.y; l.z = x.z - h.z; l.w = x.w - h.w;
+        reinterpret_cast<float4*>(hi)[i] = h;
+        reinterpret_cast<float4*>(lo)[i] = l;
+    }
+}
+inline int split_operand(cudaStream_t stream, float* hi, float* lo, const float* src, int64_t n) {
+    SAT_REQUIRE(n % 4 == 0 && ((((uintptr_t)hi | (uintptr_t)lo | (uintptr_t)src) & 15) == 0), "split_operand: 16-byte alignment");
+    const int64_t n4 = n / 4;
+    int64_t blocks = (n4 + 255) / 256;
+    if (blocks > 4 * 148) blocks = 4 * 148;
+    if (blocks < 1) return SAT_OK;
+    split_operand_kernel<<<(int)blocks, 256, 0, stream>>>(hi, lo, src, n4);
+    SAT_CHECK_CUDA(cudaGetLastError());
+    return SAT_OK;
 }
 }  // namespace tc32
