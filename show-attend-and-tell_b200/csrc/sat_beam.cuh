@@ -25,6 +25,14 @@ struct StepParams {
     float* comp_score;       // (NI, beam)
     int* comp_step;          // (NI, beam)
     int* comp_cand;          // (NI, beam)
+    // state gather fused into this kernel (decoder.py:246-247): h / c rows of the surviving beams for the next step's operands
+    void* X;                 // (R, ldx) T: next step's GEMM operand rows; the h part starts at column hoff
+    int64_t ldx;
+    int hoff;
+    const void* Hn;          // (R, H) T: h of this step
+    float* Cc;               // (R, H) cell state of the next step (out)
+    const float* Cn;         // (R, H) cell state of this step
+    int H, esize;            // hidden size, sizeof(T)
     int* ncomp;              // (NI)
     int* last_step;          // (NI) last executed step
     int* last_n;             // (NI) rows alive at the start of the last executed step
@@ -42,6 +50,8 @@ topk_step_kernel(StepParams p) {
     __shared__ float pick_val[MAXBEAM];
     __shared__ int pick_idx[MAXBEAM];
     __shared__ float s_tp[MAXBEAM];
+    __shared__ int s_parent[MAXBEAM];
+    __shared__ int s_nl;
     extern __shared__ float s_cache[];      // cumulative scores of this image, filled by the first selection pass
     const int img = blockIdx.x;
     if (p.done[img]) return;
@@ -137,21 +147,24 @@ topk_step_kernel(StepParams p) {
         if (nl == 0 || p.step > p.max_steps) {                            // decoder.py:240-241, 252-253 (Q17)
             p.done[img] = 1;
             atomicSub(p.n_active, 1);
+            nl = 0;
         }
+        s_nl = nl;
+        for (int k = 0; k < nl; ++k) s_parent[k] = p.parent[img * p.beam + k];
     }
-}
-
-// h = h[prev_word_idxs[incomplete]], c = c[...]  (decoder.py:246-247) into the next step's operand rows
-template <typename T>
-__global__ void gather_state_kernel(T* __restrict__ X, int64_t ldx, int hoff, const T* __restrict__ Hn,
-                                    float* __restrict__ Cc, const float* __restrict__ Cn, const int* __restrict__ parent,
-                                    const int* __restrict__ live, const int* __restrict__ done, int beam, int H) {
-    const int r = blockIdx.x, img = r / beam, slot = r - img * beam;
-    if (done[img] || slot >= live[img]) return;
-    const int src = img * beam + parent[r];
-    for (int j = threadIdx.x; j < H; j += blockDim.x) {
-        X[(int64_t)r * ldx + hoff + j] = Hn[(size_t)src * H + j];
-        Cc[(size_t)r * H + j] = Cn[(size_t)src * H + j];
+    // h = h[prev_word_idxs[incomplete]], c = c[...] (decoder.py:246-247) into the next step's operand rows.  Source (Hn, Cn) and
+    // destination (X, Cc) are different buffers, so the rows can be copied in any order.
+    __syncthreads();
+    const int nl = s_nl;
+    const int hv = p.H * p.esize / 16, cv = p.H / 4;                      // 16-byte vectors per h row / per c row
+    for (int i = threadIdx.x; i < nl * (hv + cv); i += TOPK_THREADS) {
+        const int slot = i / (hv + cv), j = i - slot * (hv + cv);
+        const int r = img * p.beam + slot, src = img * p.beam + s_parent[slot];
+        if (j < hv)
+            reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.X) + ((size_t)r * p.ldx + p.hoff) * p.esize)[j] =
+                reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(p.Hn) + (size_t)src * p.H * p.esize)[j];
+        else
+            reinterpret_cast<float4*>(p.Cc + (size_t)r * p.H)[j - hv] = reinterpret_cast<const float4*>(p.Cn + (size_t)src * p.H)[j - hv];
     }
 }
 
@@ -484,8 +497,8 @@ int beam_search_t(const sat_beam_args& a) {
         sp.NI = NI; sp.beam = NB; sp.V = V; sp.step = step; sp.max_steps = a.max_steps;
         sp.stop_a = 1; sp.stop_b = a.bert ? 0 : 102;
         sp.cache_floats = (int)(topk_smem / 4);
-        beam::topk_step_kernel<<<NI, beam::TOPK_THREADS, topk_smem, st>>>(sp);
-        beam::gather_state_kernel<T><<<R, 128, 0, st>>>(w.X, xw, H + D, w.Hn, w.Cc, w.Cn, w.parent, w.live, w.done, NB, H);
+        sp.X = w.X; sp.ldx = xw; sp.hoff = H + D; sp.Hn = w.Hn; sp.Cc = w.Cc; sp.Cn = w.Cn; sp.H = H; sp.esize = (int)sizeof(T);
+        beam::topk_step_kernel<<<NI, beam::TOPK_THREADS, topk_smem, st>>>(sp);                    // + the state gather
         SAT_CHECK_CUDA(cudaGetLastError());
         if ((step % 8) == 0 && step < S) {     // early exit once every image has finished (no effect on results)
             // PIPELINED poll: the flag copied after step s is only looked at after the launches of steps s+1 .. s+8 have been
