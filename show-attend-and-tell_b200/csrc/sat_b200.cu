@@ -19,6 +19,7 @@ int g_dec_split = 0;      // half-batch pipelining of the recurrent loop (sat_de
 int g_split_attn_ctas = 0, g_split_gemm_sms = 0, g_split_chain = 1;
 int g_fuse_cell_bwd = 1;  // LSTM cell backward in the epilogue of the dh GEMM (EpiDhCell)
 int g_head_overlap = 1;   // forward: initial state + embeddings on the side stream beside K1
+int g_beam_merge_h = 1;    // beam search: W_hh h computed by the [U; f_beta] GEMM (4H extra columns), gate GEMM without its h columns
 int g_beam_presplit = 1;   // beam search, fp32 mode: per-step GEMM weights pre-split into tf32 hi / lo once per call
 int g_beam_emb_table = 1;  // beam search: embedding share of the gate GEMM from a once-per-call table (sat_beam.cuh)
 int g_dpre_recompute = 1;   // streaming attention backward stores de_t only; sum_t dpre_t is rebuilt in one pass over Wa (misc::dpre_sum)

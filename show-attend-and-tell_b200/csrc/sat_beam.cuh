@@ -267,7 +267,7 @@ struct BeamWs {
     float* top_preds;
     int64_t* prev_word;
     T *w_uf_hi, *w_uf_lo, *w_gall_hi, *w_gall_lo, *w_out_hi, *w_out_lo;      // fp32 mode: operands pre-split for the 3xTF32 GEMM
-    bool presplit;
+    bool presplit, merge_h;
     T* emb_t;
     float* emb_gate;
     bool emb_table;
@@ -276,7 +276,7 @@ struct BeamWs {
     int64_t total;
 };
 
-extern int g_beam_emb_table, g_beam_presplit;
+extern int g_beam_emb_table, g_beam_presplit, g_beam_merge_h;
 // the table costs one V x 4H x H GEMM per call and V * 4H * 4 bytes; it pays from a few decode steps on while the vocabulary is small
 static inline bool beam_emb_table(const sat_beam_args& a) {
     return g_beam_emb_table && a.embedding != nullptr && (int64_t)a.V * 4 * a.H * 4 <= ((int64_t)96 << 20) && a.max_steps >= 8;
@@ -303,8 +303,13 @@ int64_t beam_carve(const sat_beam_args& a, BeamWs<T>& w, uint8_t* base) {
         return p;
     };
     const int64_t NI = a.NI, L = a.L, D = a.D, H = a.H, V = a.V, R = NI * a.beam, S = a.max_steps + 2;
+    // with attention on, the h share of the gate pre-activations rides on the [U; f_beta] GEMM (same operand h, 4H more output
+    // columns of a launch that does not fill the GPU); the gate GEMM then contracts over [emb |] z only
+    // (fp32 mode only: a 3xTF32 k-block costs ~0.7 us, so 16 fewer of them pay for the extra addend; in bf16 mode it measured 4 % slower)
+    w.merge_h = a.attention && g_beam_merge_h && IsF32<T>::value;
+    const int64_t ufw = H + D + (w.merge_h ? 4 * H : 0);
 #define TK(field, count, type) w.field = reinterpret_cast<type*>(take((int64_t)(count) * (int64_t)sizeof(type)))
-    TK(w_att, H * D, T); TK(w_uf, (H + D) * H, T); TK(w_gall, 4 * H * (2 * H + D), T); TK(w_init, 2 * H * D, T); TK(w_out, V * H, T);
+    TK(w_att, H * D, T); TK(w_uf, ufw * H, T); TK(w_gall, 4 * H * (2 * H + D), T); TK(w_init, 2 * H * D, T); TK(w_out, V * H, T);
     TK(w_fh, a.ado ? H * H : 0, T); TK(w_fz, a.ado ? H * D : 0, T);
     // embedding share of the gate pre-activations for EVERY token, once per call: emb_gate = Emb W_ih[:, :H]^T + b_ih + b_hh
     // (V x 4H fp32).  The step's gate GEMM then contracts over [z | h] only and its epilogue adds row prev_word[r].
@@ -312,15 +317,15 @@ int64_t beam_carve(const sat_beam_args& a, BeamWs<T>& w, uint8_t* base) {
     TK(emb_t, w.emb_table ? V * H : 0, T); TK(emb_gate, w.emb_table ? V * 4 * H : 0, float);
     // fp32 mode: the weights of the three per-step GEMMs pre-split into tf32 hi / lo parts once per call (tc32::split_operand)
     w.presplit = IsF32<T>::value && g_beam_presplit && a.max_steps >= 8;
-    TK(w_uf_hi, w.presplit && a.attention ? (H + D) * H : 0, T); TK(w_uf_lo, w.presplit && a.attention ? (H + D) * H : 0, T);
+    TK(w_uf_hi, w.presplit && a.attention ? ufw * H : 0, T); TK(w_uf_lo, w.presplit && a.attention ? ufw * H : 0, T);
     TK(w_gall_hi, w.presplit ? 4 * H * (2 * H + D) : 0, T); TK(w_gall_lo, w.presplit ? 4 * H * (2 * H + D) : 0, T);
     TK(w_out_hi, w.presplit ? V * H : 0, T); TK(w_out_lo, w.presplit ? V * H : 0, T);
-    TK(b_uf, H + D, float); TK(b_g, 4 * H, float); TK(b_init, 2 * H, float);
+    TK(b_uf, ufw, float); TK(b_g, 4 * H, float); TK(b_init, 2 * H, float);
     const bool a_alias = (a.a_dtype == a.dtype) && a.a_stride_d == 1 && a.a_stride_l == D && a.a_stride_b == L * D && al16(a.img_features);
     TK(a_c, a_alias ? 0 : NI * L * D, T);
     if (a_alias) w.a_c = reinterpret_cast<T*>(const_cast<void*>(a.img_features));
     TK(wa, a.attention ? NI * L * H : 0, T); TK(abar, NI * D, T); TK(abar_f, NI * D, float); TK(mean_part, 4 * NI * D, float); TK(hc0, NI * 2 * H, float);
-    TK(X, R * (2 * H + D), T); TK(Hn, R * H, T); TK(Cc, R * H, float); TK(Cn, R * H, float); TK(UF, R * (H + D), float);
+    TK(X, R * (2 * H + D), T); TK(Hn, R * H, T); TK(Cc, R * H, float); TK(Cn, R * H, float); TK(UF, R * ufw, float);
     TK(Ctx, R * D, T); TK(P1, a.ado ? R * H : 0, T); TK(P2, a.ado ? R * H : 0, T); TK(Comb, a.ado ? R * H : 0, T);
     TK(logits, R * ((V + 7) & ~(int64_t)7), float); TK(alpha_hist, a.attention ? S * R * L : 0, float);
     w.attn_stream = a.attention && attn_s::fwd_shape_ok(a.beam, a.L, a.D, a.H);
@@ -378,7 +383,12 @@ int beam_search_t(const sat_beam_args& a) {
         SAT_TRY(pl.weight(w.w_uf + (size_t)H * H, H, a.f_beta_w, H, D, H, 0, 0));
         SAT_TRY(pl.bias(w.b_uf, a.att_U_b, nullptr, H, 0));
         SAT_TRY(pl.bias(w.b_uf + H, a.f_beta_b, nullptr, D, 0));
+        if (w.merge_h) {               // rows [H+D, H+D+4H) of the uf operand: W_hh, gate rows interleaved like w_gall; no bias there
+            SAT_TRY(pl.weight(w.w_uf + (size_t)(H + D) * H, H, a.lstm_w_hh, H, 4 * H, H, 0, H));
+            SAT_CHECK_CUDA(cudaMemsetAsync(w.b_uf + H + D, 0, (size_t)4 * H * sizeof(float), st));
+        }
     }
+    const int ufw = H + D + (w.merge_h ? 4 * H : 0);
     SAT_TRY(pl.weight(w.w_gall, xw, a.lstm_w_ih, H + D, 4 * H, H + D, 0, H));      // cols [0,H+D): [emb | ctx]
     SAT_TRY(pl.weight(w.w_gall + H + D, xw, a.lstm_w_hh, H, 4 * H, H, 0, H));      // cols [H+D, 2H+D): h
     SAT_TRY(pl.bias(w.b_g, a.lstm_b_ih, a.lstm_b_hh, 4 * H, H));
@@ -399,7 +409,7 @@ int beam_search_t(const sat_beam_args& a) {
     SAT_TRY(pl.flush(st));
     if constexpr (IsF32<T>::value) {
         if (w.presplit) {
-            if (a.attention) SAT_TRY(tc32::split_operand(st, w.w_uf_hi, w.w_uf_lo, w.w_uf, (int64_t)(H + D) * H));
+            if (a.attention) SAT_TRY(tc32::split_operand(st, w.w_uf_hi, w.w_uf_lo, w.w_uf, (int64_t)ufw * H));
             SAT_TRY(tc32::split_operand(st, w.w_gall_hi, w.w_gall_lo, w.w_gall, (int64_t)4 * H * xw));
             SAT_TRY(tc32::split_operand(st, w.w_out_hi, w.w_out_lo, w.w_out, (int64_t)V * H));
         }
@@ -448,11 +458,11 @@ int beam_search_t(const sat_beam_args& a) {
         if (!w.emb_table || a.ado)      // (the advanced deep output reads the embedding itself, decoder.py:154)
             SAT_TRY(misc::gather_rows<T>(st, w.X, xw, a.embedding, H, w.prev_word, 1, R, V));              // decoder.py:183
         if (a.attention) {
-            auto e = lin<T>(R, H + D, w.b_uf, SAT_ACT_NONE, w.UF, H + D, nullptr, 0);
-            SAT_TRY(gemm<T>(st, w.X + H + D, xw, true, w.w_uf, H, true, R, H + D, H, e, 0, 0, 0, uf_hi, uf_lo));
+            auto e = lin<T>(R, ufw, w.b_uf, SAT_ACT_NONE, w.UF, ufw, nullptr, 0);
+            SAT_TRY(gemm<T>(st, w.X + H + D, xw, true, w.w_uf, H, true, R, ufw, H, e, 0, 0, 0, uf_hi, uf_lo));
             attn::FwdParams p;
             memset(&p, 0, sizeof(p));
-            p.a = w.a_c; p.wa = w.wa; p.uf = w.UF; p.ld_uf = H + D; p.v = a.att_v_w; p.bv = a.att_v_b;
+            p.a = w.a_c; p.wa = w.wa; p.uf = w.UF; p.ld_uf = ufw; p.v = a.att_v_w; p.bv = a.att_v_b;
             p.alpha = w.alpha_hist + (size_t)step * R * L; p.ld_alpha = L;
             p.ctx = w.Ctx; p.ld_ctx = D; p.z = w.X + H; p.ld_z = xw;
             p.NI = NI; p.NB = NB; p.L = L; p.D = D; p.H = H; p.gate = a.gate;
@@ -466,12 +476,14 @@ int beam_search_t(const sat_beam_args& a) {
         memset(&e, 0, sizeof(e));
         e.bias = w.b_g; e.c_prev = w.Cc; e.ld_cp = H; e.c_out = w.Cn; e.ld_co = H; e.h_next = w.Hn; e.ld_hn = H;
         e.M = R; e.H = H;
+        const int kh = w.merge_h ? 0 : H;      // the h columns of the operand are contracted here unless the uf GEMM already did
+        if (w.merge_h) { e.xg2 = w.UF + H + D; e.ld_xg2 = ufw; }
         if (w.emb_table) {              // gates = emb_gate[prev_word] + [z | h] [W_ih[:, H:] | W_hh]^T
             e.bias = nullptr; e.xg = w.emb_gate; e.ld_xg = 4 * H; e.xg_rows = w.prev_word;
-            SAT_TRY(gemm<T>(st, w.X + H, xw, true, w.w_gall + H, xw, true, R, 4 * H, D + H, e, 0, 0, 0,
+            SAT_TRY(gemm<T>(st, w.X + H, xw, true, w.w_gall + H, xw, true, R, 4 * H, D + kh, e, 0, 0, 0,
                             w.presplit ? w.w_gall_hi + H : nullptr, w.presplit ? w.w_gall_lo + H : nullptr));      // decoder.py:196-197
         } else {
-            SAT_TRY(gemm<T>(st, w.X, xw, true, w.w_gall, xw, true, R, 4 * H, (int)xw, e, 0, 0, 0,
+            SAT_TRY(gemm<T>(st, w.X, xw, true, w.w_gall, xw, true, R, 4 * H, H + D + kh, e, 0, 0, 0,
                             w.presplit ? w.w_gall_hi : nullptr, w.presplit ? w.w_gall_lo : nullptr));              // decoder.py:196-197
         }
         if (!a.ado) {

@@ -397,7 +397,7 @@ int decoder_forward_t(const sat_decoder_args& a) {
         }
         // K3: gates = Xg[t] + [z | h] [W_ih[:,H:] | W_hh]^T, LSTM cell in the epilogue (decoder.py:108-115)
         EpiLstm<T, PRECISE> e;
-        e.xg = w.Xg + ((size_t)t * B + b0) * 4 * H; e.ld_xg = 4 * H; e.xg_rows = nullptr; e.bias = nullptr;
+        e.xg = w.Xg + ((size_t)t * B + b0) * 4 * H; e.ld_xg = 4 * H; e.xg_rows = nullptr; e.xg2 = nullptr; e.ld_xg2 = 0; e.bias = nullptr;
         e.c_prev = w.Cst + ((size_t)t * B + b0) * H; e.ld_cp = H;
         e.c_out = w.Cst + ((size_t)(t + 1) * B + b0) * H; e.ld_co = H;
         e.h_next = w.ZH + ((size_t)(t + 1) * B + b0) * zw + D; e.ld_hn = zw;

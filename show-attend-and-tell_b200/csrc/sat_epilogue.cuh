@@ -223,6 +223,8 @@ struct EpiLstm {
     const float* xg;         // fp32 [M, ld_xg] pre-activation addend (interleaved) or null
     int64_t ld_xg;
     const int64_t* xg_rows;  // null: row m of xg belongs to GEMM row m; else row xg_rows[m] (beam search: a table indexed by token id)
+    const float* xg2;        // fp32 [M, ld_xg2] second pre-activation addend (interleaved) or null (beam search: the h share of the gates)
+    int64_t ld_xg2;
     const float* bias;       // fp32 [4H] interleaved or null
     const float* c_prev;     // fp32 [M, ld_cp]
     int64_t ld_cp;
@@ -276,6 +278,7 @@ struct EpiLstm {
                     const int n = n0 + 4 * (u0 + u);
                     float p[4] = {acc[4 * (u0 + u)], acc[4 * (u0 + u) + 1], acc[4 * (u0 + u) + 2], acc[4 * (u0 + u) + 3]};
                     if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + xrow * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+                    if (xg2) { float4 x = *reinterpret_cast<const float4*>(xg2 + (int64_t)m * ld_xg2 + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
                     if (bias) { float4 x = *reinterpret_cast<const float4*>(bias + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
                     cell(p, cp[u], c[u], h[u]);
                     if (gates) store4<T>(gates + (int64_t)m * ld_g + n, p);
@@ -298,6 +301,7 @@ struct EpiLstm {
                 if (j >= H) return;
                 float p[4] = {acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]};
                 if (xg) { float4 x = *reinterpret_cast<const float4*>(xg + xrow * ld_xg + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
+                if (xg2) { float4 x = *reinterpret_cast<const float4*>(xg2 + (int64_t)m * ld_xg2 + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
                 if (bias) { float4 x = *reinterpret_cast<const float4*>(bias + n); p[0] += x.x; p[1] += x.y; p[2] += x.z; p[3] += x.w; }
                 float c, h;
                 cell(p, c_prev[(int64_t)m * ld_cp + j], c, h);
