@@ -312,7 +312,10 @@ def run_ours(args, rank, world, local_rank):
     # N > 1: gradients cross NVLink as bf16 (half the bytes of the one exchange step); SAT_GRAD_EXCHANGE=f32 switches it off
     gx = torch.float32 if (world == 1 or os.environ.get("SAT_GRAD_EXCHANGE", "bf16") == "f32") else torch.bfloat16
     trainer = FusedTrainStep(dec, lr=1e-4, alpha_c=1.0, use_cuda_graph=use_graph, grad_exchange_dtype=gx)
-    trainer.buckets = int(os.environ.get("SAT_BUCKETS", trainer.buckets))      # experiment knob: 3 = side-chain bucket exchanged + updated early
+    if "SAT_BUCKETS" in os.environ:                                               # experiment knob: 2 / 3 = bucketed exchange under the backward tail
+        trainer.buckets, trainer.overlap_allreduce = int(os.environ["SAT_BUCKETS"]), True
+    if "SAT_OVERLAP" in os.environ:                                               # experiment knob: 1 = early bucket(s) under the backward tail
+        trainer.overlap_allreduce = os.environ["SAT_OVERLAP"] == "1"
     host = make_host_batches(2, B, seed0=42 + 10 * rank)
     dev_batches = [(a.to(dev, non_blocking=True), c.to(dev, non_blocking=True)) for a, c in host]
     torch.cuda.synchronize()
@@ -525,7 +528,8 @@ def run_ours(args, rank, world, local_rank):
                        "optimizer": "fused Adam inside the timed step", "dropout": "train mode (p=0.5)", "loss": loss_val,
                        "launch": graph_note or ("one CUDA graph replay per step (mask, forward, loss, backward, all-reduce, Adam captured)"
                                                 if trainer.use_cuda_graph else "eager kernel launches"),
-                       "grad_exchange": None if world == 1 else (f"bf16 all-reduce (NCCL over NVLink), {trainer.buckets} buckets, the early one(s) under the backward tail"
+                       "grad_exchange": None if world == 1 else ((f"bf16 all-reduce (NCCL over NVLink), {trainer.buckets} buckets, the early one(s) under the backward tail" if trainer.overlap_allreduce
+                                                                   else "bf16 all-reduce (NCCL over NVLink), one exchange after the backward pass")
                                                                   if gx == torch.bfloat16 else f"fp32 all-reduce (NCCL over NVLink), {trainer.buckets} buckets"),
                        "repeats": f"median of {args.repeats} timed regions of {args.steps} steps", "repeats_ms_per_step": reps,
                        "host_numa": numa},

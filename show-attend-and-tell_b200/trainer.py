@@ -59,11 +59,14 @@ class FusedTrainStep:
         self.offsets = offsets
         self.n_early = max([offsets[k] + ((named[k].numel() + 3) & ~3) for k in early], default=0)
         self.n_side = min([offsets[k] for k in last], default=n)          # [n_early, n_side): side-chain gradients; [n_side, n): last
-        self.overlap_allreduce = True
-        # buckets = 2 (default): early bucket under the backward tail, the rest after the pass, one Adam launch.  buckets = 3: the
-        # side-chain bucket is exchanged AND updated under the main chain as well (_finish_step).  Measured on 8 x B200 at c2
-        # (profiles/r2_bench_c2_n8*.json): 3.78 ms per step with 2 buckets, 3.82 ms with 3 -- the extra NCCL kernels and the early
-        # Adam compete with the HBM-bound `sum_t dpre` pass they run beside; on one GPU the two are equal (3.62 ms).
+        # Gradient exchange schedule.  overlap_allreduce = False (default): ONE all-reduce of the whole flat buffer after the backward
+        # pass.  True: buckets exchanged on a comm stream as sat_decoder_backward finishes them -- buckets = 2: the early bucket (initial
+        # state + LSTM weights, 62 % of the bytes) under the backward tail, the rest after the pass; buckets = 3: the side-chain bucket
+        # exchanged AND updated under the main chain as well (_finish_step).  The overlapped schedules won in round 1 (tail 560 us, one
+        # busy chain); with the round-2 tail (three chains that fill the GPU, 120 us shorter) NCCL's CTAs and the casts take SMs and HBM
+        # from the chain that ends the step.  Measured at c2, ms per step (profiles/r2_bench_c2_n8*.json, r2_exchange_schedule.txt):
+        #   8 x B200: one exchange 3.657, two buckets 3.700, three buckets 3.745;  2 x B200: one exchange 3.575, two buckets 3.593.
+        self.overlap_allreduce = False
         self.buckets = 2
         self._comm_stream = None
         # grad_exchange_dtype = torch.bfloat16: the gradients cross NVLink in half the bytes (cast -> all-reduce -> Adam reads the
