@@ -23,6 +23,7 @@ int g_beam_merge_h = 1;    // beam search: W_hh h computed by the [U; f_beta] GE
 int g_beam_presplit = 1;   // beam search, fp32 mode: per-step GEMM weights pre-split into tf32 hi / lo once per call
 int g_beam_emb_table = 1;  // beam search: embedding share of the gate GEMM from a once-per-call table (sat_beam.cuh)
 int g_dpre_recompute = 1;   // streaming attention backward stores de_t only; sum_t dpre_t is rebuilt in one pass over Wa (misc::dpre_sum)
+int g_pack_split = 1;       // forward head: weight packing other than w_att on the side stream beside K1 (sat_set_tail_overlap(100 + ..) = off)
 int g_tail_hp = 1;          // main chain of the backward tail on a highest-priority internal stream (sat_set_tail_overlap(10 + mode))
 int g_tail_overlap = 3;   // backward tail as a main chain + a side chain that itself forks onto two streams (sat_decoder.cuh)
 int g_gemm_max_split = 4;      // clusters of 8 launch slower than they save (tools/gemm_bench.cu)
@@ -99,7 +100,7 @@ int sat_set_gemm_splitk(int max_split) { g_gemm_max_split = max_split >= 1 ? max
 int sat_set_pdl(int on) { g_pdl = on ? 1 : 0; return SAT_OK; }
 int sat_set_gemm_static_weights(int on) { g_gemm_static_b = on ? 1 : 0; return SAT_OK; }
 int sat_set_dpre_recompute(int on) { g_dpre_recompute = on ? 1 : 0; return SAT_OK; }
-int sat_set_tail_overlap(int on) { g_tail_hp = (on >= 10); on %= 10; g_tail_overlap = (on == 2 || on == 3) ? on : (on ? 1 : 0); g_head_overlap = on ? 1 : 0; return SAT_OK; }
+int sat_set_tail_overlap(int on) { g_pack_split = on >= 100 ? 0 : 1; on %= 100; g_tail_hp = (on >= 10); on %= 10; g_tail_overlap = (on == 2 || on == 3) ? on : (on ? 1 : 0); g_head_overlap = on ? 1 : 0; return SAT_OK; }
 int sat_set_fused_cell_backward(int on) { g_fuse_cell_bwd = on ? 1 : 0; return SAT_OK; }
 /* debug: on = 1 arms the phase stamps of the in-loop GEMMs (gate GEMM = id 1, dz GEMM = id 2); the call also copies the last
  * stamps (nanoseconds of %globaltimer, 8 per id) into out[2][8] when out is not NULL (synchronises the device) */

@@ -53,7 +53,7 @@ static inline bool al16(const void* p) { return ((uintptr_t)p & 15) == 0; }
 // space; a half is only a row range [b0, b0 + nb) of every time-major slice.  The side stream and its two events are
 // created once per host thread and device; the caller's stream forks into it before the loop and joins after it.
 // ---------------------------------------------------------------------------------------------------
-extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap, g_dpre_recompute, g_tail_hp;
+extern int g_dec_split, g_split_attn_ctas, g_split_gemm_sms, g_split_chain, g_tail_overlap, g_fuse_cell_bwd, g_head_overlap, g_dpre_recompute, g_tail_hp, g_pack_split;
 struct SideStream { cudaStream_t s, s2, hp; cudaEvent_t fork, join, join2, joinhp, attn_done[2], early, side; bool ok; };
 static inline int side_stream(SideStream** out) {
     static thread_local SideStream cache[32] = {};
@@ -234,12 +234,15 @@ static inline int check_args(const sat_decoder_args* a) {
 // ---------------------------------------------------------------------------------------------------
 // forward
 // ---------------------------------------------------------------------------------------------------
+// `rest`: stream of everything but the encoder projection's weight.  K1 needs only w_att; when the forward head forks (g_head_overlap)
+// the other 80 MB of packing traffic go out on the side stream, BESIDE the tensor-bound K1 instead of in front of it.
 template <typename T>
-int prep_weights(const sat_decoder_args& a, DecWs<T>& w, cudaStream_t st) {
+int prep_weights(const sat_decoder_args& a, DecWs<T>& w, cudaStream_t st, cudaStream_t rest) {
     const int D = a.D, H = a.H, V = a.V;
-    misc::PackList<T> pl;       // every packing job of the call goes out in one launch
+    misc::PackList<T> pl;       // the packing jobs of a stream go out in one launch
     if (a.attention) {
         SAT_TRY(pl.weight(w.w_att, D, a.att_W_w, D, H, D, 0, 0));
+        if (rest != st) SAT_TRY(pl.flush(st));
         SAT_TRY(pl.weight(w.w_uf, H, a.att_U_w, H, H, H, 0, 0));                       // rows [0,H): U
         SAT_TRY(pl.weight(w.w_uf + (size_t)H * H, H, a.f_beta_w, H, D, H, 0, 0));       // rows [H,H+D): f_beta
         SAT_TRY(pl.bias(w.b_uf, a.att_U_b, nullptr, H, 0));
@@ -262,7 +265,7 @@ int prep_weights(const sat_decoder_args& a, DecWs<T>& w, cudaStream_t st) {
     } else {
         SAT_TRY(pl.weight(w.w_out, H, a.deep_w, H, V, H, 0, 0));
     }
-    return pl.flush(st);
+    return pl.flush(rest);
 }
 
 // output layer for steps [t0, t0+nt): nt == T (teacher forcing: one GEMM over all (t,b) rows) or nt == 1.
@@ -314,8 +317,6 @@ int decoder_forward_t(const sat_decoder_args& a) {
     const int B = a.B, L = a.L, D = a.D, H = a.H, V = a.V, Tn = a.T;
     const int64_t zw = D + H;
     SAT_CHECK_CUDA(cudaMemsetAsync(w.flags, 0, 4 * sizeof(int), st));
-    SAT_TRY(prep_weights<T>(a, w, st));
-
     // features in compute dtype, contiguous (Q20)
     if (reinterpret_cast<const void*>(w.a_c) != a.img_features) {
         if (a.a_dtype == SAT_DTYPE_F32)
@@ -335,6 +336,7 @@ int decoder_forward_t(const sat_decoder_args& a) {
         SAT_CHECK_CUDA(cudaEventRecord(hd->fork, st));
         SAT_CHECK_CUDA(cudaStreamWaitEvent(sh, hd->fork, 0));
     }
+    SAT_TRY(prep_weights<T>(a, w, st, g_pack_split ? sh : st));
     if (a.attention) {
         // K1: hoisted encoder projection Wa = a W^T + b_W (attention.py:16, Q3)
         auto e = lin<T>(B * L, H, a.att_W_b, SAT_ACT_NONE, nullptr, 0, w.wa, H);
